@@ -1,0 +1,143 @@
+/* msgat_sm100.h -- C ABI of libmsgat_sm100.so, the B200 (sm_100a) implementation of the
+ * MS-GAT multirelational attention hot path.
+ *
+ * The reference (luokn/ms-gat) is pure Python/PyTorch and has no FFI: its seam for this
+ * path is the nn.Module API of src/models.  The entry points below are
+ * what the torch.autograd.Functions behind those modules bind through ctypes
+ * (msgat_b200/_lib.py); INTEGRATION.md shows the reference-side stub.  Each entry point
+ * names the reference code it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to fp32 (or int32 where typed so) unless noted;
+ *   - signals are [B, C, N, T] with T == 12 innermost (reference layout, msgat.py:121);
+ *     the (n, t) plane must be contiguous, batch and channel strides are explicit;
+ *   - the library never allocates caller-visible memory: outputs, saved statistics and
+ *     scratch are caller-owned buffers whose sizes msgat_meam_sizes() reports;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), nothing
+ *     synchronises the device;
+ *   - return value 0 on success, negative on error; msgat_last_error() gives the text.
+ *     No CPU fallback exists: without an sm_100 device msgat_device_check() fails.
+ */
+#ifndef MSGAT_SM100_H
+#define MSGAT_SM100_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSGAT_T 12        /* in_timesteps is always timesteps_per_hour = 12 (main.py:45) */
+#define MSGAT_RANK 10     /* hard-coded rank of Wt1/Wt2 (attention.py:58-59) */
+#define MSGAT_MAX_CONV 4  /* longest TACN chain: msgat96 [1,1,2,2] (msgat.py:229) */
+
+/* msgat_meam_desc.flags */
+#define MSGAT_F_LN 1          /* LayerNorm([T]) on the input first          (msgat.py:122) */
+#define MSGAT_F_RES 2         /* + Conv2d 1x1 residual of the raw input      (msgat.py:131) */
+#define MSGAT_F_RELU 4        /* ReLU on the sum                             (msgat.py:131) */
+#define MSGAT_F_CMIX 8        /* CACN: Conv2d 1x1 (+bias) after the attention (msgat.py:94) */
+#define MSGAT_F_SMIX 16       /* GACN: x W^T after the attention             (msgat.py:27)  */
+#define MSGAT_F_DOUT_MASKED 32 /* backward: dout already carries the ReLU mask */
+#define MSGAT_F_X_IS_RELU 64  /* backward: x is the ReLU output of the previous MEAM; dx is
+                                 returned already multiplied by (x > 0) so that the previous
+                                 MEAM can set MSGAT_F_DOUT_MASKED */
+
+#define MSGAT_PREC_FP32 0 /* CUDA-core fp32 everywhere (1e-5 path) */
+#define MSGAT_PREC_TF32 1 /* tcgen05 kind::tf32 for the N x N spatial contractions (2e-3 path) */
+
+/* One MEAM-shaped operator.  With all three widths set, LN|RES|RELU|CMIX|SMIX it is
+ * MEAM.forward (msgat.py:121-131); with a single width and no flags it is the bare
+ * ChannelAttention / TemporalAttention / GraphAttention (attention.py:91,62,32); with
+ * CMIX / n_conv / SMIX it is CACN / TACN / GACN (msgat.py:96,76,25). */
+typedef struct msgat_meam_desc {
+  int32_t B, C, N;      /* batch, input channels, nodes */
+  int32_t Oc, Ot, Os;   /* output widths of the channel / temporal / spatial branch, 0 = absent.
+                           Without CMIX Oc == C, without convs Ot == C, without SMIX Os == C. */
+  int32_t flags;
+  int32_t n_conv;       /* TACN: number of dilated causal convs, 0..MSGAT_MAX_CONV */
+  int32_t dil[MSGAT_MAX_CONV];
+  int32_t precision;    /* MSGAT_PREC_* */
+  int32_t reserved;
+  int64_t x_sb, x_sc;   /* element strides of x over batch and channel */
+} msgat_meam_desc;
+
+/* Parameters, named after the reference state_dict. */
+typedef struct msgat_meam_params {
+  const float *ln_w, *ln_b;               /* ln.weight, ln.bias            [12]            */
+  const float *res_w, *res_b;             /* res.weight [O,C,1,1], res.bias [O]            */
+  const float *ca_Wc, *ca_alpha;          /* cacn.seq.0.Wc [12,12], .alpha [N]             */
+  const float *ca_w, *ca_b;               /* cacn.seq.1.weight [Oc,C,1,1], .bias [Oc]      */
+  const float *ta_Wt1, *ta_Wt2, *ta_alpha; /* tacn.seq.0.Wt1/Wt2 [10,N], .alpha [C]        */
+  const float *conv_w[MSGAT_MAX_CONV];    /* tacn.seq.{1,3,..}.weight [Ot,Cin,1,2]         */
+  const float *conv_b[MSGAT_MAX_CONV];    /* tacn.seq.{1,3,..}.bias   [Ot]                 */
+  const float *sa_W;                      /* gacn.W [Os,C]                                 */
+  const float *sa_Wg, *sa_alpha;          /* gacn.gatt.Wg [12,12], .alpha [C]              */
+} msgat_meam_params;
+
+/* Gradients of the same parameters (written, not accumulated). Null = not wanted. */
+typedef struct msgat_meam_grads {
+  float *ln_w, *ln_b, *res_w, *res_b, *ca_Wc, *ca_alpha, *ca_w, *ca_b;
+  float *ta_Wt1, *ta_Wt2, *ta_alpha;
+  float *conv_w[MSGAT_MAX_CONV], *conv_b[MSGAT_MAX_CONV];
+  float *sa_W, *sa_Wg, *sa_alpha;
+} msgat_meam_grads;
+
+/* Sparse view of the (constant) normalised adjacency, built once by msgat_adj_build
+ * (replaces the dense [N,N] fp32 parameter of msgat.py:190 on the data path). */
+typedef struct msgat_adj {
+  int32_t N, nnz;
+  const int32_t *row_ptr;  /* [N+1]   CSR                                           */
+  const int32_t *col_idx;  /* [nnz]                                                 */
+  const float *val;        /* [nnz]                                                 */
+  const int32_t *csc_ptr;  /* [N+1]   CSC of the same pattern                       */
+  const int32_t *csc_row;  /* [nnz]   row of each CSC entry                         */
+  const int32_t *csc_eid;  /* [nnz]   index of that entry in the CSR arrays         */
+} msgat_adj;
+
+const char *msgat_version(void);
+const char *msgat_last_error(void);
+/* 0 iff the current device is compute capability 10.x. */
+int msgat_device_check(void);
+
+/* Adjacency preparation.  count: per-row non-zeros of dense adj [N,N] into row_nnz[N] and
+ * col_nnz[N].  fill: given exclusive scans row_ptr/csc_ptr [N+1] (caller computes them),
+ * write col_idx/val and csc_row/csc_eid. */
+int msgat_adj_count(const float *adj, int32_t N, int32_t *row_nnz, int32_t *col_nnz, void *stream);
+int msgat_adj_fill(const float *adj, int32_t N, const int32_t *row_ptr, const int32_t *csc_ptr,
+                   int32_t *col_idx, float *val, int32_t *csc_row, int32_t *csc_eid, void *stream);
+
+/* Sizes, in floats, of the `saved` buffer (forward -> backward) and of `scratch`
+ * (max of forward and backward needs) for this descriptor and adjacency nnz. */
+int msgat_meam_sizes(const msgat_meam_desc *d, int32_t nnz, int64_t *saved_floats, int64_t *scratch_floats);
+
+/* Forward of the MEAM-shaped operator: x [B,C,N,12] -> out [B,Oc+Ot+Os,N,12] (contiguous). */
+int msgat_meam_forward(const msgat_meam_desc *d, const msgat_meam_params *p, const msgat_adj *adj,
+                       const float *x, float *out, float *saved, float *scratch, void *stream);
+
+/* Backward: dout [B,O,N,12] contiguous -> dx [B,C,N,12] contiguous and parameter grads.
+ * `out` is the forward output (ReLU mask) and may be null when DOUT_MASKED or no RELU. */
+int msgat_meam_backward(const msgat_meam_desc *d, const msgat_meam_params *p, const msgat_adj *adj,
+                        const float *x, const float *out, const float *dout, const float *saved,
+                        float *scratch, float *dx, const msgat_meam_grads *g, void *stream);
+
+/* TPC head (msgat.py:158-160) fused with the time-embedding gate of MSGAT.forward
+ * (msgat.py:204): y[b,n,o] = (sum_{c,t} fc_w[o,t,0,c] LN_T(x)[b,c,n,t] + fc_b[o]);
+ * out[b,n,o] (+)= y * gate[b,n,o] (gate null = 1).  head_out keeps y for the backward. */
+typedef struct msgat_head_desc {
+  int32_t B, C, N, Tout;
+  int32_t accumulate;   /* forward: out += instead of out = */
+  int32_t x_is_relu;    /* backward: return dx * (x > 0) */
+  int64_t gate_sb;      /* batch stride of gate (elements); (n,o) contiguous */
+} msgat_head_desc;
+int msgat_head_forward(const msgat_head_desc *d, const float *x, const float *ln_w, const float *ln_b,
+                       const float *fc_w, const float *fc_b, const float *gate, float *head_out,
+                       float *out, void *stream);
+int64_t msgat_head_scratch_floats(const msgat_head_desc *d);
+int msgat_head_backward(const msgat_head_desc *d, const float *x, const float *ln_w, const float *ln_b,
+                        const float *fc_w, const float *gate, const float *head_out, const float *dout,
+                        float *dx, float *d_ln_w, float *d_ln_b, float *d_fc_w, float *d_fc_b,
+                        float *d_gate, float *scratch, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,138 @@
+// api.cu -- the extern "C" surface declared in include/msgat_sm100.h.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "compat.cuh"
+#include "kernels.h"
+
+static thread_local char g_err[512] = "";
+
+void msgat_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    msgat_set_error("%s: %s", what, cudaGetErrorString(e));
+    return -100;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// adjacency: dense [N,N] -> CSR + CSC (data_loader.py:59-66 produces the dense matrix;
+// msgat.py:190 stores it).  Built once per adjacency by the Python wrapper.
+MSGAT_KERNEL k_adj_count(const float* adj, int N, int32_t* row_nnz, int32_t* col_nnz) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  int rc = 0, cc = 0;
+  for (int j = 0; j < N; ++j) {
+    rc += adj[(int64_t)r * N + j] != 0.f;
+    cc += adj[(int64_t)j * N + r] != 0.f;
+  }
+  row_nnz[r] = rc;
+  col_nnz[r] = cc;
+}
+
+MSGAT_KERNEL k_adj_fill_rows(const float* adj, int N, const int32_t* row_ptr, int32_t* col_idx, float* val) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  int e = row_ptr[r];
+  for (int j = 0; j < N; ++j) {
+    const float v = adj[(int64_t)r * N + j];
+    if (v != 0.f) { col_idx[e] = j; val[e] = v; ++e; }
+  }
+}
+
+MSGAT_KERNEL k_adj_fill_cols(const float* adj, int N, const int32_t* row_ptr, const int32_t* col_idx,
+                             const int32_t* csc_ptr, int32_t* csc_row, int32_t* csc_eid) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  int k = csc_ptr[c];
+  for (int r = 0; r < N; ++r) {
+    if (adj[(int64_t)r * N + c] == 0.f) continue;
+    // position of column c inside CSR row r (columns ascending)
+    int e = row_ptr[r];
+    while (col_idx[e] != c) ++e;
+    csc_row[k] = r;
+    csc_eid[k] = e;
+    ++k;
+  }
+}
+
+extern "C" {
+
+const char* msgat_version(void) { return "msgat_sm100 0.1 (sm_100a)"; }
+const char* msgat_last_error(void) { return g_err; }
+
+int msgat_device_check(void) {
+#ifdef MSGAT_EMU
+  return 0;
+#else
+  int dev = 0;
+  cudaDeviceProp prop;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    msgat_set_error("no CUDA device");
+    return -1;
+  }
+  if (prop.major != 10) {
+    msgat_set_error("libmsgat_sm100 needs compute capability 10.x (B200), found %d.%d", prop.major, prop.minor);
+    return -2;
+  }
+  return 0;
+#endif
+}
+
+int msgat_adj_count(const float* adj, int32_t N, int32_t* row_nnz, int32_t* col_nnz, void* stream) {
+  MSGAT_LAUNCH(k_adj_count, dim3((N + 127) / 128), dim3(128), 0, stream, adj, N, row_nnz, col_nnz);
+  return check_launch("adj_count");
+}
+
+int msgat_adj_fill(const float* adj, int32_t N, const int32_t* row_ptr, const int32_t* csc_ptr, int32_t* col_idx,
+                   float* val, int32_t* csc_row, int32_t* csc_eid, void* stream) {
+  MSGAT_LAUNCH(k_adj_fill_rows, dim3((N + 127) / 128), dim3(128), 0, stream, adj, N, row_ptr, col_idx, val);
+  MSGAT_LAUNCH(k_adj_fill_cols, dim3((N + 127) / 128), dim3(128), 0, stream, adj, N, row_ptr, (const int32_t*)col_idx,
+               csc_ptr, csc_row, csc_eid);
+  return check_launch("adj_fill");
+}
+
+int msgat_meam_sizes(const msgat_meam_desc* d, int32_t nnz, int64_t* saved_floats, int64_t* scratch_floats) {
+  Plan p;
+  int rc = make_plan(d, nnz, &p);
+  if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
+  int64_t bs = meam_backward_scratch(p);
+  if (bs < 0) { msgat_set_error("unsupported MEAM descriptor for backward (code %lld)", (long long)bs); return (int)bs; }
+  *saved_floats = p.saved_total;
+  *scratch_floats = p.fwd_scratch > bs ? p.fwd_scratch : bs;
+  return 0;
+}
+
+int msgat_meam_forward(const msgat_meam_desc* d, const msgat_meam_params* prm, const msgat_adj* adj, const float* x,
+                       float* out, float* saved, float* scratch, void* stream) {
+  Plan p;
+  int rc = make_plan(d, adj ? adj->nnz : 0, &p);
+  if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
+  if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  rc = meam_forward_impl(p, prm, adj, x, out, saved, scratch, stream);
+  if (rc) return rc;
+  return check_launch("meam_forward");
+}
+
+int msgat_meam_backward(const msgat_meam_desc* d, const msgat_meam_params* prm, const msgat_adj* adj, const float* x,
+                        const float* out, const float* dout, const float* saved, float* scratch, float* dx,
+                        const msgat_meam_grads* g, void* stream) {
+  Plan p;
+  int rc = make_plan(d, adj ? adj->nnz : 0, &p);
+  if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
+  if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  rc = meam_backward_impl(p, prm, adj, x, out, dout, saved, scratch, dx, g, stream);
+  if (rc) return rc;
+  return check_launch("meam_backward");
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+// compat.cuh -- one spelling of launch / shared-memory / qualifiers for two builds:
+//   * the product build: nvcc -gencode arch=compute_100a,code=sm_100a (libmsgat_sm100.so)
+//   * the debug build used by tests/emu only: g++ -DMSGAT_EMU with tests/emu/emu_runtime.h,
+//     which runs the same kernel bodies as host fibers (the build container has no GPU).
+// The product never contains or loads the emulated build.
+#pragma once
+#include <stdint.h>
+
+#ifdef MSGAT_EMU
+#include "emu_runtime.h"
+#define MSGAT_KERNEL static void
+#define MSGAT_DEV static inline
+#define MSGAT_LB(n, m)
+#define MSGAT_RESTRICT __restrict__
+#define MSGAT_DYN_SMEM(name) unsigned char* name = emu::cur()->smem
+#define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...) \
+  emu::launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
+#define MSGAT_UNROLL
+#else
+#include <cuda_runtime.h>
+#define MSGAT_KERNEL __global__ void
+#define MSGAT_DEV __device__ __forceinline__
+#define MSGAT_LB(n, m) __launch_bounds__(n, m)
+#define MSGAT_RESTRICT __restrict__
+#define MSGAT_DYN_SMEM(name) extern __shared__ __align__(1024) unsigned char name[]
+#define MSGAT_MAX_SMEM 232448
+#define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...)                                        \
+  do {                                                                                            \
+    static bool _attr = false;                                                                    \
+    if (!_attr) {                                                                                 \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MSGAT_MAX_SMEM);    \
+      _attr = true;                                                                               \
+    }                                                                                             \
+    kern<<<(grid), (block), (smem), (cudaStream_t)(stream)>>>(__VA_ARGS__);                       \
+  } while (0)
+#define MSGAT_UNROLL _Pragma("unroll")
+#endif
+
+#define MSGAT_T12 12
+
+MSGAT_DEV float warp_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+MSGAT_DEV float warp_max(float v) {
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 16));
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 8));
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 4));
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 2));
+  v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));
+  return v;
+}
+
+MSGAT_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+MSGAT_DEV void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+MSGAT_DEV float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+MSGAT_DEV void fma4(float4& a, float w, const float4& x) {
+  a.x = fmaf(w, x.x, a.x); a.y = fmaf(w, x.y, a.y); a.z = fmaf(w, x.z, a.z); a.w = fmaf(w, x.w, a.w);
+}
+MSGAT_DEV float dot4(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+// value of a 12-step row at t-d for t = t0..t0+3, given the quad at t0 and the quad before it
+// (zeros when t0 == 0): the causal "past" tap of Conv2d(k=[1,2], dilation d) + Chomp(d).
+MSGAT_DEV float4 quad_past(const float* row, int t0, int d) {
+  float4 r;
+  int t = t0 - d;
+  r.x = (t >= 0) ? row[t] : 0.f;
+  r.y = (t + 1 >= 0) ? row[t + 1] : 0.f;
+  r.z = (t + 2 >= 0) ? row[t + 2] : 0.f;
+  r.w = (t + 3 >= 0) ? row[t + 3] : 0.f;
+  return r;
+}
+// value at t+d (transpose of the past tap), zero beyond the 12-step window
+MSGAT_DEV float4 quad_future(const float* row, int t0, int d) {
+  float4 r;
+  int t = t0 + d;
+  r.x = (t < MSGAT_T12) ? row[t] : 0.f;
+  r.y = (t + 1 < MSGAT_T12) ? row[t + 1] : 0.f;
+  r.z = (t + 2 < MSGAT_T12) ? row[t + 2] : 0.f;
+  r.w = (t + 3 < MSGAT_T12) ? row[t + 3] : 0.f;
+  return r;
+}

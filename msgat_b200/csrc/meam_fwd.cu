@@ -1,0 +1,412 @@
+// meam_fwd.cu -- forward of the MEAM-shaped operator (reference msgat.py:121-131 and the
+// three attentions of attention.py) as four launches:
+//   k_prep    reads x once: LayerNorm_T, the spatial query q_s, the temporal query q_t,
+//             Z = W h (or h) for the spatial gather, per-tile partial sums of the two
+//             per-sample reductions (channel query over N, temporal keys over N);
+//   k_small   per sample: finish the reductions, C x C and 12 x 12 softmaxes, fold the
+//             1x1 conv of CACN into the channel attention (Mc = W1 Pc);
+//   k_sstats  (spatial.cu) softmax statistics of q Wg q^T over ALL N columns + the
+//             attention weights at the adjacency non-zeros;
+//   k_apply   reads x again: LN, residual 1x1, Mc h, temporal attention + dilated causal
+//             conv chain, sparse spatial aggregation, concat, ReLU, one write of the output.
+// The N x N attention matrix never exists in HBM.
+#include "kernels.h"
+#include "tile_ops.cuh"
+
+// ---------------------------------------------------------------------------------------
+struct PrepArgs {
+  const float* x; int64_t x_sb, x_sc;
+  int C, N, Oc, Ot, Os, Cz, s_pre, do_ln, ntile;
+  const float *ln_w, *ln_b, *sa_alpha, *ta_alpha, *ca_alpha, *Wt1, *Wt2, *sa_W;
+  float *qs, *qt, *Z, *pqc, *pK;
+};
+
+template <int NT>
+MSGAT_KERNEL MSGAT_LB(256, 1) k_prep(PrepArgs a) {
+  constexpr int P = NT * 12, PS = P + 4, PQ = NT * 3;
+  MSGAT_DYN_SMEM(smem_raw);
+  float* H = reinterpret_cast<float*>(smem_raw);  // [C][PS]
+  float* QT = H + a.C * PS;                       // [P]
+  float* LW = QT + P;                             // ln w,b [24]
+  float* WsT = LW + 24;                           // [C][rup4(Os)] when s_pre
+  const int tile = blockIdx.x, b = blockIdx.y, n0 = tile * NT;
+  const int WS = (a.Os + 3) & ~3;
+  if (threadIdx.x < 12) {
+    LW[threadIdx.x] = a.do_ln ? a.ln_w[threadIdx.x] : 1.f;
+    LW[12 + threadIdx.x] = a.do_ln ? a.ln_b[threadIdx.x] : 0.f;
+  }
+  if (a.s_pre) stage_wT(WsT, a.sa_W, a.Os, a.C, WS, 1, 0);
+  __syncthreads();
+  tile_load_ln(a.x + b * a.x_sb, a.x_sc, a.C, a.N, n0, NT, PS, nullptr, H, LW, LW + 12, a.do_ln, nullptr);
+  __syncthreads();
+  // spatial / temporal queries: q[n,t] = sum_c alpha[c] h[c,n,t]   (attention.py:33,63)
+  for (int p = threadIdx.x; p < P; p += blockDim.x) {
+    const int nl = p / 12, n = n0 + nl;
+    float s = 0.f, t = 0.f;
+    if (a.Os) for (int c = 0; c < a.C; ++c) s = fmaf(__ldg(a.sa_alpha + c), H[c * PS + p], s);
+    if (a.Ot) for (int c = 0; c < a.C; ++c) t = fmaf(__ldg(a.ta_alpha + c), H[c * PS + p], t);
+    QT[p] = t;
+    if (n < a.N) {
+      if (a.Os) a.qs[((int64_t)b * a.N + n0) * 12 + p] = s;
+      if (a.Ot) a.qt[((int64_t)b * a.N + n0) * 12 + p] = t;
+    }
+  }
+  // Z for the spatial aggregation: W h when that narrows the rows (msgat.py:27 commuted in
+  // front of the aggregation: A (h W^T) == (A h) W^T), else h itself.
+  if (a.Os) {
+    const int nch = (a.Cz + 3) >> 2;
+    for (int it = threadIdx.x; it < nch * PQ; it += blockDim.x) {
+      const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4, n = n0 + nl;
+      float4 acc[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+      if (a.s_pre) {
+        mix_item(acc, H, PS, a.C, WsT, WS, o0, nl, t0);
+      } else {
+        for (int j = 0; j < 4; ++j)
+          if (o0 + j < a.Cz) acc[j] = ld4(H + (o0 + j) * PS + nl * 12 + t0);
+      }
+      if (n < a.N)
+        for (int j = 0; j < 4; ++j)
+          if (o0 + j < a.Cz) st4(a.Z + (((int64_t)b * a.Cz + o0 + j) * a.N + n) * 12 + t0, acc[j]);
+    }
+  }
+  // per-tile partial of the channel query q_c[c,t] = sum_n alpha[n] h[c,n,t]  (attention.py:92)
+  if (a.Oc) {
+    float* dst = a.pqc + ((int64_t)b * a.ntile + tile) * a.C * 12;
+    for (int i = threadIdx.x; i < a.C * 12; i += blockDim.x) {
+      const int c = i / 12, t = i - c * 12;
+      float s = 0.f;
+      for (int nl = 0; nl < NT; ++nl)
+        if (n0 + nl < a.N) s = fmaf(__ldg(a.ca_alpha + n0 + nl), H[c * PS + nl * 12 + t], s);
+      dst[i] = s;
+    }
+  }
+  __syncthreads();
+  // per-tile partial of the temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T  (attention.py:65)
+  if (a.Ot) {
+    float* dst = a.pK + ((int64_t)b * a.ntile + tile) * 240;
+    for (int i = threadIdx.x; i < 240; i += blockDim.x) {
+      const int t = i / 20, r = i - t * 20;
+      const float* W = (r < 10) ? a.Wt1 + (int64_t)r * a.N : a.Wt2 + (int64_t)(r - 10) * a.N;
+      float s = 0.f;
+      for (int nl = 0; nl < NT; ++nl)
+        if (n0 + nl < a.N) s = fmaf(__ldg(W + n0 + nl), QT[nl * 12 + t], s);
+      dst[i] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+struct SmallArgs {
+  int C, Oc, Ot, cmix, ntile;
+  const float *pqc, *pK, *Wc, *ca_w;
+  float *qc, *Pc, *Mc, *K, *Pt;
+};
+
+MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.x;
+  float* qc = reinterpret_cast<float*>(smem_raw);  // [C][12]
+  float* tmp = qc + C * 12;                        // [C][12]
+  float* S = tmp + C * 12;                         // [C][C]
+  float* K = S + C * C;                            // [12][20]
+  float* St = K + 240;                             // [144]
+  if (a.Oc) {
+    for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
+      float s = 0.f;
+      for (int tl = 0; tl < a.ntile; ++tl) s += a.pqc[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      qc[i] = s;
+      a.qc[(int64_t)b * C * 12 + i] = s;
+    }
+  }
+  if (a.Ot) {
+    for (int i = threadIdx.x; i < 240; i += blockDim.x) {
+      float s = 0.f;
+      for (int tl = 0; tl < a.ntile; ++tl) s += a.pK[((int64_t)b * a.ntile + tl) * 240 + i];
+      K[i] = s;
+      a.K[(int64_t)b * 240 + i] = s;
+    }
+  }
+  __syncthreads();
+  if (a.Oc) {
+    // S = (qc Wc) qc^T, softmax over the last axis (attention.py:93)
+    for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
+      const int c = i / 12, t2 = i - c * 12;
+      float s = 0.f;
+      for (int t = 0; t < 12; ++t) s = fmaf(qc[c * 12 + t], __ldg(a.Wc + t * 12 + t2), s);
+      tmp[i] = s;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) {
+      const int c = i / C, j = i - c * C;
+      float s = 0.f;
+      for (int t = 0; t < 12; ++t) s = fmaf(tmp[c * 12 + t], qc[j * 12 + t], s);
+      S[i] = s;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float m = -INFINITY;
+      for (int j = 0; j < C; ++j) m = fmaxf(m, S[c * C + j]);
+      float l = 0.f;
+      for (int j = 0; j < C; ++j) { float e = expf(S[c * C + j] - m); S[c * C + j] = e; l += e; }
+      float inv = 1.0f / l;
+      for (int j = 0; j < C; ++j) S[c * C + j] *= inv;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) a.Pc[(int64_t)b * C * C + i] = S[i];
+    // fold the 1x1 conv of CACN (msgat.py:94) into the attention: Mc = W1 Pc
+    for (int i = threadIdx.x; i < a.Oc * C; i += blockDim.x) {
+      const int o = i / C, j = i - o * C;
+      float s;
+      if (a.cmix) {
+        s = 0.f;
+        for (int c = 0; c < C; ++c) s = fmaf(__ldg(a.ca_w + o * C + c), S[c * C + j], s);
+      } else {
+        s = S[o * C + j];
+      }
+      a.Mc[(int64_t)b * a.Oc * C + i] = s;
+    }
+  }
+  if (a.Ot) {
+    // temporal scores K1 K2^T, softmax over the last axis (attention.py:65)
+    for (int i = threadIdx.x; i < 144; i += blockDim.x) {
+      const int t = i / 12, j = i - t * 12;
+      float s = 0.f;
+      for (int r = 0; r < 10; ++r) s = fmaf(K[t * 20 + r], K[j * 20 + 10 + r], s);
+      St[i] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+      const int t = threadIdx.x;
+      float m = -INFINITY;
+      for (int j = 0; j < 12; ++j) m = fmaxf(m, St[t * 12 + j]);
+      float e[12], l = 0.f;
+      for (int j = 0; j < 12; ++j) { e[j] = expf(St[t * 12 + j] - m); l += e[j]; }
+      float inv = 1.0f / l;
+      for (int j = 0; j < 12; ++j) a.Pt[(int64_t)b * 144 + t * 12 + j] = e[j] * inv;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+struct ApplyArgs {
+  const float* x; int64_t x_sb, x_sc;
+  int C, N, O, Oc, Ot, Os, Cz, s_pre, flags, n_conv, ntile, J;
+  int dil[MSGAT_MAX_CONV];
+  const float *ln_w, *ln_b, *res_w, *res_b, *ca_b, *sa_W;
+  const float* conv_w[MSGAT_MAX_CONV];
+  const float* conv_b[MSGAT_MAX_CONV];
+  const float *Mc, *Pt, *Z, *pw;
+  const int32_t *row_ptr, *col_idx;
+  int nnz;
+  float* out;
+};
+
+template <int NT>
+MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
+  constexpr int P = NT * 12, PS = P + 4, PQ = NT * 3;
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.y;
+  const int WO = (a.O + 3) & ~3, WOc = (a.Oc + 3) & ~3, WOt = (a.Ot + 3) & ~3, WOs = (a.Os + 3) & ~3;
+  const bool has_res = a.flags & MSGAT_F_RES, smix = a.flags & MSGAT_F_SMIX;
+  // ---- carve shared memory (same order as apply_smem_floats in plan.h)
+  float* sp = reinterpret_cast<float*>(smem_raw);
+  float* X = sp; sp += C * PS;
+  float* H = sp; sp += C * PS;
+  float* OT = nullptr; if (a.Ot) { OT = sp; sp += C * PS; }
+  float* YA = nullptr; if (a.n_conv >= 2) { YA = sp; sp += a.Ot * PS; }
+  float* YB = nullptr; if (a.n_conv >= 3) { YB = sp; sp += a.Ot * PS; }
+  float* OS = nullptr; if (a.Os && !a.s_pre) { OS = sp; sp += C * PS; }
+  float *resT = nullptr, *resB = nullptr;
+  if (has_res) { resT = sp; sp += C * WO; resB = sp; sp += WO; }
+  float *McT = nullptr, *caB = nullptr;
+  if (a.Oc) { McT = sp; sp += C * WOc; caB = sp; sp += WOc; }
+  float *cvA[MSGAT_MAX_CONV], *cvP[MSGAT_MAX_CONV], *cvB[MSGAT_MAX_CONV];
+  for (int i = 0; i < a.n_conv; ++i) {
+    const int K = i == 0 ? C : a.Ot;
+    cvA[i] = sp; sp += K * WOt; cvP[i] = sp; sp += K * WOt; cvB[i] = sp; sp += WOt;
+  }
+  float* WsT = nullptr; if (a.Os && smix && !a.s_pre) { WsT = sp; sp += C * WOs; }
+  float* Pt = sp; sp += 144;
+  float* LW = sp; sp += 24;
+  // ---- stage the weights once per block (the block works on one sample only)
+  if (has_res) { stage_wT(resT, a.res_w, a.O, C, WO, 1, 0); stage_vec(resB, a.res_b, a.O, WO); }
+  if (a.Oc) {
+    stage_wT(McT, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, WOc, 1, 0);
+    stage_vec(caB, (a.flags & MSGAT_F_CMIX) ? a.ca_b : nullptr, a.Oc, WOc);
+  }
+  for (int i = 0; i < a.n_conv; ++i) {
+    const int K = i == 0 ? C : a.Ot;
+    stage_wT(cvA[i], a.conv_w[i], a.Ot, K, WOt, 2, 1);  // tap 1 multiplies x[t]
+    stage_wT(cvP[i], a.conv_w[i], a.Ot, K, WOt, 2, 0);  // tap 0 multiplies x[t-d]
+    stage_vec(cvB[i], a.conv_b[i], a.Ot, WOt);
+  }
+  if (WsT) stage_wT(WsT, a.sa_W, a.Os, C, WOs, 1, 0);
+  if (a.Ot) for (int i = threadIdx.x; i < 144; i += blockDim.x) Pt[i] = a.Pt[(int64_t)b * 144 + i];
+  const bool do_ln = a.flags & MSGAT_F_LN;
+  if (threadIdx.x < 12) {
+    LW[threadIdx.x] = do_ln ? a.ln_w[threadIdx.x] : 1.f;
+    LW[12 + threadIdx.x] = do_ln ? a.ln_b[threadIdx.x] : 0.f;
+  }
+  const int chC = (a.Oc + 3) >> 2, chT = (a.Ot + 3) >> 2, chS = (a.Os + 3) >> 2;
+  const float* pwb = a.pw + (int64_t)b * a.nnz;
+  const float* Zb = a.Z + (int64_t)b * a.Cz * a.N * 12;
+
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+    const int n0 = tile * NT;
+    __syncthreads();  // previous tile fully consumed (also orders the weight staging)
+    tile_load_ln(a.x + b * a.x_sb, a.x_sc, C, a.N, n0, NT, PS, X, H, LW, LW + 12, do_ln, nullptr);
+    __syncthreads();
+    // temporal attention apply (attention.py:66): OT[c][n][t] = sum_i Pt[t][i] H[c][n][i]
+    if (a.Ot) tile_temporal(OT, H, PS, C, NT, Pt, false, false);
+    // spatial aggregation of un-mixed rows into OS (few channels): sum over adjacency nnz
+    if (OS) {
+      for (int it = threadIdx.x; it < C * PQ; it += blockDim.x) {
+        const int c = it / PQ, pq = it - c * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, n = n0 + nl;
+        float4 acc = f4zero();
+        if (n < a.N) {
+          const int e1 = a.row_ptr[n + 1];
+          for (int e = a.row_ptr[n]; e < e1; ++e) {
+            const float w = pwb[e];
+            fma4(acc, w, ld4(Zb + ((int64_t)c * a.N + a.col_idx[e]) * 12 + t0));
+          }
+        }
+        st4(OS + c * PS + nl * 12 + t0, acc);
+      }
+    }
+    __syncthreads();
+    // intermediate convs of the TACN chain (msgat.py:68-74): no activation in between
+    const float* cin = OT;
+    for (int i = 0; i + 1 < a.n_conv; ++i) {
+      float* dst = (i & 1) ? YB : YA;
+      const int K = i == 0 ? C : a.Ot;
+      for (int it = threadIdx.x; it < chT * PQ; it += blockDim.x) {
+        const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4;
+        float4 acc[4];
+        for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
+        mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
+        for (int j = 0; j < 4; ++j)
+          if (o0 + j < a.Ot) st4(dst + (o0 + j) * PS + nl * 12 + t0, acc[j]);
+      }
+      __syncthreads();
+      cin = dst;
+    }
+    // output items: 4 output channels x 4 time steps of one node each
+    for (int it = threadIdx.x; it < (chC + chT + chS) * PQ; it += blockDim.x) {
+      const int chg = it / PQ, pq = it - chg * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, n = n0 + nl;
+      float4 acc[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+      int obase, width, o0;
+      if (chg < chC) {  // channel branch: Mc[b] h + bias  (attention.py:94 + msgat.py:94)
+        o0 = chg * 4; obase = 0; width = a.Oc;
+        for (int j = 0; j < 4; ++j) { float bj = caB[o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
+        mix_item(acc, H, PS, C, McT, WOc, o0, nl, t0);
+      } else if (chg < chC + chT) {  // temporal branch: last conv of the chain (or OT itself)
+        o0 = (chg - chC) * 4; obase = a.Oc; width = a.Ot;
+        if (a.n_conv == 0) {
+          for (int j = 0; j < 4; ++j) if (o0 + j < width) acc[j] = ld4(OT + (o0 + j) * PS + nl * 12 + t0);
+        } else {
+          const int i = a.n_conv - 1, K = i == 0 ? C : a.Ot;
+          for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
+          mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
+        }
+      } else {  // spatial branch (attention.py:36 + msgat.py:27)
+        o0 = (chg - chC - chT) * 4; obase = a.Oc + a.Ot; width = a.Os;
+        if (a.s_pre) {
+          if (n < a.N) {
+            const int e1 = a.row_ptr[n + 1];
+            for (int e = a.row_ptr[n]; e < e1; ++e) {
+              const float w = pwb[e];
+              const float* zr = Zb + (int64_t)a.col_idx[e] * 12 + t0;
+              for (int j = 0; j < 4; ++j)
+                if (o0 + j < width) fma4(acc[j], w, ld4(zr + (int64_t)(o0 + j) * a.N * 12));
+            }
+          }
+        } else if (smix) {
+          mix_item(acc, OS, PS, C, WsT, WOs, o0, nl, t0);
+        } else {
+          for (int j = 0; j < 4; ++j) if (o0 + j < width) acc[j] = ld4(OS + (o0 + j) * PS + nl * 12 + t0);
+        }
+      }
+      if (has_res) {
+        float4 r[4];
+        for (int j = 0; j < 4; ++j) { float bj = (o0 + j < width) ? resB[obase + o0 + j] : 0.f; r[j] = make_float4(bj, bj, bj, bj); }
+        // residual rows obase+o0.. may be unaligned to 4 in resT when widths are not
+        // multiples of 4 (bare attentions never have a residual), so index per row
+        const float* s = X + nl * 12 + t0;
+        for (int k = 0; k < C; ++k) {
+          float4 xv = ld4(s + k * PS);
+          const float* w = resT + k * WO + obase + o0;
+          for (int j = 0; j < 4; ++j) if (o0 + j < width) fma4(r[j], w[j], xv);
+        }
+        for (int j = 0; j < 4; ++j) { acc[j].x += r[j].x; acc[j].y += r[j].y; acc[j].z += r[j].z; acc[j].w += r[j].w; }
+      }
+      if (n < a.N) {
+        for (int j = 0; j < 4; ++j) {
+          if (o0 + j >= width) continue;
+          float4 v = acc[j];
+          if (a.flags & MSGAT_F_RELU) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          st4(a.out + (((int64_t)b * a.O + obase + o0 + j) * a.N + n) * 12 + t0, v);
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+static int pick_threads(int items, int cap) {
+  int rounds = (items + cap - 1) / cap;
+  int t = (items + rounds - 1) / rounds;
+  t = (t + 31) & ~31;
+  return t < 64 ? 64 : t;
+}
+
+int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
+                      float* saved, float* scratch, void* stream) {
+  const bool do_ln = p.flags & MSGAT_F_LN;
+  {
+    PrepArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
+    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre; a.do_ln = do_ln;
+    a.ntile = p.ntile_p;
+    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.sa_alpha = prm->sa_alpha; a.ta_alpha = prm->ta_alpha;
+    a.ca_alpha = prm->ca_alpha; a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.sa_W = prm->sa_W;
+    a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
+    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
+    constexpr int NT = 16;
+    size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
+    MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B), dim3(256), smem, stream, a);
+  }
+  if (p.Oc || p.Ot) {
+    SmallArgs a;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = p.ntile_p;
+    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK; a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w;
+    a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
+    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 4;
+    MSGAT_LAUNCH(k_small, dim3(p.B), dim3(256), smem, stream, a);
+  }
+  if (p.Os) launch_sstats(p, prm, adj, saved, stream);
+  {
+    ApplyArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
+    a.C = p.C; a.N = p.N; a.O = p.O; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre;
+    a.flags = p.flags; a.n_conv = p.n_conv; a.ntile = p.ntile_a;
+    for (int i = 0; i < MSGAT_MAX_CONV; ++i) { a.dil[i] = p.dil[i]; a.conv_w[i] = prm->conv_w[i]; a.conv_b[i] = prm->conv_b[i]; }
+    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.res_b = prm->res_b; a.ca_b = prm->ca_b;
+    a.sa_W = prm->sa_W;
+    a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
+    a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr; a.nnz = p.nnz;
+    a.out = out;
+    int J = (2 * 148 + p.B - 1) / p.B;
+    if (J > p.ntile_a) J = p.ntile_a;
+    if (J < 1) J = 1;
+    a.J = J;
+    const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
+    size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
+    switch (p.NTa) {
+      case 16: MSGAT_LAUNCH(k_apply<16>, dim3(J, p.B), dim3(pick_threads(chunks * 48, 512)), smem, stream, a); break;
+      case 8: MSGAT_LAUNCH(k_apply<8>, dim3(J, p.B), dim3(pick_threads(chunks * 24, 512)), smem, stream, a); break;
+      case 4: MSGAT_LAUNCH(k_apply<4>, dim3(J, p.B), dim3(pick_threads(chunks * 12, 512)), smem, stream, a); break;
+      default: MSGAT_LAUNCH(k_apply<2>, dim3(J, p.B), dim3(pick_threads(chunks * 6, 512)), smem, stream, a); break;
+    }
+  }
+  return 0;
+}

@@ -1,0 +1,160 @@
+"""torch.autograd.Functions over the C ABI (``include/msgat_sm100.h``).
+
+``meam_op`` is the one MEAM-shaped operator every layer class of the reference maps to
+(``MEAM`` msgat.py:121, ``CACN``/``TACN``/``GACN`` msgat.py:96/76/25 and the three bare
+attentions attention.py:91/62/32); ``head_op`` is the TPC head fused with the time gate
+(msgat.py:158-160,204).  PyTorch only owns memory and streams here: every FLOP of the
+path runs in the hand-written kernels of ``csrc/``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+SLOTS = (["ln_w", "ln_b", "res_w", "res_b", "ca_Wc", "ca_alpha", "ca_w", "ca_b", "ta_Wt1", "ta_Wt2", "ta_alpha"]
+         + [f"conv_{k}{i}" for i in range(_lib.MAX_CONV) for k in ("w", "b")] + ["sa_W", "sa_Wg", "sa_alpha"])
+
+
+class SparseAdjacency:
+    """CSR + CSC view of the constant normalised adjacency (msgat.py:190), built on the
+    device by ``msgat_adj_count`` / ``msgat_adj_fill``."""
+
+    def __init__(self, adj: torch.Tensor):
+        lib = _lib.get()
+        adj = adj.detach().to(torch.float32).contiguous()
+        N = adj.shape[0]
+        assert adj.shape == (N, N)
+        dev = adj.device
+        st = _lib.stream_of(adj)
+        rn = torch.empty(N, dtype=torch.int32, device=dev)
+        cn = torch.empty(N, dtype=torch.int32, device=dev)
+        _lib.check(lib.msgat_adj_count(_lib.ptr(adj), N, _lib.ptr(rn), _lib.ptr(cn), st), "msgat_adj_count")
+        zero = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.row_ptr = torch.cat([zero, torch.cumsum(rn, 0, dtype=torch.int32)])
+        self.csc_ptr = torch.cat([zero, torch.cumsum(cn, 0, dtype=torch.int32)])
+        nnz = int(self.row_ptr[-1].item())
+        self.N, self.nnz = N, nnz
+        self.col_idx = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+        self.val = torch.empty(max(nnz, 1), dtype=torch.float32, device=dev)
+        self.csc_row = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+        self.csc_eid = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+        _lib.check(lib.msgat_adj_fill(_lib.ptr(adj), N, _lib.ptr(self.row_ptr), _lib.ptr(self.csc_ptr),
+                                      _lib.ptr(self.col_idx), _lib.ptr(self.val), _lib.ptr(self.csc_row),
+                                      _lib.ptr(self.csc_eid), st), "msgat_adj_fill")
+        self.struct = _lib.Adj(N, nnz, *[t.data_ptr() for t in (self.row_ptr, self.col_idx, self.val, self.csc_ptr,
+                                                                 self.csc_row, self.csc_eid)])
+
+
+_ADJ_CACHE: Dict[tuple, SparseAdjacency] = {}
+
+
+def sparse_adjacency(adj: torch.Tensor) -> SparseAdjacency:
+    """Cached per (storage, version): the adjacency is a frozen parameter."""
+    key = (adj.data_ptr(), adj._version, str(adj.device), tuple(adj.shape))
+    sp = _ADJ_CACHE.get(key)
+    if sp is None:
+        if len(_ADJ_CACHE) > 64:
+            _ADJ_CACHE.clear()
+        sp = _ADJ_CACHE[key] = SparseAdjacency(adj)
+    return sp
+
+
+class MeamConfig:
+    def __init__(self, Oc: int, Ot: int, Os: int, flags: int, dilations: Sequence[int] = (), precision: int = 0,
+                 dout_masked: bool = False, x_is_relu: bool = False):
+        self.Oc, self.Ot, self.Os, self.flags = Oc, Ot, Os, flags
+        self.dilations = tuple(int(d) for d in dilations)
+        self.precision, self.dout_masked, self.x_is_relu = precision, dout_masked, x_is_relu
+        if len(self.dilations) > _lib.MAX_CONV:
+            raise ValueError(f"TACN chains longer than {_lib.MAX_CONV} convs are not supported")
+
+
+def _desc(cfg: MeamConfig, x: torch.Tensor, backward: bool) -> _lib.MeamDesc:
+    B, Cc, N, T = x.shape
+    flags = cfg.flags
+    if backward:
+        flags |= (_lib.F_DOUT_MASKED if cfg.dout_masked else 0) | (_lib.F_X_IS_RELU if cfg.x_is_relu else 0)
+    d = _lib.MeamDesc(B, Cc, N, cfg.Oc, cfg.Ot, cfg.Os, flags, len(cfg.dilations))
+    for i, v in enumerate(cfg.dilations):
+        d.dil[i] = v
+    d.precision = cfg.precision
+    d.x_sb, d.x_sc = x.stride(0), x.stride(1)
+    return d
+
+
+def _plane_contiguous(x: torch.Tensor) -> torch.Tensor:
+    if x.stride(3) == 1 and x.stride(2) == x.shape[3] and x.data_ptr() % 16 == 0 \
+            and x.stride(0) % 4 == 0 and x.stride(1) % 4 == 0:
+        return x
+    return x.contiguous()
+
+
+def _param_struct(cls, tensors: Sequence[Optional[torch.Tensor]]):
+    s = cls()
+    byname = dict(zip(SLOTS, tensors))
+    for n in _lib._PARAM_FIELDS + ["sa_W", "sa_Wg", "sa_alpha"]:
+        t = byname[n]
+        setattr(s, n, None if t is None else t.data_ptr())
+    for i in range(_lib.MAX_CONV):
+        w, b = byname[f"conv_w{i}"], byname[f"conv_b{i}"]
+        s.conv_w[i] = None if w is None else w.data_ptr()
+        s.conv_b[i] = None if b is None else b.data_ptr()
+    return s
+
+
+class _MeamFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cfg: MeamConfig, adj: Optional[SparseAdjacency], *params):
+        lib = _lib.get()
+        if x.dtype != torch.float32:
+            x = x.float()  # the path computes in fp32 whatever autocast says (mixed precision)
+        if x.shape[3] != 12:
+            raise ValueError("msgat_b200 kernels are specialised for 12 timesteps (main.py:45)")
+        x = _plane_contiguous(x)
+        params = tuple(None if p is None else p.detach().float().contiguous() for p in params)
+        B, Cc, N, T = x.shape
+        d = _desc(cfg, x, backward=False)
+        nnz = adj.nnz if adj is not None else 0
+        sv, sc = C.c_int64(), C.c_int64()
+        _lib.check(lib.msgat_meam_sizes(C.byref(d), nnz, C.byref(sv), C.byref(sc)), "msgat_meam_sizes")
+        saved = torch.empty(max(sv.value, 4), dtype=torch.float32, device=x.device)
+        scratch = torch.empty(max(sc.value, 4), dtype=torch.float32, device=x.device)
+        out = torch.empty(B, cfg.Oc + cfg.Ot + cfg.Os, N, T, dtype=torch.float32, device=x.device)
+        ps = _param_struct(_lib.MeamParams, params)
+        _lib.check(lib.msgat_meam_forward(C.byref(d), C.byref(ps), C.byref(adj.struct) if adj is not None else None,
+                                          _lib.ptr(x), _lib.ptr(out), _lib.ptr(saved), _lib.ptr(scratch),
+                                          _lib.stream_of(x)), "msgat_meam_forward")
+        ctx.cfg, ctx.adj, ctx.scratch = cfg, adj, scratch
+        ctx.save_for_backward(x, out, saved, *[p for p in params if p is not None])
+        ctx.present = [p is not None for p in params]
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.get()
+        x, out, saved, *rest = ctx.saved_tensors
+        it = iter(rest)
+        params = tuple(next(it) if pr else None for pr in ctx.present)
+        cfg, adj = ctx.cfg, ctx.adj
+        dout = dout.float().contiguous()
+        d = _desc(cfg, x, backward=True)
+        dx = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+        grads = [None if p is None else torch.empty_like(p) for p in params]
+        ps = _param_struct(_lib.MeamParams, params)
+        gs = _param_struct(_lib.MeamGrads, grads)
+        _lib.check(lib.msgat_meam_backward(C.byref(d), C.byref(ps), C.byref(adj.struct) if adj is not None else None,
+                                           _lib.ptr(x), _lib.ptr(out), _lib.ptr(dout), _lib.ptr(saved),
+                                           _lib.ptr(ctx.scratch), _lib.ptr(dx), C.byref(gs), _lib.stream_of(x)),
+                   "msgat_meam_backward")
+        return (dx, None, None, *grads)
+
+
+def meam_op(x: torch.Tensor, cfg: MeamConfig, adj: Optional[SparseAdjacency],
+            params: Dict[str, Optional[torch.Tensor]]) -> torch.Tensor:
+    """Run the MEAM-shaped operator; ``params`` maps slot names (``SLOTS``) to tensors."""
+    with torch.autocast(device_type=x.device.type, enabled=False):
+        return _MeamFunction.apply(x, cfg, adj, *[params.get(n) for n in SLOTS])
