@@ -98,6 +98,12 @@ const char *msgat_last_error(void);
 /* 0 iff the current device is compute capability 10.x. */
 int msgat_device_check(void);
 
+/* Launch accounting (bench.py): number of kernels this library has launched since load;
+ * optional per-kernel CUDA-event timing on the launching stream. */
+long long msgat_launch_count(void);
+int msgat_profile(int enable);
+int msgat_profile_report(char *buf, long long cap);
+
 /* Adjacency preparation.  count: per-row non-zeros of dense adj [N,N] into row_nnz[N] and
  * col_nnz[N].  fill: given exclusive scans row_ptr/csc_ptr [N+1] (caller computes them),
  * write col_idx/val and csc_row/csc_eid. */

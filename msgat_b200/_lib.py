@@ -53,7 +53,8 @@ class HeadDesc(C.Structure):
                 ("accumulate", C.c_int32), ("x_is_relu", C.c_int32), ("gate_sb", C.c_int64)]
 
 
-EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_adj_count", "msgat_adj_fill",
+EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_launch_count", "msgat_profile",
+           "msgat_profile_report", "msgat_adj_count", "msgat_adj_fill",
            "msgat_meam_sizes", "msgat_meam_forward", "msgat_meam_backward", "msgat_head_forward",
            "msgat_head_scratch_floats", "msgat_head_backward"]
 
@@ -66,6 +67,7 @@ def _declare(lib):
     lib.msgat_last_error.restype = C.c_char_p
     lib.msgat_device_check.restype = C.c_int
     lib.msgat_head_scratch_floats.restype = C.c_int64
+    lib.msgat_launch_count.restype = C.c_longlong
     for name in EXPORTS:
         getattr(lib, name)  # AttributeError if the .so is stale
     return lib
@@ -107,3 +109,22 @@ def stream_of(t: torch.Tensor):
     if not _DEBUG_BACKEND:
         raise RuntimeError("msgat_b200 operators take CUDA tensors only")
     return C.c_void_p(0)
+
+
+def launch_count() -> int:
+    return int(get().msgat_launch_count())
+
+
+def profile(enable: bool):
+    get().msgat_profile(1 if enable else 0)
+
+
+def profile_report() -> dict:
+    """{kernel: (launches, total_ms)} of the launches recorded since profile(True)."""
+    buf = C.create_string_buffer(1 << 16)
+    check(get().msgat_profile_report(buf, len(buf)), "msgat_profile_report")
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.rsplit(" ", 2)
+        out[name] = (int(cnt), float(ms))
+    return out

@@ -15,6 +15,40 @@ void msgat_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+// ---------------------------------------------------------------------------------------
+// launch accounting: every kernel launch of this library is counted (bench.py reports the
+// count as gpu_launches); with msgat_profile(1) each launch is bracketed by CUDA events on
+// its own stream so that bench.py can attribute device time to kernels without a profiler.
+#ifndef MSGAT_EMU
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_prof{0};
+struct ProfRec { std::string name; cudaEvent_t e0, e1; };
+static std::vector<ProfRec> g_recs;
+static std::mutex g_prof_mu;
+static thread_local char g_tag[48] = "";
+void msgat_prof_tag(const char* fmt, int a, int b) { snprintf(g_tag, sizeof(g_tag), fmt, a, b); }
+int msgat_prof_begin(const char* name, cudaStream_t s) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (!g_prof.load(std::memory_order_relaxed)) return -1;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r;
+  r.name = std::string(name) + g_tag;
+  cudaEventCreate(&r.e0); cudaEventCreate(&r.e1);
+  cudaEventRecord(r.e0, s);
+  g_recs.push_back(r);
+  return (int)g_recs.size() - 1;
+}
+void msgat_prof_end(int slot, cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEventRecord(g_recs[slot].e1, s);
+}
+#endif
+
 static int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -70,6 +104,50 @@ extern "C" {
 const char* msgat_version(void) { return "msgat_sm100 0.1 (sm_100a)"; }
 const char* msgat_last_error(void) { return g_err; }
 
+long long msgat_launch_count(void) {
+#ifdef MSGAT_EMU
+  return 0;
+#else
+  return g_launches.load();
+#endif
+}
+
+int msgat_profile(int enable) {
+#ifndef MSGAT_EMU
+  g_prof.store(enable ? 1 : 0);
+#endif
+  return 0;
+}
+
+/* Synchronises the recorded events and writes "kernel launches total_ms\n" lines. */
+int msgat_profile_report(char* buf, long long cap) {
+#ifdef MSGAT_EMU
+  if (cap > 0) buf[0] = 0;
+  return 0;
+#else
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto& r : g_recs) {
+    cudaEventSynchronize(r.e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.e0, r.e1);
+    auto& a = agg[r.name];
+    a.first += 1; a.second += ms;
+    cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+  }
+  g_recs.clear();
+  std::string out;
+  for (auto& kv : agg) {
+    char line[256];
+    snprintf(line, sizeof(line), "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+  if ((long long)out.size() + 1 > cap) { msgat_set_error("profile report needs %zu bytes", out.size() + 1); return -50; }
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return 0;
+#endif
+}
+
 int msgat_device_check(void) {
 #ifdef MSGAT_EMU
   return 0;
@@ -118,6 +196,7 @@ int msgat_meam_forward(const msgat_meam_desc* d, const msgat_meam_params* prm, c
   int rc = make_plan(d, adj ? adj->nnz : 0, &p);
   if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
   if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  msgat_prof_tag("@C%dO%d", p.C, p.O);
   rc = meam_forward_impl(p, prm, adj, x, out, saved, scratch, stream);
   if (rc) return rc;
   return check_launch("meam_forward");
@@ -130,6 +209,7 @@ int msgat_meam_backward(const msgat_meam_desc* d, const msgat_meam_params* prm, 
   int rc = make_plan(d, adj ? adj->nnz : 0, &p);
   if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
   if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  msgat_prof_tag("@C%dO%d", p.C, p.O);
   rc = meam_backward_impl(p, prm, adj, x, out, dout, saved, scratch, dx, g, stream);
   if (rc) return rc;
   return check_launch("meam_backward");

@@ -16,14 +16,18 @@
 #define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...) \
   emu::launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
 #define MSGAT_UNROLL
+static inline void msgat_prof_tag(const char*, int, int) {}
 #else
 #include <cuda_runtime.h>
-#define MSGAT_KERNEL __global__ void
+#define MSGAT_KERNEL static __global__ void
 #define MSGAT_DEV __device__ __forceinline__
 #define MSGAT_LB(n, m) __launch_bounds__(n, m)
 #define MSGAT_RESTRICT __restrict__
 #define MSGAT_DYN_SMEM(name) extern __shared__ __align__(1024) unsigned char name[]
 #define MSGAT_MAX_SMEM 232448
+int msgat_prof_begin(const char* name, cudaStream_t s);  // counts the launch; >= 0 when event timing is on
+void msgat_prof_end(int slot, cudaStream_t s);
+void msgat_prof_tag(const char* fmt, int a, int b);
 #define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...)                                        \
   do {                                                                                            \
     static bool _attr = false;                                                                    \
@@ -31,7 +35,9 @@
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MSGAT_MAX_SMEM);    \
       _attr = true;                                                                               \
     }                                                                                             \
+    int _slot = msgat_prof_begin(#kern, (cudaStream_t)(stream));                                  \
     kern<<<(grid), (block), (smem), (cudaStream_t)(stream)>>>(__VA_ARGS__);                       \
+    if (_slot >= 0) msgat_prof_end(_slot, (cudaStream_t)(stream));                                \
   } while (0)
 #define MSGAT_UNROLL _Pragma("unroll")
 #endif

@@ -1,5 +1,915 @@
-// placeholder, replaced below
+// meam_bwd.cu -- backward of the MEAM-shaped operator.  Nothing but x, the output (for the
+// ReLU mask) and per-sample / per-node statistics was saved by the forward: LayerNorm, the
+// temporal apply and the conv chain are recomputed per tile, the N x N attention is
+// re-evaluated from (q, m, l) (north_star d: "recompute the scores instead of storing them").
+//
+// Launch sequence (see meam_backward_impl at the bottom):
+//   k_relu_mask  G = dout * (out > 0)                      (skipped when the consumer pre-masked)
+//   k_bwd_main   per tile: all data gradients that are local to a node, all weight gradients
+//                (register-resident 4x4 blocks, one partial per thread block), the per-sample
+//                reductions dMc, dPt and the sparse spatial terms dA, delta
+//   k_scol       dense column pass of the spatial softmax backward (spatial.cu)
+//   k_sfin       spatial: dU, dq_s, dWg partials
+//   k_bwd_small  per sample: softmax backward of the C x C and 12 x 12 attentions
+//   k_dwt        dWt1, dWt2
+//   k_bwd_fix    second pass over x: the rank-structured terms alpha (x) dq that only exist once
+//                the per-sample reductions are complete, pushed through the LayerNorm backward
+//                (linear in its incoming gradient) and added to dx; alpha gradients
+//   k_reduce     sums every partial into the caller's gradient tensors
 #include "kernels.h"
-int64_t meam_backward_scratch(Plan& p) { return 0; }
-int meam_backward_impl(Plan& p, const msgat_meam_params*, const msgat_adj*, const float*, const float*, const float*,
-                       const float*, float*, float*, const msgat_meam_grads*, void*) { msgat_set_error("nyi"); return -99; }
+#include "tile_ops.cuh"
+
+#define RB 4  // 4x4 weight-gradient blocks held in registers per thread
+
+struct WJob {
+  int start, nblk, nkb, Oa, Kb;
+  float* out;          // partial base of block 0
+  int64_t blk_stride;  // floats between partials of consecutive thread blocks
+};
+enum { JOB_RES = 0, JOB_MC = 1, JOB_WS = 2, JOB_CONV = 3, NJOBS = 3 + 2 * MSGAT_MAX_CONV };
+
+struct BwdArgs {
+  const float* x; int64_t x_sb, x_sc;
+  const float* G;  // masked dout [B,O,N,12]
+  int C, N, O, Oc, Ot, Os, Cz, s_pre, flags, n_conv, ntile, J, nnz;
+  int dil[MSGAT_MAX_CONV];
+  const float *ln_w, *ln_b, *res_w, *sa_W;
+  const float* conv_w[MSGAT_MAX_CONV];
+  const float* conv_b[MSGAT_MAX_CONV];
+  const float *Mc, *Pt, *Z, *pw;
+  const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
+  WJob jobs[NJOBS];
+  float *bias_part, *ln_part, *dPt_part, *delta, *dSnz, *dx;
+  int nbias, arena_floats;
+};
+
+// acc[r] (+)= A[oa..oa+3][p] . B[kb..kb+3][p] over the tile's positions, for the blocks of job jb
+MSGAT_DEV void wgrad_accum(float (&acc)[RB][16], const WJob& jb, const float* A, const float* Bm, int PS, int PQ, int tapd) {
+  MSGAT_UNROLL
+  for (int r = 0; r < RB; ++r) {
+    const int local = (int)threadIdx.x + r * (int)blockDim.x - jb.start;
+    if (local < 0 || local >= jb.nblk) continue;
+    const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
+    const float* ar[4];
+    const float* br[4];
+    for (int i = 0; i < 4; ++i) {
+      ar[i] = A + (oa + i < jb.Oa ? oa + i : jb.Oa - 1) * PS;
+      br[i] = Bm + (kb + i < jb.Kb ? kb + i : jb.Kb - 1) * PS;
+    }
+    for (int pq = 0; pq < PQ; ++pq) {
+      const int nl = pq / 3, t0 = (pq - nl * 3) * 4, off = nl * 12;
+      float4 a[4], b[4];
+      for (int i = 0; i < 4; ++i) a[i] = ld4(ar[i] + off + t0);
+      for (int i = 0; i < 4; ++i) b[i] = (tapd < 0) ? ld4(br[i] + off + t0) : quad_past(br[i] + off, t0, tapd);
+      MSGAT_UNROLL
+      for (int i = 0; i < 4; ++i) {
+        MSGAT_UNROLL
+        for (int j = 0; j < 4; ++j) acc[r][i * 4 + j] += dot4(a[i], b[j]);
+      }
+    }
+  }
+}
+
+MSGAT_DEV void wgrad_flush(const float (&acc)[RB][16], const WJob* jobs, int blk) {
+  for (int r = 0; r < RB; ++r) {
+    const int id = (int)threadIdx.x + r * (int)blockDim.x;
+    for (int q = 0; q < NJOBS; ++q) {
+      const WJob& jb = jobs[q];
+      const int local = id - jb.start;
+      if (jb.nblk == 0 || local < 0 || local >= jb.nblk) continue;
+      const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
+      float* dst = jb.out + (int64_t)blk * jb.blk_stride;
+      for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+          if (oa + i < jb.Oa && kb + j < jb.Kb) dst[(oa + i) * jb.Kb + kb + j] = acc[r][i * 4 + j];
+    }
+  }
+}
+
+MSGAT_KERNEL k_relu_mask(const float4* dout, const float4* out, float4* G, int64_t n4) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 d = dout[i], o = out[i];
+    d.x = o.x > 0.f ? d.x : 0.f; d.y = o.y > 0.f ? d.y : 0.f; d.z = o.z > 0.f ? d.z : 0.f; d.w = o.w > 0.f ? d.w : 0.f;
+    G[i] = d;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// shared memory (floats) of k_bwd_main; mirrored by the carve-up inside the kernel
+static int bwd_arena_floats(const Plan& p, int nthreads) {
+  int a = 0, v;
+  if (p.flags & MSGAT_F_RES) { v = p.O * rup4(p.C); a = v > a ? v : a; }
+  if (p.Oc) { v = p.Oc * rup4(p.C); a = v > a ? v : a; }
+  for (int i = 0; i < p.n_conv; ++i) {
+    const int K = i == 0 ? p.C : p.Ot;
+    v = 2 * K * rup4(p.Ot) + rup4(p.Ot); a = v > a ? v : a;   // transposed taps + bias (recompute)
+    v = 2 * p.Ot * rup4(K); a = v > a ? v : a;                // untransposed taps (conv^T)
+  }
+  if (p.Os && (p.flags & MSGAT_F_SMIX)) { v = p.Os * rup4(p.C); a = v > a ? v : a; }
+  if (p.Ot) { v = (nthreads / 9) * 144; a = v > a ? v : a; }
+  v = (nthreads / 32) * 24; a = v > a ? v : a;
+  return rup4(a);
+}
+static int64_t bwd_smem_floats(const Plan& p, int NT, int nthreads) {
+  const int PS = NT * 12 + 4;
+  int64_t f = 0;
+  f += (int64_t)p.C * PS * 3;  // H, OT, DH
+  f += (int64_t)p.O * PS;      // G
+  if (p.n_conv >= 2) f += (int64_t)(p.n_conv - 1) * p.Ot * PS + 2 * (int64_t)p.Ot * PS;  // Y[i], DYa, DYb
+  if (p.Os) f += (int64_t)p.Os * PS;                                                       // GZ
+  if (p.Os && (p.flags & MSGAT_F_SMIX) && !p.s_pre) f += (int64_t)p.C * PS;                // DOS
+  f += rup4(p.C * NT * 2) + 144 + 24;
+  f += bwd_arena_floats(p, nthreads);
+  return f;
+}
+
+template <int NT>
+MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
+  constexpr int P = NT * 12, PS = P + 4, PQ = NT * 3;
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
+  const int RC = (C + 3) & ~3;
+  const bool has_res = a.flags & MSGAT_F_RES, smix = a.flags & MSGAT_F_SMIX, do_ln = a.flags & MSGAT_F_LN;
+  float* sp = reinterpret_cast<float*>(smem_raw);
+  float* H = sp; sp += C * PS;
+  float* OT = sp; sp += C * PS;
+  float* DH = sp; sp += C * PS;
+  float* G = sp; sp += a.O * PS;
+  float* Y[MSGAT_MAX_CONV] = {nullptr, nullptr, nullptr, nullptr};
+  float* DY[2] = {nullptr, nullptr};
+  if (a.n_conv >= 2) {
+    for (int i = 0; i + 1 < a.n_conv; ++i) { Y[i] = sp; sp += a.Ot * PS; }
+    DY[0] = sp; sp += a.Ot * PS; DY[1] = sp; sp += a.Ot * PS;
+  }
+  float* GZ = nullptr; if (a.Os) { GZ = sp; sp += a.Os * PS; }
+  float* DOS = nullptr; if (a.Os && smix && !a.s_pre) { DOS = sp; sp += C * PS; }
+  float* ST = sp; sp += (C * NT * 2 + 3) & ~3;
+  float* Pt = sp; sp += 144;
+  float* LW = sp; sp += 24;
+  float* AR = sp;  // arena
+  const int Ooff = a.Oc + a.Ot;
+  const int chC = (C + 3) >> 2;
+  const int blk = b * a.J + blockIdx.x;
+  const float* Gb = a.G + (int64_t)b * a.O * a.N * 12;
+  const float* pwb = a.pw + (int64_t)b * a.nnz;
+  const float* Zb = a.Z + (int64_t)b * a.Cz * a.N * 12;
+
+  if (a.Ot) for (int i = tid; i < 144; i += T) Pt[i] = a.Pt[(int64_t)b * 144 + i];
+  if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
+
+  float acc[RB][16];
+  for (int r = 0; r < RB; ++r) for (int i = 0; i < 16; ++i) acc[r][i] = 0.f;
+  float bacc = 0.f, pt_acc = 0.f, lnw_acc[12], lnb_acc[12];
+  for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
+
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+    const int n0 = tile * NT;
+    __syncthreads();
+    // ---- S0: x -> OT (raw) and H (LayerNorm, stats kept); masked dout tile -> G
+    tile_load_ln(a.x + b * a.x_sb, a.x_sc, C, a.N, n0, NT, PS, OT, H, LW, LW + 12, do_ln, ST);
+    for (int r = tid; r < a.O * NT; r += T) {
+      const int o = r / NT, nl = r - o * NT, n = n0 + nl;
+      float4 u = f4zero(), v = f4zero(), w = f4zero();
+      if (n < a.N) { const float* s = Gb + ((int64_t)o * a.N + n) * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
+      float* q = G + o * PS + nl * 12;
+      st4(q, u); st4(q + 4, v); st4(q + 8, w);
+    }
+    __syncthreads();
+    // ---- S1: residual weight gradient (msgat.py:116,131) and the row sums behind three biases
+    if (has_res) wgrad_accum(acc, a.jobs[JOB_RES], G, OT, PS, PQ, -1);
+    if (tid < a.O) {
+      const float* q = G + tid * PS;
+      float s = 0.f;
+      for (int i = 0; i < P; i += 4) { float4 v = ld4(q + i); s += (v.x + v.y) + (v.z + v.w); }
+      bacc += s;
+    }
+    // ---- S2: channel branch: dh = Mc^T g_c ; dMc = g_c h^T
+    if (a.Oc) stage_w(AR, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, RC, 1, 0);
+    __syncthreads();
+    for (int it = tid; it < chC * PQ; it += T) {
+      const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4;
+      float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+      if (a.Oc) mix_item(d, G, PS, a.Oc, AR, RC, c0, nl, t0);
+      for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
+    }
+    if (a.Oc) wgrad_accum(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1);
+    __syncthreads();
+    // ---- S3: temporal branch
+    if (a.Ot) {
+      tile_temporal(OT, H, PS, C, NT, Pt, false, false);
+      __syncthreads();
+      // recompute the intermediate conv outputs (inputs of the later convs' weight gradients)
+      const float* cin = OT;
+      for (int i = 0; i + 1 < a.n_conv; ++i) {
+        const int K = i == 0 ? C : a.Ot, WOt = (a.Ot + 3) & ~3;
+        float *cvA = AR, *cvP = AR + K * WOt, *cvB = AR + 2 * K * WOt;
+        stage_wT(cvA, a.conv_w[i], a.Ot, K, WOt, 2, 1);
+        stage_wT(cvP, a.conv_w[i], a.Ot, K, WOt, 2, 0);
+        stage_vec(cvB, a.conv_b[i], a.Ot, WOt);
+        __syncthreads();
+        for (int it = tid; it < (WOt >> 2) * PQ; it += T) {
+          const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4;
+          float4 d[4];
+          for (int j = 0; j < 4; ++j) { float bj = cvB[o0 + j]; d[j] = make_float4(bj, bj, bj, bj); }
+          mix_item_taps(d, cin, PS, K, cvA, cvP, WOt, o0, nl, t0, a.dil[i]);
+          for (int j = 0; j < 4; ++j) if (o0 + j < a.Ot) st4(Y[i] + (o0 + j) * PS + nl * 12 + t0, d[j]);
+        }
+        __syncthreads();
+        cin = Y[i];
+      }
+      // walk the chain backwards
+      const float* dy = G + a.Oc * PS;
+      for (int i = a.n_conv - 1; i >= 0; --i) {
+        const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
+        const float* in = i == 0 ? OT : Y[i - 1];
+        wgrad_accum(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i]);
+        wgrad_accum(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1);
+        if (i + 1 < a.n_conv) {
+          const int row = tid - a.O - i * a.Ot;
+          if (row >= 0 && row < a.Ot) {
+            const float* q = dy + row * PS;
+            float s = 0.f;
+            for (int k = 0; k < P; k += 4) { float4 v = ld4(q + k); s += (v.x + v.y) + (v.z + v.w); }
+            bacc += s;
+          }
+        }
+        float *Wn = AR, *Wp = AR + a.Ot * RK;
+        stage_w(Wn, a.conv_w[i], a.Ot, K, RK, 2, 1);
+        stage_w(Wp, a.conv_w[i], a.Ot, K, RK, 2, 0);
+        __syncthreads();
+        float* dst = i == 0 ? OT : DY[i & 1];
+        for (int it = tid; it < (RK >> 2) * PQ; it += T) {
+          const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, k0 = ch * 4;
+          float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+          mix_item_taps_T(d, dy, PS, a.Ot, Wn, Wp, RK, k0, nl, t0, a.dil[i]);
+          for (int j = 0; j < 4; ++j) if (k0 + j < K) st4(dst + (k0 + j) * PS + nl * 12 + t0, d[j]);
+        }
+        __syncthreads();
+        dy = dst;
+      }
+      const float* dOt = dy;  // gradient of the temporal attention output, C rows
+      // dPt[t][i] = sum_{c,n} dOt[c,n,t] h[c,n,i]   (attention.py:66 transposed)
+      {
+        const int ngr = T / 9;
+        if (tid < ngr * 9) {
+          const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4;
+          float o16[16];
+          for (int i = 0; i < 16; ++i) o16[i] = 0.f;
+          for (int r = grp; r < C * NT; r += ngr) {
+            const int c = r / NT, nl = r - c * NT;
+            const float4 g = ld4(dOt + c * PS + nl * 12 + tb), h = ld4(H + c * PS + nl * 12 + ib);
+            o16[0] += g.x * h.x; o16[1] += g.x * h.y; o16[2] += g.x * h.z; o16[3] += g.x * h.w;
+            o16[4] += g.y * h.x; o16[5] += g.y * h.y; o16[6] += g.y * h.z; o16[7] += g.y * h.w;
+            o16[8] += g.z * h.x; o16[9] += g.z * h.y; o16[10] += g.z * h.z; o16[11] += g.z * h.w;
+            o16[12] += g.w * h.x; o16[13] += g.w * h.y; o16[14] += g.w * h.z; o16[15] += g.w * h.w;
+          }
+          for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = o16[i * 4 + j];
+        }
+        // dh[c,n,i] += sum_t Pt[t][i] dOt[c,n,t]
+        tile_temporal(DH, dOt, PS, C, NT, Pt, true, true);
+        __syncthreads();
+        if (tid < 144) {
+          float s = 0.f;
+          for (int g2 = 0; g2 < ngr; ++g2) s += AR[g2 * 144 + tid];
+          pt_acc += s;
+        }
+        __syncthreads();
+      }
+    }
+    // ---- S4: spatial branch
+    if (a.Os) {
+      const float* Gs = G + Ooff * PS;
+      const int RCs = RC;
+      if (smix) stage_w(AR, a.sa_W, a.Os, C, RCs, 1, 0);
+      // GZ[o][i] = sum_n A[n,i] g_s[o][n]  (transpose aggregation through the CSC view)
+      const int chS = (a.Os + 3) >> 2;
+      for (int it = tid; it < chS * PQ; it += T) {
+        const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4, n = n0 + nl;
+        float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+        if (n < a.N) {
+          const int k1 = a.csc_ptr[n + 1];
+          for (int k = a.csc_ptr[n]; k < k1; ++k) {
+            const float w = pwb[a.csc_eid[k]];
+            const float* gr = Gb + ((int64_t)(Ooff + o0) * a.N + a.csc_row[k]) * 12 + t0;
+            for (int j = 0; j < 4; ++j) if (o0 + j < a.Os) fma4(d[j], w, ld4(gr + (int64_t)j * a.N * 12));
+          }
+        }
+        for (int j = 0; j < 4; ++j) if (o0 + j < a.Os) st4(GZ + (o0 + j) * PS + nl * 12 + t0, d[j]);
+      }
+      __syncthreads();
+      for (int it = tid; it < chC * PQ; it += T) {
+        const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4;
+        float4 d[4];
+        for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
+        if (smix) {
+          mix_item(d, GZ, PS, a.Os, AR, RCs, c0, nl, t0);
+        } else {
+          for (int j = 0; j < 4; ++j)
+            if (c0 + j < C) { float4 z = ld4(GZ + (c0 + j) * PS + nl * 12 + t0); d[j].x += z.x; d[j].y += z.y; d[j].z += z.z; d[j].w += z.w; }
+        }
+        for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
+        if (DOS) {  // d(aggregated h) = W^T g_s, the left operand of dA when h (not W h) was aggregated
+          float4 e[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+          mix_item(e, Gs, PS, a.Os, AR, RCs, c0, nl, t0);
+          for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DOS + (c0 + j) * PS + nl * 12 + t0, e[j]);
+        }
+      }
+      if (smix) wgrad_accum(acc, a.jobs[JOB_WS], GZ, H, PS, PQ, -1);
+      __syncthreads();
+      // dA[n,i] at the adjacency non-zeros, delta[n] = sum_i A[n,i] dA[n,i]; one warp per row
+      const float* GA = DOS ? DOS : Gs;
+      const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
+      for (int nl = warp; nl < NT; nl += nwarp) {
+        const int n = n0 + nl;
+        if (n >= a.N) continue;
+        float delta = 0.f;
+        const int e1 = a.row_ptr[n + 1];
+        for (int e = a.row_ptr[n]; e < e1; ++e) {
+          const float* zr = Zb + (int64_t)a.col_idx[e] * 12;
+          float s = 0.f;
+          for (int pr = lane; pr < a.Cz * 3; pr += 32) {
+            const int cz = pr / 3, q4 = (pr - cz * 3) * 4;
+            s += dot4(ld4(GA + cz * PS + nl * 12 + q4), ld4(zr + (int64_t)cz * a.N * 12 + q4));
+          }
+          s = warp_sum(s);
+          const float dsn = pwb[e] * s;
+          delta += dsn;
+          if (lane == 0) a.dSnz[(int64_t)b * a.nnz + e] = dsn;
+        }
+        if (lane == 0) a.delta[(int64_t)b * a.N + n] = delta;
+      }
+    }
+    __syncthreads();
+    // ---- S5: LayerNorm backward on the rows of DH (in place) + affine gradient partials
+    if (do_ln) {
+      for (int r = tid; r < C * NT; r += T) {
+        const int c = r / NT, nl = r - c * NT, n = n0 + nl;
+        if (n >= a.N) continue;
+        const float* src = a.x + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
+        const float mu = ST[2 * r], rs = ST[2 * r + 1];
+        float xh[12], dh[12];
+        float* q = DH + c * PS + nl * 12;
+        for (int t = 0; t < 12; ++t) { xh[t] = (src[t] - mu) * rs; dh[t] = q[t]; }
+        float m1 = 0.f, m2 = 0.f;
+        for (int t = 0; t < 12; ++t) {
+          lnw_acc[t] += dh[t] * xh[t];
+          lnb_acc[t] += dh[t];
+          const float gg = dh[t] * LW[t];
+          m1 += gg; m2 += gg * xh[t];
+        }
+        m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+        for (int t = 0; t < 12; ++t) q[t] = rs * (dh[t] * LW[t] - m1 - xh[t] * m2);
+      }
+    }
+    // ---- S6: dx = LN^T(dh) + Wres^T g
+    if (has_res) stage_w(AR, a.res_w, a.O, C, RC, 1, 0);
+    __syncthreads();
+    for (int it = tid; it < chC * PQ; it += T) {
+      const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4, n = n0 + nl;
+      float4 d[4];
+      for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
+      if (has_res) mix_item(d, G, PS, a.O, AR, RC, c0, nl, t0);
+      if (n < a.N) {
+        for (int j = 0; j < 4; ++j) {
+          if (c0 + j >= C) continue;
+          float4 v = d[j];
+          if (a.flags & MSGAT_F_X_IS_RELU) {
+            const float4 xv = ld4(a.x + b * a.x_sb + (c0 + j) * a.x_sc + (int64_t)n * 12 + t0);
+            v.x = xv.x > 0.f ? v.x : 0.f; v.y = xv.y > 0.f ? v.y : 0.f; v.z = xv.z > 0.f ? v.z : 0.f; v.w = xv.w > 0.f ? v.w : 0.f;
+          }
+          st4(a.dx + (((int64_t)b * C + c0 + j) * a.N + n) * 12 + t0, v);
+        }
+      }
+    }
+  }
+  // ---- flush the per-block partials
+  __syncthreads();
+  wgrad_flush(acc, a.jobs, blk);
+  if (tid < a.nbias) a.bias_part[(int64_t)blk * a.nbias + tid] = bacc;
+  if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
+  {
+    const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
+    for (int t = 0; t < 12; ++t) {
+      const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
+      if (lane == 0) { AR[warp * 24 + t] = w; AR[warp * 24 + 12 + t] = bb; }
+    }
+    __syncthreads();
+    if (tid < 24) {
+      float s = 0.f;
+      for (int w = 0; w < nwarp; ++w) s += AR[w * 24 + tid];
+      a.ln_part[(int64_t)blk * 24 + tid] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// spatial finalisation, one thread per (b, n):
+//   dU[n,:] = sum_e dSnz[e] q[i_e,:] - delta[n] E[n,:]
+//   dq[n,:] = dq_dense[n,:] + sum_{k in col n} dSnz[eid_k] U[row_k,:] + dU[n,:] Wg^T
+//   dWg    += q[n,:]^T dU[n,:]
+struct SFinArgs {
+  int N, nnz;
+  const float *qs, *Wg, *E, *delta, *dSnz, *dq_dense;
+  const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
+  float *dqs, *Wg_part;
+};
+
+MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  float* WG = reinterpret_cast<float*>(smem_raw);  // [144]
+  float* QD = WG + 144;                            // [128][24]: q, dU of every node of the block
+  const int b = blockIdx.y, n = blockIdx.x * blockDim.x + threadIdx.x;
+  const float* qb = a.qs + (int64_t)b * a.N * 12;
+  const float* ds = a.dSnz + (int64_t)b * a.nnz;
+  for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = a.Wg[i];
+  __syncthreads();
+  float q[12], dU[12], dq[12];
+  for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.f; dq[t] = 0.f; }
+  if (n < a.N) {
+    const int64_t g = (int64_t)b * a.N + n;
+    const float dl = a.delta[g];
+    for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * a.E[g * 12 + t]; dq[t] = a.dq_dense[g * 12 + t]; }
+    for (int e = a.row_ptr[n]; e < a.row_ptr[n + 1]; ++e) {
+      const float w = ds[e];
+      const float* qi = qb + (int64_t)a.col_idx[e] * 12;
+      for (int t = 0; t < 12; ++t) dU[t] = fmaf(w, qi[t], dU[t]);
+    }
+    for (int k = a.csc_ptr[n]; k < a.csc_ptr[n + 1]; ++k) {
+      const float w = ds[a.csc_eid[k]];
+      const float* qr = qb + (int64_t)a.csc_row[k] * 12;
+      for (int t = 0; t < 12; ++t) {
+        float u = 0.f;
+        for (int t1 = 0; t1 < 12; ++t1) u = fmaf(qr[t1], WG[t1 * 12 + t], u);
+        dq[t] = fmaf(w, u, dq[t]);
+      }
+    }
+    for (int t = 0; t < 12; ++t) {
+      float s = 0.f;
+      for (int t2 = 0; t2 < 12; ++t2) s = fmaf(dU[t2], WG[t * 12 + t2], s);
+      a.dqs[g * 12 + t] = dq[t] + s;
+    }
+  }
+  for (int t = 0; t < 12; ++t) { QD[threadIdx.x * 24 + t] = q[t]; QD[threadIdx.x * 24 + 12 + t] = dU[t]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 144; i += blockDim.x) {
+    const int t = i / 12, t2 = i - t * 12;
+    float s = 0.f;
+    for (int k = 0; k < (int)blockDim.x; ++k) s = fmaf(QD[k * 24 + t], QD[k * 24 + 12 + t2], s);
+    a.Wg_part[((int64_t)b * gridDim.x + blockIdx.x) * 144 + i] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+struct BSmallArgs {
+  int C, Oc, Ot, cmix, J;
+  const float *dMc_part, *dPt_part, *Pc, *qc, *Wc, *ca_w, *Pt, *K;
+  float *caw_part, *Wc_part, *dqc, *dK;
+};
+
+MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
+  float* sp = reinterpret_cast<float*>(smem_raw);
+  float* qc = sp; sp += C * 12;
+  float* A1 = sp; sp += C * 12;
+  float* A2 = sp; sp += C * 12;
+  float* T2 = sp; sp += C * 12;
+  float* Pc = sp; sp += C * C;
+  float* dS = sp; sp += C * C;
+  float* dMc = sp; sp += a.Oc * C;
+  float* TP = sp; sp += 144 * 2 + 240;  // Pt, dSt, K
+  if (a.Oc) {
+    for (int i = tid; i < C * 12; i += T) qc[i] = a.qc[(int64_t)b * C * 12 + i];
+    for (int i = tid; i < C * C; i += T) Pc[i] = a.Pc[(int64_t)b * C * C + i];
+    for (int i = tid; i < a.Oc * C; i += T) {
+      float s = 0.f;
+      for (int j = 0; j < a.J; ++j) s += a.dMc_part[((int64_t)b * a.J + j) * a.Oc * C + i];
+      dMc[i] = s;
+    }
+    __syncthreads();
+    if (a.cmix) {  // dW1 = dMc Pc^T ; dPc = W1^T dMc   (msgat.py:94)
+      for (int i = tid; i < a.Oc * C; i += T) {
+        const int o = i / C, c = i - o * C;
+        float s = 0.f;
+        for (int k = 0; k < C; ++k) s = fmaf(dMc[o * C + k], Pc[c * C + k], s);
+        a.caw_part[(int64_t)b * a.Oc * C + i] = s;
+      }
+      for (int i = tid; i < C * C; i += T) {
+        const int c = i / C, k = i - c * C;
+        float s = 0.f;
+        for (int o = 0; o < a.Oc; ++o) s = fmaf(__ldg(a.ca_w + o * C + c), dMc[o * C + k], s);
+        dS[i] = s;
+      }
+    } else {
+      for (int i = tid; i < C * C; i += T) dS[i] = dMc[i];
+    }
+    __syncthreads();
+    for (int c = tid; c < C; c += T) {  // softmax backward, row-wise
+      float s = 0.f;
+      for (int k = 0; k < C; ++k) s = fmaf(Pc[c * C + k], dS[c * C + k], s);
+      for (int k = 0; k < C; ++k) dS[c * C + k] = Pc[c * C + k] * (dS[c * C + k] - s);
+    }
+    for (int i = tid; i < C * 12; i += T) {
+      const int c = i / 12, t = i - c * 12;
+      float s1 = 0.f, s2 = 0.f;
+      for (int u = 0; u < 12; ++u) {
+        s1 = fmaf(__ldg(a.Wc + t * 12 + u), qc[c * 12 + u], s1);   // (qc Wc^T)[c][t]
+        s2 = fmaf(qc[c * 12 + u], __ldg(a.Wc + u * 12 + t), s2);   // (qc Wc)[c][t]
+      }
+      A1[i] = s1; A2[i] = s2;
+    }
+    __syncthreads();
+    for (int i = tid; i < C * 12; i += T) {
+      const int c = i / 12, t = i - c * 12;
+      float s = 0.f, s3 = 0.f;
+      for (int k = 0; k < C; ++k) {
+        s = fmaf(dS[c * C + k], A1[k * 12 + t], s);
+        s = fmaf(dS[k * C + c], A2[k * 12 + t], s);
+        s3 = fmaf(dS[c * C + k], qc[k * 12 + t], s3);
+      }
+      a.dqc[(int64_t)b * C * 12 + i] = s;
+      T2[i] = s3;
+    }
+    __syncthreads();
+    for (int i = tid; i < 144; i += T) {
+      const int t = i / 12, u = i - t * 12;
+      float s = 0.f;
+      for (int c = 0; c < C; ++c) s = fmaf(qc[c * 12 + t], T2[c * 12 + u], s);
+      a.Wc_part[(int64_t)b * 144 + i] = s;
+    }
+  }
+  if (a.Ot) {
+    float *Pt = TP, *dSt = TP + 144, *K = TP + 288;
+    __syncthreads();
+    for (int i = tid; i < 144; i += T) {
+      Pt[i] = a.Pt[(int64_t)b * 144 + i];
+      float s = 0.f;
+      for (int j = 0; j < a.J; ++j) s += a.dPt_part[((int64_t)b * a.J + j) * 144 + i];
+      dSt[i] = s;
+    }
+    for (int i = tid; i < 240; i += T) K[i] = a.K[(int64_t)b * 240 + i];
+    __syncthreads();
+    if (tid < 12) {
+      float s = 0.f;
+      for (int k = 0; k < 12; ++k) s = fmaf(Pt[tid * 12 + k], dSt[tid * 12 + k], s);
+      for (int k = 0; k < 12; ++k) dSt[tid * 12 + k] = Pt[tid * 12 + k] * (dSt[tid * 12 + k] - s);
+    }
+    __syncthreads();
+    for (int i = tid; i < 240; i += T) {
+      const int t = i / 20, r = i - t * 20;
+      float s = 0.f;
+      if (r < 10) { for (int k = 0; k < 12; ++k) s = fmaf(dSt[t * 12 + k], K[k * 20 + 10 + r], s); }   // dK1 = dS K2
+      else { for (int k = 0; k < 12; ++k) s = fmaf(dSt[k * 12 + t], K[k * 20 + r - 10], s); }         // dK2 = dS^T K1
+      a.dK[(int64_t)b * 240 + i] = s;
+    }
+  }
+}
+
+// dWt1[r][n] = sum_{b,t} dK1[b,t,r] q_t[b,n,t]   (attention.py:65)
+MSGAT_KERNEL k_dwt(const float* dK, const float* qt, int B, int N, float* dWt1, float* dWt2) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * 20) return;
+  const int n = i / 20, r = i - n * 20;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b)
+    for (int t = 0; t < 12; ++t) s = fmaf(dK[(int64_t)b * 240 + t * 20 + r], qt[((int64_t)b * N + n) * 12 + t], s);
+  if (r < 10) { if (dWt1) dWt1[(int64_t)r * N + n] = s; }
+  else { if (dWt2) dWt2[(int64_t)(r - 10) * N + n] = s; }
+}
+
+// ---------------------------------------------------------------------------------------
+// second pass: dh2[c,n,t] = alpha_n[n] dqc[b,c,t] + alpha_t[c] dqt[b,t,n] + alpha_s[c] dqs[b,n,t]
+// (the gradients of the three query reductions, attention.py:92,63,33), through the
+// LayerNorm backward, added to dx; gradients of the three alphas.
+struct FixArgs {
+  const float* x; int64_t x_sb, x_sc;
+  int C, N, Oc, Ot, Os, flags, ntile, J;
+  const float *ln_w, *ln_b, *ca_alpha, *ta_alpha, *sa_alpha, *Wt1, *Wt2, *dqc, *dK, *dqs;
+  float *dx, *pa_n, *pa_t, *pa_s, *ln_part;
+};
+
+template <int NT>
+MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
+  constexpr int P = NT * 12;
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
+  const bool do_ln = a.flags & MSGAT_F_LN;
+  float* sp = reinterpret_cast<float*>(smem_raw);
+  float* DQC = sp; sp += C * 12;
+  float* DQT = sp; sp += P;
+  float* DQS = sp; sp += P;
+  float* V1 = sp; sp += C * NT;
+  float* V2 = sp; sp += C * NT;
+  float* V3 = sp; sp += C * NT;
+  float* DK = sp; sp += 240;
+  float* LW = sp; sp += 24;
+  float* RED = sp;  // [T/32][24]
+  if (a.Oc) for (int i = tid; i < C * 12; i += T) DQC[i] = a.dqc[(int64_t)b * C * 12 + i];
+  if (a.Ot) for (int i = tid; i < 240; i += T) DK[i] = a.dK[(int64_t)b * 240 + i];
+  if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
+  float at_acc = 0.f, as_acc = 0.f, lnw_acc[12], lnb_acc[12];
+  for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+    const int n0 = tile * NT;
+    __syncthreads();
+    for (int p = tid; p < P; p += T) {
+      const int nl = p / 12, t = p - nl * 12, n = n0 + nl;
+      float s = 0.f, q = 0.f;
+      if (n < a.N) {
+        if (a.Ot)
+          for (int r = 0; r < 10; ++r) {
+            s = fmaf(DK[t * 20 + r], __ldg(a.Wt1 + (int64_t)r * a.N + n), s);
+            s = fmaf(DK[t * 20 + 10 + r], __ldg(a.Wt2 + (int64_t)r * a.N + n), s);
+          }
+        if (a.Os) q = a.dqs[((int64_t)b * a.N + n) * 12 + t];
+      }
+      DQT[p] = s; DQS[p] = q;
+    }
+    __syncthreads();
+    for (int r = tid; r < C * NT; r += T) {
+      const int c = r / NT, nl = r - c * NT, n = n0 + nl;
+      float v1 = 0.f, v2 = 0.f, v3 = 0.f;
+      if (n < a.N) {
+        const float* src = a.x + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
+        float xv[12], xh[12], h[12], dh[12];
+        float4 u = ld4(src), v = ld4(src + 4), w = ld4(src + 8);
+        xv[0] = u.x; xv[1] = u.y; xv[2] = u.z; xv[3] = u.w; xv[4] = v.x; xv[5] = v.y; xv[6] = v.z; xv[7] = v.w;
+        xv[8] = w.x; xv[9] = w.y; xv[10] = w.z; xv[11] = w.w;
+        float mu = 0.f, rs = 1.f;
+        if (do_ln) {
+          for (int t = 0; t < 12; ++t) mu += xv[t];
+          mu *= (1.0f / 12.0f);
+          float var = 0.f;
+          for (int t = 0; t < 12; ++t) { const float d = xv[t] - mu; var = fmaf(d, d, var); }
+          rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
+          for (int t = 0; t < 12; ++t) { xh[t] = (xv[t] - mu) * rs; h[t] = xh[t] * LW[t] + LW[12 + t]; }
+        } else {
+          for (int t = 0; t < 12; ++t) { xh[t] = 0.f; h[t] = xv[t]; }
+        }
+        const float an = a.Oc ? __ldg(a.ca_alpha + n) : 0.f;
+        const float att = a.Ot ? __ldg(a.ta_alpha + c) : 0.f;
+        const float as = a.Os ? __ldg(a.sa_alpha + c) : 0.f;
+        for (int t = 0; t < 12; ++t) {
+          const float dqc = a.Oc ? DQC[c * 12 + t] : 0.f, dqt = DQT[nl * 12 + t], dqs = DQS[nl * 12 + t];
+          dh[t] = an * dqc + att * dqt + as * dqs;
+          v1 = fmaf(dqc, h[t], v1); v2 = fmaf(dqt, h[t], v2); v3 = fmaf(dqs, h[t], v3);
+        }
+        float out[12];
+        if (do_ln) {
+          float m1 = 0.f, m2 = 0.f;
+          for (int t = 0; t < 12; ++t) {
+            lnw_acc[t] += dh[t] * xh[t];
+            lnb_acc[t] += dh[t];
+            const float gg = dh[t] * LW[t];
+            m1 += gg; m2 += gg * xh[t];
+          }
+          m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+          for (int t = 0; t < 12; ++t) out[t] = rs * (dh[t] * LW[t] - m1 - xh[t] * m2);
+        } else {
+          for (int t = 0; t < 12; ++t) out[t] = dh[t];
+        }
+        if (a.flags & MSGAT_F_X_IS_RELU)
+          for (int t = 0; t < 12; ++t) out[t] = xv[t] > 0.f ? out[t] : 0.f;
+        float* d = a.dx + (((int64_t)b * C + c) * a.N + n) * 12;
+        float4 d0 = ld4(d), d1 = ld4(d + 4), d2 = ld4(d + 8);
+        d0.x += out[0]; d0.y += out[1]; d0.z += out[2]; d0.w += out[3];
+        d1.x += out[4]; d1.y += out[5]; d1.z += out[6]; d1.w += out[7];
+        d2.x += out[8]; d2.y += out[9]; d2.z += out[10]; d2.w += out[11];
+        st4(d, d0); st4(d + 4, d1); st4(d + 8, d2);
+      }
+      V1[r] = v1; V2[r] = v2; V3[r] = v3;
+    }
+    __syncthreads();
+    if (a.Oc) for (int nl = tid; nl < NT; nl += T) {
+      if (n0 + nl < a.N) {
+        float s = 0.f;
+        for (int c = 0; c < C; ++c) s += V1[c * NT + nl];
+        a.pa_n[(int64_t)b * a.N + n0 + nl] = s;
+      }
+    }
+    for (int c = tid; c < C; c += T) {  // a thread owns channel c for the whole kernel (needs T >= C)
+      float s2 = 0.f, s3 = 0.f;
+      for (int nl = 0; nl < NT; ++nl) { s2 += V2[c * NT + nl]; s3 += V3[c * NT + nl]; }
+      at_acc += s2; as_acc += s3;
+    }
+  }
+  const int blk = b * a.J + blockIdx.x;
+  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = at_acc; a.pa_s[(int64_t)blk * C + tid] = as_acc; }
+  __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
+  for (int t = 0; t < 12; ++t) {
+    const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
+    if (lane == 0) { RED[warp * 24 + t] = w; RED[warp * 24 + 12 + t] = bb; }
+  }
+  __syncthreads();
+  if (tid < 24) {
+    float s = 0.f;
+    for (int w = 0; w < nwarp; ++w) s += RED[w * 24 + tid];
+    a.ln_part[(int64_t)blk * 24 + tid] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+#include "reduce.cuh"
+
+// ---------------------------------------------------------------------------------------
+struct BwdLayout {
+  int NT, T, J, nblk, nwblk, nbias, NT4, J4, nblk4, ntile4, nfin;
+  int64_t WGT;  // floats of weight-gradient partial per thread block
+  int64_t off_job[NJOBS];
+  int64_t o_G, o_wg, o_bias, o_ln, o_dMc, o_dPt, o_delta, o_dSnz, o_dqd, o_dqs, o_dK, o_dqc, o_caw, o_Wc, o_Wg,
+      o_pat, o_pas, o_pan, total;
+  WJob jobs[NJOBS];
+};
+
+static int bwd_layout(Plan& p, BwdLayout& L) {
+  // weight-gradient jobs as lists of 4x4 blocks
+  int start = 0;
+  int64_t woff = 0;
+  for (int q = 0; q < NJOBS; ++q) { L.jobs[q] = WJob{0, 0, 1, 1, 1, nullptr, 0}; L.off_job[q] = 0; }
+  auto add = [&](int q, int Oa, int Kb, bool in_wg) {
+    WJob& jb = L.jobs[q];
+    jb.Oa = Oa; jb.Kb = Kb; jb.nkb = (Kb + 3) / 4; jb.nblk = ((Oa + 3) / 4) * jb.nkb; jb.start = start;
+    start += jb.nblk;
+    if (in_wg) { L.off_job[q] = woff; woff += rup4l((int64_t)Oa * Kb); }
+  };
+  if (p.flags & MSGAT_F_RES) add(JOB_RES, p.O, p.C, true);
+  if (p.Oc) add(JOB_MC, p.Oc, p.C, false);
+  if (p.Os && (p.flags & MSGAT_F_SMIX)) add(JOB_WS, p.Os, p.C, true);
+  for (int i = 0; i < p.n_conv; ++i) {
+    const int K = i == 0 ? p.C : p.Ot;
+    add(JOB_CONV + 2 * i, p.Ot, K, true);
+    add(JOB_CONV + 2 * i + 1, p.Ot, K, true);
+  }
+  L.nwblk = start;
+  L.WGT = woff;
+  L.nbias = p.O + (p.n_conv > 1 ? (p.n_conv - 1) * p.Ot : 0);
+  int T = ((start + RB - 1) / RB + 31) & ~31;
+  if (T < 160) T = 160;
+  if (T < ((L.nbias + 31) & ~31)) T = (L.nbias + 31) & ~31;
+  if (T < ((p.C + 31) & ~31)) T = (p.C + 31) & ~31;
+  if (T > 384) return -30;
+  L.T = T;
+  int NT = 8;
+  while (NT > 1 && bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) NT >>= 1;
+  if (bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) return -31;
+  L.NT = NT; p.NTb = NT; p.ntile_b = (p.N + NT - 1) / NT;
+  int J = (2 * 148 + p.B - 1) / p.B;
+  if (J > p.ntile_b) J = p.ntile_b;
+  L.J = J; L.nblk = J * p.B;
+  L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
+  int J4 = (4 * 148 + p.B - 1) / p.B;
+  if (J4 > L.ntile4) J4 = L.ntile4;
+  L.J4 = J4; L.nblk4 = J4 * p.B;
+  L.nfin = (p.N + 127) / 128;
+  int64_t o = 0;
+  const int64_t BN = (int64_t)p.B * p.N;
+  const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
+  L.o_G = o; o += need_mask ? rup4l(BN * 12 * p.O) : 0;
+  L.o_wg = o; o += rup4l((int64_t)L.nblk * L.WGT);
+  L.o_bias = o; o += rup4l((int64_t)L.nblk * L.nbias);
+  L.o_ln = o; o += rup4l((int64_t)(L.nblk + L.nblk4) * 24);
+  L.o_dMc = o; o += rup4l((int64_t)L.nblk * p.Oc * p.C);
+  L.o_dPt = o; o += rup4l((int64_t)L.nblk * 144);
+  L.o_delta = o; o += rup4l(BN);
+  L.o_dSnz = o; o += rup4l((int64_t)p.B * p.nnz);
+  L.o_dqd = o; o += rup4l(BN * 12);
+  L.o_dqs = o; o += rup4l(BN * 12);
+  L.o_dK = o; o += rup4l((int64_t)p.B * 240);
+  L.o_dqc = o; o += rup4l((int64_t)p.B * p.C * 12);
+  L.o_caw = o; o += rup4l((int64_t)p.B * p.Oc * p.C);
+  L.o_Wc = o; o += rup4l((int64_t)p.B * 144);
+  L.o_Wg = o; o += rup4l((int64_t)p.B * L.nfin * 144);
+  L.o_pat = o; o += rup4l((int64_t)L.nblk4 * p.C);
+  L.o_pas = o; o += rup4l((int64_t)L.nblk4 * p.C);
+  L.o_pan = o; o += rup4l(BN);
+  L.total = o;
+  return 0;
+}
+
+int64_t meam_backward_scratch(Plan& p) {
+  BwdLayout L;
+  int rc = bwd_layout(p, L);
+  if (rc) return rc;
+  return L.total;
+}
+
+int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* out,
+                       const float* dout, const float* saved, float* scratch, float* dx, const msgat_meam_grads* g,
+                       void* stream) {
+  BwdLayout L;
+  int rc = bwd_layout(p, L);
+  if (rc) { msgat_set_error("MEAM backward: unsupported shape (code %d)", rc); return rc; }
+  const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
+  const float* G = dout;
+  if (need_mask) {
+    if (!out) { msgat_set_error("MEAM backward: forward output needed for the ReLU mask"); return -32; }
+    const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
+    int blocks = (int)((n4 + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)dout, (const float4*)out,
+                 (float4*)(scratch + L.o_G), n4);
+    G = scratch + L.o_G;
+  }
+  {
+    BwdArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
+    a.C = p.C; a.N = p.N; a.O = p.O; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre;
+    a.flags = p.flags; a.n_conv = p.n_conv; a.ntile = p.ntile_b; a.J = L.J; a.nnz = p.nnz;
+    for (int i = 0; i < MSGAT_MAX_CONV; ++i) { a.dil[i] = p.dil[i]; a.conv_w[i] = prm->conv_w[i]; a.conv_b[i] = prm->conv_b[i]; }
+    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.sa_W = prm->sa_W;
+    a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
+    a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr;
+    a.csc_ptr = adj ? adj->csc_ptr : nullptr; a.csc_row = adj ? adj->csc_row : nullptr; a.csc_eid = adj ? adj->csc_eid : nullptr;
+    for (int q = 0; q < NJOBS; ++q) {
+      a.jobs[q] = L.jobs[q];
+      if (q == JOB_MC) { a.jobs[q].out = scratch + L.o_dMc; a.jobs[q].blk_stride = (int64_t)p.Oc * p.C; }
+      else { a.jobs[q].out = scratch + L.o_wg + L.off_job[q]; a.jobs[q].blk_stride = L.WGT; }
+    }
+    a.bias_part = scratch + L.o_bias; a.ln_part = scratch + L.o_ln; a.dPt_part = scratch + L.o_dPt;
+    a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dx = dx;
+    a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
+    size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
+    switch (L.NT) {
+      case 8: MSGAT_LAUNCH(k_bwd_main<8>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
+      case 4: MSGAT_LAUNCH(k_bwd_main<4>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
+      case 2: MSGAT_LAUNCH(k_bwd_main<2>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
+      default: MSGAT_LAUNCH(k_bwd_main<1>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
+    }
+  }
+  if (p.Os) {
+    launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
+    SFinArgs a;
+    a.N = p.N; a.nnz = p.nnz; a.qs = saved + p.o_qs; a.Wg = prm->sa_Wg; a.E = saved + p.o_E;
+    a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dq_dense = scratch + L.o_dqd;
+    a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+    a.dqs = scratch + L.o_dqs; a.Wg_part = scratch + L.o_Wg;
+    MSGAT_LAUNCH(k_sfin, dim3(L.nfin, p.B), dim3(128), (144 + 128 * 24) * 4, stream, a);
+  }
+  if (p.Oc || p.Ot) {
+    BSmallArgs a;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J;
+    a.dMc_part = scratch + L.o_dMc; a.dPt_part = scratch + L.o_dPt; a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
+    a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w; a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
+    a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
+    size_t smem = ((size_t)p.C * 48 + 2 * (size_t)p.C * p.C + (size_t)p.Oc * p.C + 528) * 4;
+    MSGAT_LAUNCH(k_bwd_small, dim3(p.B), dim3(256), smem, stream, a);
+  }
+  if (p.Ot && (g->ta_Wt1 || g->ta_Wt2))
+    MSGAT_LAUNCH(k_dwt, dim3((p.N * 20 + 255) / 256), dim3(256), 0, stream, (const float*)(scratch + L.o_dK),
+                 saved + p.o_qt, p.B, p.N, g->ta_Wt1, g->ta_Wt2);
+  {
+    FixArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
+    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.flags = p.flags; a.ntile = L.ntile4; a.J = L.J4;
+    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.ca_alpha = prm->ca_alpha; a.ta_alpha = prm->ta_alpha; a.sa_alpha = prm->sa_alpha;
+    a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK; a.dqs = scratch + L.o_dqs;
+    a.dx = dx; a.pa_n = scratch + L.o_pan; a.pa_t = scratch + L.o_pat; a.pa_s = scratch + L.o_pas;
+    a.ln_part = scratch + L.o_ln + (int64_t)L.nblk * 24;
+    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 3 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
+    MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B), dim3(256), smem, stream, a);
+  }
+  {
+    ReduceArgs r;
+    int nj = 0, tot = 0;
+    auto add = [&](float* dst, const float* src, int n, int nparts, int64_t pstride, int dmul, int doff) {
+      if (!dst || n <= 0 || nj >= MAX_RJOBS) return;
+      r.j[nj] = RJob{dst, src, n, nparts, dmul, doff, pstride};
+      r.starts[nj] = tot; tot += n; ++nj;
+    };
+    const float* wg = scratch + L.o_wg;
+    const float* bp = scratch + L.o_bias;
+    if (p.flags & MSGAT_F_RES) {
+      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, L.nblk, L.WGT, 1, 0);
+      add(g->res_b, bp, p.O, L.nblk, L.nbias, 1, 0);
+    }
+    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, L.nblk, L.WGT, 1, 0);
+    for (int i = 0; i < p.n_conv; ++i) {
+      const int K = i == 0 ? p.C : p.Ot;
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, L.nblk, L.WGT, 2, 0);
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, L.nblk, L.WGT, 2, 1);
+      add(g->conv_b[i], i + 1 == p.n_conv ? bp + p.Oc : bp + p.O + i * p.Ot, p.Ot, L.nblk, L.nbias, 1, 0);
+    }
+    if (p.flags & MSGAT_F_LN) {
+      add(g->ln_w, scratch + L.o_ln, 12, L.nblk + L.nblk4, 24, 1, 0);
+      add(g->ln_b, scratch + L.o_ln + 12, 12, L.nblk + L.nblk4, 24, 1, 0);
+    }
+    if (p.Oc) {
+      if (p.flags & MSGAT_F_CMIX) {
+        add(g->ca_w, scratch + L.o_caw, p.Oc * p.C, p.B, (int64_t)p.Oc * p.C, 1, 0);
+        add(g->ca_b, bp, p.Oc, L.nblk, L.nbias, 1, 0);
+      }
+      add(g->ca_Wc, scratch + L.o_Wc, 144, p.B, 144, 1, 0);
+      add(g->ca_alpha, scratch + L.o_pan, p.N, p.B, p.N, 1, 0);
+    }
+    if (p.Ot) add(g->ta_alpha, scratch + L.o_pat, p.C, L.nblk4, p.C, 1, 0);
+    if (p.Os) {
+      add(g->sa_alpha, scratch + L.o_pas, p.C, L.nblk4, p.C, 1, 0);
+      add(g->sa_Wg, scratch + L.o_Wg, 144, p.B * L.nfin, 144, 1, 0);
+    }
+    r.starts[nj] = tot; r.njobs = nj;
+    if (tot > 0) MSGAT_LAUNCH(k_reduce, dim3((tot + 127) / 128), dim3(128), 0, stream, r);
+  }
+  return 0;
+}

@@ -1,0 +1,40 @@
+"""Batch-sharded data parallelism: one process per GPU, one NCCL all-reduce of a flat
+gradient buffer per step (replaces the reference's single-process ``nn.DataParallel``,
+``src/main.py:53-54``).  Every op of the path is per-sample, so the only
+exchange is the gradient sum: 7.8 MB at PEMSD7, latency-bound on NVLink 5 / NVSwitch."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+class FlatGradients:
+    """Gives every trainable parameter a ``.grad`` that is a view into ONE flat fp32
+    buffer, so that the exchange is a single collective and the optimizer sees reduced
+    gradients.  ``zero()`` clears the buffer in place (do not use ``set_to_none``)."""
+
+    def __init__(self, model: torch.nn.Module):
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        n = sum(p.numel() for p in self.params)
+        dev = self.params[0].device
+        self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
+        o = 0
+        for p in self.params:
+            p.grad = self.flat[o:o + p.numel()].view_as(p)
+            o += p.numel()
+
+    def zero(self):
+        self.flat.zero_()
+
+    def all_reduce_mean(self):
+        """Sum over ranks, divide by the world size: the loss is a mean over the global
+        batch (loss.py:51-52) and every rank holds an equal shard."""
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+            self.flat.div_(dist.get_world_size())
+
+
+def shard_bounds(B: int, rank: int, world: int):
+    if B % world:
+        raise ValueError("global batch must divide evenly across ranks")
+    return rank * B // world, (rank + 1) * B // world

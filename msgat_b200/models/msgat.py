@@ -1,0 +1,243 @@
+"""Drop-in ``GACN`` / ``TACN`` / ``CACN`` / ``MEAM`` / ``TPC`` / ``MSGAT`` and the factories.
+
+Constructor arguments, ``forward`` signatures, attribute paths and parameter shapes follow
+the reference (``src/models/msgat.py``) so that ``engine.py`` / ``main.py`` drive these
+modules unchanged and reference checkpoints load with ``load_state_dict``.  ``nn.Conv2d`` /
+``nn.LayerNorm`` / ``Chomp`` children exist only as parameter holders that keep the
+reference's ``state_dict`` names; they are never called -- every layer's arithmetic is one
+call into the sm_100a kernels (``msgat_b200.ops``).
+"""
+from typing import List
+
+import torch
+from torch import nn
+
+from .. import _lib, ops
+from .attention import ChannelAttention, GraphAttention, TemporalAttention
+from .embeddings import TimeEmbedding
+
+F = _lib
+
+
+class GACN(nn.Module):
+    """GraphAttention followed by ``x W^T`` (msgat.py:25-28)."""
+
+    def __init__(self, in_channels: int, out_channels: int, n_timesteps: int):
+        super().__init__()
+        self.in_channels, self.out_channels, self.n_timesteps = in_channels, out_channels, n_timesteps
+        self.gatt = GraphAttention(n_channels=in_channels, n_timesteps=n_timesteps)
+        self.W = nn.Parameter(torch.empty(out_channels, in_channels))
+
+    def slots(self):
+        return {"sa_W": self.W, "sa_Wg": self.gatt.Wg, "sa_alpha": self.gatt.alpha}
+
+    def forward(self, signals: torch.Tensor, adjacency: torch.Tensor) -> torch.Tensor:
+        cfg = ops.MeamConfig(0, 0, self.out_channels, F.F_SMIX, precision=int(getattr(self, "precision", 0)))
+        return ops.meam_op(signals, cfg, ops.sparse_adjacency(adjacency), self.slots())
+
+    def extra_repr(self) -> str:
+        return f"in_channels={self.in_channels}, out_channels={self.out_channels}, n_timesteps={self.n_timesteps}"
+
+
+class Chomp(nn.Module):
+    """Placeholder that keeps the even slots of ``TACN.seq`` occupied (msgat.py:36-54); the
+    crop it stands for is folded into the causal two-tap form of the conv kernels."""
+
+    def __init__(self, chomp_size: int):
+        super().__init__()
+        self.chomp_size = chomp_size
+
+    def forward(self, input: torch.Tensor) -> torch.Tensor:
+        return input[..., :-self.chomp_size]
+
+    def extra_repr(self) -> str:
+        return f"chomp_size={self.chomp_size}"
+
+
+class TACN(nn.Module):
+    """TemporalAttention then dilated causal convs without activations (msgat.py:59-77)."""
+
+    def __init__(self, in_channels: int, out_channels: int, n_nodes: int, dilations: List[int]):
+        super().__init__()
+        self.in_channels, self.out_channels, self.n_nodes, self.dilations = in_channels, out_channels, n_nodes, dilations
+        layers: List[nn.Module] = [TemporalAttention(n_channels=in_channels, n_nodes=n_nodes)]
+        cin = in_channels
+        for d in dilations:
+            layers.append(nn.Conv2d(cin, out_channels, [1, 2], padding=[0, d], dilation=[1, d]))
+            layers.append(Chomp(chomp_size=d))
+            cin = out_channels
+        self.seq = nn.Sequential(*layers)
+
+    def slots(self):
+        att = self.seq[0]
+        s = {"ta_Wt1": att.Wt1, "ta_Wt2": att.Wt2, "ta_alpha": att.alpha}
+        for i in range(len(self.dilations)):
+            conv = self.seq[1 + 2 * i]
+            s[f"conv_w{i}"], s[f"conv_b{i}"] = conv.weight, conv.bias
+        return s
+
+    def forward(self, signals: torch.Tensor) -> torch.Tensor:
+        width = self.out_channels if len(self.dilations) else signals.shape[1]
+        cfg = ops.MeamConfig(0, width, 0, 0, self.dilations)
+        return ops.meam_op(signals, cfg, None, self.slots())
+
+    def extra_repr(self) -> str:
+        return (f"in_channels={self.in_channels}, out_channels={self.out_channels}, n_nodes={self.n_nodes}, "
+                f"dilations={self.dilations}")
+
+
+class CACN(nn.Module):
+    """ChannelAttention then a 1x1 conv with bias (msgat.py:85-97)."""
+
+    def __init__(self, in_channels: int, out_channels: int, n_nodes: int, n_timesteps: int):
+        super().__init__()
+        self.in_channels, self.out_channels, self.n_nodes, self.n_timesteps = in_channels, out_channels, n_nodes, n_timesteps
+        self.seq = nn.Sequential(ChannelAttention(n_nodes=n_nodes, n_timesteps=n_timesteps),
+                                 nn.Conv2d(in_channels, out_channels, 1))
+
+    def slots(self):
+        return {"ca_Wc": self.seq[0].Wc, "ca_alpha": self.seq[0].alpha, "ca_w": self.seq[1].weight,
+                "ca_b": self.seq[1].bias}
+
+    def forward(self, signals: torch.Tensor) -> torch.Tensor:
+        cfg = ops.MeamConfig(self.out_channels, 0, 0, F.F_CMIX)
+        return ops.meam_op(signals, cfg, None, self.slots())
+
+    def extra_repr(self) -> str:
+        return (f"in_channels={self.in_channels}, out_channels={self.out_channels}, n_nodes={self.n_nodes}, "
+                f"n_timesteps={self.n_timesteps}")
+
+
+class MEAM(nn.Module):
+    """LayerNorm_T, [cacn | tacn | gacn], + 1x1 residual of the raw input, ReLU
+    (msgat.py:105-131) as ONE fused operator."""
+
+    def __init__(self, in_channels: int, out_channels: int, n_nodes: int, n_timesteps: int, dilations: List[int]):
+        assert out_channels % 3 == 0
+        super().__init__()
+        self.in_channels, self.out_channels, self.n_nodes, self.n_timesteps, self.dilations = (
+            in_channels, out_channels, n_nodes, n_timesteps, dilations)
+        self.ln = nn.LayerNorm([n_timesteps])
+        self.res = nn.Conv2d(in_channels, out_channels, kernel_size=1)
+        self.cacn = CACN(in_channels, out_channels // 3, n_nodes=n_nodes, n_timesteps=n_timesteps)
+        self.tacn = TACN(in_channels, out_channels // 3, n_nodes=n_nodes, dilations=dilations)
+        self.gacn = GACN(in_channels, out_channels // 3, n_timesteps=n_timesteps)
+        self.precision = F.PREC_FP32
+
+    def slots(self):
+        s = {"ln_w": self.ln.weight, "ln_b": self.ln.bias, "res_w": self.res.weight, "res_b": self.res.bias}
+        s.update(self.cacn.slots())
+        s.update(self.tacn.slots())
+        s.update(self.gacn.slots())
+        return s
+
+    def forward(self, signals: torch.Tensor, adjacency: torch.Tensor) -> torch.Tensor:
+        return self._run(signals, adjacency, False, False)
+
+    def _run(self, signals, adjacency, dout_masked: bool, x_is_relu: bool):
+        """``dout_masked`` / ``x_is_relu`` are set only by TPC for MEAMs chained inside it
+        (see ``ops.MeamConfig``); the public ``forward`` has plain autograd semantics."""
+        b = self.out_channels // 3
+        if abs(float(self.ln.eps) - 1e-5) > 0:
+            raise ValueError("kernels assume the LayerNorm default eps=1e-5 (msgat.py:115)")
+        cfg = ops.MeamConfig(b, b, b, F.F_LN | F.F_RES | F.F_RELU | F.F_CMIX | F.F_SMIX, self.dilations,
+                             precision=self.precision, dout_masked=dout_masked, x_is_relu=x_is_relu)
+        return ops.meam_op(signals, cfg, ops.sparse_adjacency(adjacency), self.slots())
+
+    def extra_repr(self) -> str:
+        return (f"in_channels={self.in_channels}, out_channels={self.out_channels}, n_nodes={self.n_nodes}, "
+                f"n_timesteps={self.n_timesteps}, dilations={self.dilations}")
+
+
+class TPC(nn.Module):
+    """Stack of MEAMs, LayerNorm_T and the ``Conv2d(T -> Tout, [1, C])`` head (msgat.py:139-160).
+
+    Inside the stack each MEAM's backward hands the previous one a gradient that already
+    carries that MEAM's ReLU mask (the mask is free there: the ReLU output is the next
+    layer's input tile), so no separate masking pass over the activations runs."""
+
+    def __init__(self, channels: List[int], n_nodes: int, in_timesteps: int, out_timesteps: int, dilations: List[int]):
+        super().__init__()
+        self.channels, self.n_nodes, self.in_timesteps, self.out_timesteps, self.dilations = (
+            channels, n_nodes, in_timesteps, out_timesteps, dilations)
+        self.tgacns = nn.ModuleList([
+            MEAM(channels[i], channels[i + 1], n_nodes=n_nodes, n_timesteps=in_timesteps, dilations=d)
+            for i, d in enumerate(dilations)
+        ])
+        self.ln = nn.LayerNorm([in_timesteps])
+        self.fc = nn.Conv2d(in_timesteps, out_timesteps, kernel_size=[1, channels[-1]])
+
+    def forward(self, signals: torch.Tensor, adjacency: torch.Tensor, gate: torch.Tensor = None,
+                acc: torch.Tensor = None) -> torch.Tensor:
+        for i, meam in enumerate(self.tgacns):
+            # the only consumer of this MEAM's output (next MEAM or the head) returns a masked gradient
+            signals = meam._run(signals, adjacency, dout_masked=True, x_is_relu=i > 0)
+        return ops.head_op(signals, self.ln.weight, self.ln.bias, self.fc.weight, self.fc.bias, gate=gate, acc=acc,
+                           x_is_relu=len(self.tgacns) > 0)
+
+    def extra_repr(self) -> str:
+        return (f"channels={self.channels}, n_nodes={self.n_nodes}, in_timesteps={self.in_timesteps}, "
+                f"out_timesteps={self.out_timesteps}, dilations={self.dilations}")
+
+
+class MSGAT(nn.Module):
+    """sum_m TPC_m(X[:, m], adj) * gate_m (msgat.py:184-217).
+
+    Shapes: ``X [B, M, C, N, T]``, ``H [B]``, ``D [B]`` -> ``[B, N, Tout]``."""
+
+    def __init__(self, components: List[dict], in_timesteps: int, out_timesteps: int, use_te: bool, adj: torch.Tensor):
+        super().__init__()
+        if use_te:
+            self.te = TimeEmbedding(len(components), len(adj), out_timesteps)
+        else:
+            # the reference's forward dereferences self.te unconditionally and crashes here
+            # (SURVEY.md 7.3-9); the static gate is honoured instead, everything else is unchanged
+            self.te = None
+            self.W = nn.Parameter(torch.empty(len(components), len(adj), out_timesteps))
+        self.adj = nn.Parameter(adj, requires_grad=False)
+        self.tpcs = nn.ModuleList([
+            TPC(channels=c["channels"], n_nodes=len(adj), in_timesteps=in_timesteps, out_timesteps=out_timesteps,
+                dilations=c["dilations"]) for c in components
+        ])
+        self.reset_parameters()
+
+    def set_precision(self, precision: int):
+        for tpc in self.tpcs:
+            for m in tpc.tgacns:
+                m.precision = precision
+        return self
+
+    def forward(self, X: torch.Tensor, H: torch.Tensor, D: torch.Tensor) -> torch.Tensor:
+        if self.te is not None:
+            G = self.te(H, D).float()  # [B, M, N, Tout]
+            gates = [G[:, m] for m in range(len(self.tpcs))]
+        else:
+            gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(len(self.tpcs))]
+        out = None
+        for m, tpc in enumerate(self.tpcs):
+            out = tpc(X[:, m], self.adj, gate=gates[m], acc=out)
+        return out
+
+    def reset_parameters(self):
+        """xavier-normal for matrices, U(+-1/sqrt(size0)) for vectors incl. the LayerNorm
+        affine (msgat.py:206-217)."""
+        for prm in self.parameters():
+            if not prm.requires_grad:
+                continue
+            if prm.ndim >= 2:
+                nn.init.xavier_normal_(prm)
+            else:
+                s = prm.size(0) ** -0.5
+                nn.init.uniform_(prm, -s, s)
+
+
+def _stack(width: int, dilations):
+    def factory(n_components: int, in_channels: int, **kwargs):
+        comp = {"channels": [in_channels] + [width] * len(dilations), "dilations": dilations}
+        return MSGAT([dict(comp) for _ in range(n_components)], **kwargs)
+    return factory
+
+
+msgat48 = _stack(48, [[1, 2], [2, 4]])
+msgat72 = _stack(72, [[1, 2], [2, 4]])
+msgat96 = _stack(96, [[1, 1, 2, 2], [4, 4]])

@@ -158,3 +158,59 @@ def meam_op(x: torch.Tensor, cfg: MeamConfig, adj: Optional[SparseAdjacency],
     """Run the MEAM-shaped operator; ``params`` maps slot names (``SLOTS``) to tensors."""
     with torch.autocast(device_type=x.device.type, enabled=False):
         return _MeamFunction.apply(x, cfg, adj, *[params.get(n) for n in SLOTS])
+
+
+class _HeadFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, fc_w, fc_b, gate, acc, x_is_relu):
+        lib = _lib.get()
+        x = x.float().contiguous()
+        B, Cc, N, T = x.shape
+        if T != 12:
+            raise ValueError("msgat_b200 kernels are specialised for 12 timesteps (main.py:45)")
+        Tout = fc_w.shape[0]
+        ln_w, ln_b, fc_w, fc_b = (t.detach().float().contiguous() for t in (ln_w, ln_b, fc_w, fc_b))
+        if gate is not None:
+            gate = gate.detach().float()
+            if gate.stride(2) != 1 or gate.stride(1) != Tout:
+                gate = gate.contiguous()
+        d = _lib.HeadDesc(B, Cc, N, Tout, 0 if acc is None else 1, 1 if x_is_relu else 0,
+                          0 if gate is None else gate.stride(0))
+        head_out = torch.empty(B, N, Tout, dtype=torch.float32, device=x.device)
+        out = torch.empty_like(head_out) if acc is None else acc.detach().float().contiguous().clone()
+        _lib.check(lib.msgat_head_forward(C.byref(d), _lib.ptr(x), _lib.ptr(ln_w), _lib.ptr(ln_b), _lib.ptr(fc_w),
+                                          _lib.ptr(fc_b), _lib.ptr(gate), _lib.ptr(head_out), _lib.ptr(out),
+                                          _lib.stream_of(x)), "msgat_head_forward")
+        ctx.save_for_backward(x, ln_w, ln_b, fc_w, gate if gate is not None else head_out, head_out)
+        ctx.has_gate, ctx.has_acc, ctx.x_is_relu = gate is not None, acc is not None, x_is_relu
+        ctx.gate_needs_grad = gate is not None and ctx.needs_input_grad[5]
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.get()
+        x, ln_w, ln_b, fc_w, gate, head_out = ctx.saved_tensors
+        if not ctx.has_gate:
+            gate = None
+        dout = dout.float().contiguous()
+        B, Cc, N, T = x.shape
+        Tout = fc_w.shape[0]
+        d = _lib.HeadDesc(B, Cc, N, Tout, 0, 1 if ctx.x_is_relu else 0, 0 if gate is None else gate.stride(0))
+        dx = torch.empty_like(x)
+        g_lnw, g_lnb, g_fcw = torch.empty_like(ln_w), torch.empty_like(ln_b), torch.empty_like(fc_w)
+        g_fcb = torch.empty(Tout, dtype=torch.float32, device=x.device)
+        g_gate = torch.empty_like(head_out) if ctx.gate_needs_grad else None
+        scratch = torch.empty(max(int(lib.msgat_head_scratch_floats(C.byref(d))), 4), dtype=torch.float32,
+                              device=x.device)
+        _lib.check(lib.msgat_head_backward(C.byref(d), _lib.ptr(x), _lib.ptr(ln_w), _lib.ptr(ln_b), _lib.ptr(fc_w),
+                                           _lib.ptr(gate), _lib.ptr(head_out), _lib.ptr(dout), _lib.ptr(dx),
+                                           _lib.ptr(g_lnw), _lib.ptr(g_lnb), _lib.ptr(g_fcw), _lib.ptr(g_fcb),
+                                           _lib.ptr(g_gate), _lib.ptr(scratch), _lib.stream_of(x)),
+                   "msgat_head_backward")
+        return dx, g_lnw, g_lnb, g_fcw, g_fcb, g_gate, (dout if ctx.has_acc else None), None
+
+
+def head_op(x, ln_w, ln_b, fc_w, fc_b, gate=None, acc=None, x_is_relu=False):
+    """TPC head + gate (+ running sum over components): returns ``acc + head(x) * gate``."""
+    with torch.autocast(device_type=x.device.type, enabled=False):
+        return _HeadFunction.apply(x, ln_w, ln_b, fc_w, fc_b, gate, acc, x_is_relu)

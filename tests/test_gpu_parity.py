@@ -1,0 +1,141 @@
+"""Parity of the sm_100a kernels (through the drop-in modules -> ctypes -> C ABI) with the
+reference: golden fixtures minted from the unmodified reference, the CPU oracle on seeded
+PEMS-shaped inputs, and size-independent properties at the full benchmark shapes."""
+import pytest
+import torch
+
+from conftest import Golden, golden_cases, rel_l2
+from layer_cases import run_case
+from parity import check_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", golden_cases(""))
+def test_kernels_match_reference_golden(case):
+    G = Golden(case)
+    out, grads, gin = run_case(G, device="cuda")
+    fails, _ = check_case(G, out, grads, gin)
+    assert not fails, "\n".join(fails)
+
+
+def _model_and_batch(name, B, width="msgat72", seed=0, N=None):
+    from msgat_b200 import models, synthetic
+    s = dict(synthetic.PEMS_SHAPES[name])
+    if N is not None:
+        s["N"], s["E"] = N, int(N * 1.2)
+    torch.manual_seed(seed)
+    adj = synthetic.road_graph(s["N"], s["E"], seed=0) if s["E"] else synthetic.geometric_graph(s["N"])
+    model = getattr(models, width)(n_components=s["M"], in_channels=s["C"], in_timesteps=12, out_timesteps=12,
+                                   use_te=True, adj=adj.clone())
+    batch = synthetic.make_batch(B, s["M"], s["C"], s["N"], seed=1234)
+    return model, batch
+
+
+@pytest.mark.parametrize("name,B", [("pemsd8", 3), ("pemsd4", 2), ("pemsd3", 2), ("pemsd7", 2)])
+def test_full_model_matches_oracle_fp64(name, B):
+    """Forward, dX and every parameter gradient of the whole MSGAT at the real graph sizes
+    against the CPU oracle in fp64 (same state_dict)."""
+    from oracle import msgat_oracle as O
+    model, batch = _model_and_batch(name, B)
+    p = {k: v.detach().double().requires_grad_(v.is_floating_point() and k != "adj")
+         for k, v in model.state_dict().items()}
+    X64 = batch.X.double().requires_grad_(True)
+    ref = O.msgat(X64, batch.H, batch.D, p, O.MODEL_DILATIONS["msgat72"])
+    O.huber(ref, batch.Y.double(), 50.0).backward()
+    # the reference arithmetic in fp32 on the same inputs gives the noise floor of each tensor
+    p32 = {k: v.detach().float().requires_grad_(v.is_floating_point() and k != "adj") for k, v in p.items()}
+    X32 = batch.X.clone().requires_grad_(True)
+    ref32 = O.msgat(X32, batch.H, batch.D, p32, O.MODEL_DILATIONS["msgat72"])
+    O.huber(ref32, batch.Y, 50.0).backward()
+
+    model = model.cuda()
+    X = batch.X.cuda().requires_grad_(True)
+    out = model(X, batch.H.cuda(), batch.D.cuda())
+    O.huber(out, batch.Y.cuda(), 50.0).backward()
+    fails = []
+
+    def one(label, got, want, want32):
+        e, n = rel_l2(got, want), rel_l2(want32, want)
+        if not e < max(1e-5, 4 * n):
+            fails.append(f"{label}: {e:.3e} (fp32 oracle noise {n:.2e})")
+    one("out", out, ref, ref32)
+    one("dX", X.grad, X64.grad, X32.grad)
+    for n, prm in model.named_parameters():
+        if p[n].grad is None:
+            continue
+        one(n, prm.grad, p[n].grad, p32[n].grad)
+    assert not fails, "\n".join(fails)
+
+
+def test_pemsd7_full_batch_properties():
+    """At BASELINE.json's full size (N=883, B=32) the oracle is too slow; check properties:
+    every sample of the batch is computed independently (bit-exact vs a batch of one),
+    the result is deterministic, and the loss gradient is finite everywhere."""
+    from oracle import msgat_oracle as O
+    model, batch = _model_and_batch("pemsd7", 32)
+    model = model.cuda()
+    X, H, D, Y = batch.X.cuda(), batch.H.cuda(), batch.D.cuda(), batch.Y.cuda()
+    Xg = X.clone().requires_grad_(True)
+    out = model(Xg, H, D)
+    O.huber(out, Y, 50.0).backward()
+    assert torch.isfinite(out).all() and torch.isfinite(Xg.grad).all()
+    for prm in model.parameters():
+        if prm.grad is not None:
+            assert torch.isfinite(prm.grad).all()
+    with torch.no_grad():
+        out2 = model(X, H, D)
+        assert torch.equal(out2, out.detach()), "forward is not deterministic"
+        for b in (0, 17, 31):
+            ob = model(X[b:b + 1], H[b:b + 1], D[b:b + 1])
+            assert torch.equal(ob[0], out2[b]), f"sample {b} depends on its batch"
+
+
+def test_node_permutation_equivariance():
+    """Relabelling the sensors (adjacency, per-node parameters, inputs) permutes the output:
+    attention over N is permutation-equivariant (attention.py:32-36)."""
+    from msgat_b200 import models
+    model, batch = _model_and_batch("pemsd8", 2)
+    N = model.adj.shape[0]
+    perm = torch.randperm(N, generator=torch.Generator().manual_seed(5))
+    sd = model.state_dict()
+    sd2 = {}
+    M, Tout = len(model.tpcs), 12
+    for k, v in sd.items():
+        if k == "adj":
+            sd2[k] = v[perm][:, perm]
+        elif k.endswith(("cacn.seq.0.alpha",)):
+            sd2[k] = v[perm]
+        elif k.endswith(("Wt1", "Wt2")):
+            sd2[k] = v[:, perm]
+        elif k.startswith("te."):
+            sd2[k] = v.view(v.shape[0], M, N, Tout)[:, :, perm].reshape(v.shape)
+        else:
+            sd2[k] = v
+    model2 = models.msgat72(n_components=M, in_channels=batch.X.shape[2], in_timesteps=12, out_timesteps=12,
+                            use_te=True, adj=sd2["adj"].clone())
+    model2.load_state_dict(sd2)
+    model, model2 = model.cuda(), model2.cuda()
+    with torch.no_grad():
+        a = model(batch.X.cuda(), batch.H.cuda(), batch.D.cuda())
+        b = model2(batch.X[:, :, :, perm].cuda(), batch.H.cuda(), batch.D.cuda())
+    assert rel_l2(b, a[:, perm]) < 1e-5
+
+
+def test_engine_protocol_autocast_and_state_dict():
+    """The reference engine calls the model under cuda.amp.autocast with a GradScaler
+    (engine.py:54,61) and round-trips state_dict (engine.py:139,152)."""
+    from oracle import msgat_oracle as O
+    model, batch = _model_and_batch("pemsd8", 2)
+    model = model.cuda()
+    scaler = torch.amp.GradScaler("cuda")
+    with torch.autocast("cuda"):
+        out = model(batch.X.cuda(), batch.H.cuda(), batch.D.cuda())
+        loss = O.huber(out.float(), batch.Y.cuda(), 50.0)
+    scaler.scale(loss).backward()
+    assert out.dtype == torch.float32
+    with torch.no_grad():
+        ref = model(batch.X.cuda(), batch.H.cuda(), batch.D.cuda())
+    assert torch.equal(ref, out.detach()), "autocast changed the arithmetic of the fp32 path"
+    sd = {k: v.clone() for k, v in model.state_dict().items()}
+    model.load_state_dict(sd)
