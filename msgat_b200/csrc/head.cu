@@ -172,7 +172,7 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_head_bwd(HeadArgs a) {
 }
 
 static int head_J(const msgat_head_desc* d, int ntile) {
-  int J = (2 * 148 + d->B - 1) / d->B;
+  int J = (2 * 148) / d->B;
   return J > ntile ? ntile : (J < 1 ? 1 : J);
 }
 static int head_check(const msgat_head_desc* d) {

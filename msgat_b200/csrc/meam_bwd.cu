@@ -19,7 +19,8 @@
 #include "kernels.h"
 #include "tile_ops.cuh"
 
-#define RB 4  // 4x4 weight-gradient blocks held in registers per thread
+// Weight gradients: every 4x4 block of every weight matrix is owned by one (thread, register slot);
+// when there are fewer blocks than slots each block is split into S position slices.
 
 struct WJob {
   int start, nblk, nkb, Oa, Kb;
@@ -40,15 +41,17 @@ struct BwdArgs {
   const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
   WJob jobs[NJOBS];
   float *bias_part, *ln_part, *dPt_part, *delta, *dSnz, *dx;
-  int nbias, arena_floats;
+  int nbias, arena_floats, S;
 };
 
 // acc[r] (+)= A[oa..oa+3][p] . B[kb..kb+3][p] over the tile's positions, for the blocks of job jb
-MSGAT_DEV void wgrad_accum(float (&acc)[RB][16], const WJob& jb, const float* A, const float* Bm, int PS, int PQ, int tapd) {
+template <int RBT>
+MSGAT_DEV void wgrad_accum(float (&acc)[RBT][16], const WJob& jb, const float* A, const float* Bm, int PS, int PQ, int tapd, int S) {
   MSGAT_UNROLL
-  for (int r = 0; r < RB; ++r) {
-    const int local = (int)threadIdx.x + r * (int)blockDim.x - jb.start;
-    if (local < 0 || local >= jb.nblk) continue;
+  for (int r = 0; r < RBT; ++r) {
+    const int vloc = (int)threadIdx.x + r * (int)blockDim.x - jb.start;
+    if (vloc < 0 || vloc >= jb.nblk * S) continue;
+    const int slice = vloc / jb.nblk, local = vloc - slice * jb.nblk;
     const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
     const float* ar[4];
     const float* br[4];
@@ -56,7 +59,10 @@ MSGAT_DEV void wgrad_accum(float (&acc)[RB][16], const WJob& jb, const float* A,
       ar[i] = A + (oa + i < jb.Oa ? oa + i : jb.Oa - 1) * PS;
       br[i] = Bm + (kb + i < jb.Kb ? kb + i : jb.Kb - 1) * PS;
     }
-    for (int pq = 0; pq < PQ; ++pq) {
+    float tl[16];  // tile-local sums first, then one add into the long-running accumulator
+    MSGAT_UNROLL
+    for (int i = 0; i < 16; ++i) tl[i] = 0.f;
+    for (int pq = slice; pq < PQ; pq += S) {
       const int nl = pq / 3, t0 = (pq - nl * 3) * 4, off = nl * 12;
       float4 a[4], b[4];
       for (int i = 0; i < 4; ++i) a[i] = ld4(ar[i] + off + t0);
@@ -64,21 +70,25 @@ MSGAT_DEV void wgrad_accum(float (&acc)[RB][16], const WJob& jb, const float* A,
       MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) {
         MSGAT_UNROLL
-        for (int j = 0; j < 4; ++j) acc[r][i * 4 + j] += dot4(a[i], b[j]);
+        for (int j = 0; j < 4; ++j) tl[i * 4 + j] += dot4(a[i], b[j]);
       }
     }
+    MSGAT_UNROLL
+    for (int i = 0; i < 16; ++i) acc[r][i] += tl[i];
   }
 }
 
-MSGAT_DEV void wgrad_flush(const float (&acc)[RB][16], const WJob* jobs, int blk) {
-  for (int r = 0; r < RB; ++r) {
+template <int RBT>
+MSGAT_DEV void wgrad_flush(const float (&acc)[RBT][16], const WJob* jobs, int blk, int S) {
+  for (int r = 0; r < RBT; ++r) {
     const int id = (int)threadIdx.x + r * (int)blockDim.x;
     for (int q = 0; q < NJOBS; ++q) {
       const WJob& jb = jobs[q];
-      const int local = id - jb.start;
-      if (jb.nblk == 0 || local < 0 || local >= jb.nblk) continue;
+      const int vloc = id - jb.start;
+      if (jb.nblk == 0 || vloc < 0 || vloc >= jb.nblk * S) continue;
+      const int slice = vloc / jb.nblk, local = vloc - slice * jb.nblk;
       const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
-      float* dst = jb.out + (int64_t)blk * jb.blk_stride;
+      float* dst = jb.out + ((int64_t)blk * S + slice) * jb.blk_stride;
       for (int i = 0; i < 4; ++i)
         for (int j = 0; j < 4; ++j)
           if (oa + i < jb.Oa && kb + j < jb.Kb) dst[(oa + i) * jb.Kb + kb + j] = acc[r][i * 4 + j];
@@ -123,8 +133,8 @@ static int64_t bwd_smem_floats(const Plan& p, int NT, int nthreads) {
   return f;
 }
 
-template <int NT>
-MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
+template <int NT, int RBT>
+MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   constexpr int P = NT * 12, PS = P + 4, PQ = NT * 3;
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
@@ -157,9 +167,10 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
   if (a.Ot) for (int i = tid; i < 144; i += T) Pt[i] = a.Pt[(int64_t)b * 144 + i];
   if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
 
-  float acc[RB][16];
-  for (int r = 0; r < RB; ++r) for (int i = 0; i < 16; ++i) acc[r][i] = 0.f;
-  float bacc = 0.f, pt_acc = 0.f, lnw_acc[12], lnb_acc[12];
+  float acc[RBT][16];
+  for (int r = 0; r < RBT; ++r) for (int i = 0; i < 16; ++i) acc[r][i] = 0.f;
+  float bacc = 0.f, lnw_acc[12], lnb_acc[12];
+  double pt_acc = 0.0;
   for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
 
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
@@ -176,7 +187,7 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
     }
     __syncthreads();
     // ---- S1: residual weight gradient (msgat.py:116,131) and the row sums behind three biases
-    if (has_res) wgrad_accum(acc, a.jobs[JOB_RES], G, OT, PS, PQ, -1);
+    if (has_res) wgrad_accum<RBT>(acc, a.jobs[JOB_RES], G, OT, PS, PQ, -1, a.S);
     if (tid < a.O) {
       const float* q = G + tid * PS;
       float s = 0.f;
@@ -192,7 +203,7 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
       if (a.Oc) mix_item(d, G, PS, a.Oc, AR, RC, c0, nl, t0);
       for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
     }
-    if (a.Oc) wgrad_accum(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1);
+    if (a.Oc) wgrad_accum<RBT>(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1, a.S);
     __syncthreads();
     // ---- S3: temporal branch
     if (a.Ot) {
@@ -222,8 +233,8 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
       for (int i = a.n_conv - 1; i >= 0; --i) {
         const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
         const float* in = i == 0 ? OT : Y[i - 1];
-        wgrad_accum(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i]);
-        wgrad_accum(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1);
+        wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i], a.S);
+        wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1, a.S);
         if (i + 1 < a.n_conv) {
           const int row = tid - a.O - i * a.Ot;
           if (row >= 0 && row < a.Ot) {
@@ -253,8 +264,8 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
         const int ngr = T / 9;
         if (tid < ngr * 9) {
           const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4;
-          float o16[16];
-          for (int i = 0; i < 16; ++i) o16[i] = 0.f;
+          double o16[16];
+          for (int i = 0; i < 16; ++i) o16[i] = 0.0;
           for (int r = grp; r < C * NT; r += ngr) {
             const int c = r / NT, nl = r - c * NT;
             const float4 g = ld4(dOt + c * PS + nl * 12 + tb), h = ld4(H + c * PS + nl * 12 + ib);
@@ -264,14 +275,14 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
             o16[12] += g.w * h.x; o16[13] += g.w * h.y; o16[14] += g.w * h.z; o16[15] += g.w * h.w;
           }
           for (int i = 0; i < 4; ++i)
-            for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = o16[i * 4 + j];
+            for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
         }
         // dh[c,n,i] += sum_t Pt[t][i] dOt[c,n,t]
         tile_temporal(DH, dOt, PS, C, NT, Pt, true, true);
         __syncthreads();
         if (tid < 144) {
-          float s = 0.f;
-          for (int g2 = 0; g2 < ngr; ++g2) s += AR[g2 * 144 + tid];
+          double s = 0.0;
+          for (int g2 = 0; g2 < ngr; ++g2) s += (double)AR[g2 * 144 + tid];
           pt_acc += s;
         }
         __syncthreads();
@@ -315,7 +326,7 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
           for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DOS + (c0 + j) * PS + nl * 12 + t0, e[j]);
         }
       }
-      if (smix) wgrad_accum(acc, a.jobs[JOB_WS], GZ, H, PS, PQ, -1);
+      if (smix) wgrad_accum<RBT>(acc, a.jobs[JOB_WS], GZ, H, PS, PQ, -1, a.S);
       __syncthreads();
       // dA[n,i] at the adjacency non-zeros, delta[n] = sum_i A[n,i] dA[n,i]; one warp per row
       const float* GA = DOS ? DOS : Gs;
@@ -385,9 +396,9 @@ MSGAT_KERNEL MSGAT_LB(384, 1) k_bwd_main(BwdArgs a) {
   }
   // ---- flush the per-block partials
   __syncthreads();
-  wgrad_flush(acc, a.jobs, blk);
+  wgrad_flush<RBT>(acc, a.jobs, blk, a.S);
   if (tid < a.nbias) a.bias_part[(int64_t)blk * a.nbias + tid] = bacc;
-  if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
+  if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = (float)pt_acc;
   {
     const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
     for (int t = 0; t < 12; ++t) {
@@ -462,7 +473,7 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
 
 // ---------------------------------------------------------------------------------------
 struct BSmallArgs {
-  int C, Oc, Ot, cmix, J;
+  int C, Oc, Ot, cmix, J, Jm;
   const float *dMc_part, *dPt_part, *Pc, *qc, *Wc, *ca_w, *Pt, *K;
   float *caw_part, *Wc_part, *dqc, *dK;
 };
@@ -483,22 +494,22 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     for (int i = tid; i < C * 12; i += T) qc[i] = a.qc[(int64_t)b * C * 12 + i];
     for (int i = tid; i < C * C; i += T) Pc[i] = a.Pc[(int64_t)b * C * C + i];
     for (int i = tid; i < a.Oc * C; i += T) {
-      float s = 0.f;
-      for (int j = 0; j < a.J; ++j) s += a.dMc_part[((int64_t)b * a.J + j) * a.Oc * C + i];
+      double s = 0.0;
+      for (int j = 0; j < a.Jm; ++j) s += a.dMc_part[((int64_t)b * a.Jm + j) * a.Oc * C + i];
       dMc[i] = s;
     }
     __syncthreads();
     if (a.cmix) {  // dW1 = dMc Pc^T ; dPc = W1^T dMc   (msgat.py:94)
       for (int i = tid; i < a.Oc * C; i += T) {
         const int o = i / C, c = i - o * C;
-        float s = 0.f;
-        for (int k = 0; k < C; ++k) s = fmaf(dMc[o * C + k], Pc[c * C + k], s);
+        double s = 0.0;
+        for (int k = 0; k < C; ++k) s += (double)(dMc[o * C + k]) * (double)(Pc[c * C + k]);
         a.caw_part[(int64_t)b * a.Oc * C + i] = s;
       }
       for (int i = tid; i < C * C; i += T) {
         const int c = i / C, k = i - c * C;
-        float s = 0.f;
-        for (int o = 0; o < a.Oc; ++o) s = fmaf(__ldg(a.ca_w + o * C + c), dMc[o * C + k], s);
+        double s = 0.0;
+        for (int o = 0; o < a.Oc; ++o) s += (double)(__ldg(a.ca_w + o * C + c)) * (double)(dMc[o * C + k]);
         dS[i] = s;
       }
     } else {
@@ -506,27 +517,27 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     }
     __syncthreads();
     for (int c = tid; c < C; c += T) {  // softmax backward, row-wise
-      float s = 0.f;
-      for (int k = 0; k < C; ++k) s = fmaf(Pc[c * C + k], dS[c * C + k], s);
-      for (int k = 0; k < C; ++k) dS[c * C + k] = Pc[c * C + k] * (dS[c * C + k] - s);
+      double s = 0.0;
+      for (int k = 0; k < C; ++k) s += (double)(Pc[c * C + k]) * (double)(dS[c * C + k]);
+      for (int k = 0; k < C; ++k) dS[c * C + k] = (float)((double)Pc[c * C + k] * ((double)dS[c * C + k] - s));
     }
     for (int i = tid; i < C * 12; i += T) {
       const int c = i / 12, t = i - c * 12;
-      float s1 = 0.f, s2 = 0.f;
+      double s1 = 0.0, s2 = 0.0;
       for (int u = 0; u < 12; ++u) {
-        s1 = fmaf(__ldg(a.Wc + t * 12 + u), qc[c * 12 + u], s1);   // (qc Wc^T)[c][t]
-        s2 = fmaf(qc[c * 12 + u], __ldg(a.Wc + u * 12 + t), s2);   // (qc Wc)[c][t]
+        s1 += (double)(__ldg(a.Wc + t * 12 + u)) * (double)(qc[c * 12 + u]);   // (qc Wc^T)[c][t]
+        s2 += (double)(qc[c * 12 + u]) * (double)(__ldg(a.Wc + u * 12 + t));   // (qc Wc)[c][t]
       }
       A1[i] = s1; A2[i] = s2;
     }
     __syncthreads();
     for (int i = tid; i < C * 12; i += T) {
       const int c = i / 12, t = i - c * 12;
-      float s = 0.f, s3 = 0.f;
+      double s = 0.0, s3 = 0.0;
       for (int k = 0; k < C; ++k) {
-        s = fmaf(dS[c * C + k], A1[k * 12 + t], s);
-        s = fmaf(dS[k * C + c], A2[k * 12 + t], s);
-        s3 = fmaf(dS[c * C + k], qc[k * 12 + t], s3);
+        s += (double)(dS[c * C + k]) * (double)(A1[k * 12 + t]);
+        s += (double)(dS[k * C + c]) * (double)(A2[k * 12 + t]);
+        s3 += (double)(dS[c * C + k]) * (double)(qc[k * 12 + t]);
       }
       a.dqc[(int64_t)b * C * 12 + i] = s;
       T2[i] = s3;
@@ -534,8 +545,8 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     __syncthreads();
     for (int i = tid; i < 144; i += T) {
       const int t = i / 12, u = i - t * 12;
-      float s = 0.f;
-      for (int c = 0; c < C; ++c) s = fmaf(qc[c * 12 + t], T2[c * 12 + u], s);
+      double s = 0.0;
+      for (int c = 0; c < C; ++c) s += (double)(qc[c * 12 + t]) * (double)(T2[c * 12 + u]);
       a.Wc_part[(int64_t)b * 144 + i] = s;
     }
   }
@@ -544,23 +555,23 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     __syncthreads();
     for (int i = tid; i < 144; i += T) {
       Pt[i] = a.Pt[(int64_t)b * 144 + i];
-      float s = 0.f;
+      double s = 0.0;
       for (int j = 0; j < a.J; ++j) s += a.dPt_part[((int64_t)b * a.J + j) * 144 + i];
       dSt[i] = s;
     }
     for (int i = tid; i < 240; i += T) K[i] = a.K[(int64_t)b * 240 + i];
     __syncthreads();
     if (tid < 12) {
-      float s = 0.f;
-      for (int k = 0; k < 12; ++k) s = fmaf(Pt[tid * 12 + k], dSt[tid * 12 + k], s);
-      for (int k = 0; k < 12; ++k) dSt[tid * 12 + k] = Pt[tid * 12 + k] * (dSt[tid * 12 + k] - s);
+      double s = 0.0;
+      for (int k = 0; k < 12; ++k) s += (double)(Pt[tid * 12 + k]) * (double)(dSt[tid * 12 + k]);
+      for (int k = 0; k < 12; ++k) dSt[tid * 12 + k] = (float)((double)Pt[tid * 12 + k] * ((double)dSt[tid * 12 + k] - s));
     }
     __syncthreads();
     for (int i = tid; i < 240; i += T) {
       const int t = i / 20, r = i - t * 20;
-      float s = 0.f;
-      if (r < 10) { for (int k = 0; k < 12; ++k) s = fmaf(dSt[t * 12 + k], K[k * 20 + 10 + r], s); }   // dK1 = dS K2
-      else { for (int k = 0; k < 12; ++k) s = fmaf(dSt[k * 12 + t], K[k * 20 + r - 10], s); }         // dK2 = dS^T K1
+      double s = 0.0;
+      if (r < 10) { for (int k = 0; k < 12; ++k) s += (double)(dSt[t * 12 + k]) * (double)(K[k * 20 + 10 + r]); }   // dK1 = dS K2
+      else { for (int k = 0; k < 12; ++k) s += (double)(dSt[k * 12 + t]) * (double)(K[k * 20 + r - 10]); }         // dK2 = dS^T K1
       a.dK[(int64_t)b * 240 + i] = s;
     }
   }
@@ -608,7 +619,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   if (a.Oc) for (int i = tid; i < C * 12; i += T) DQC[i] = a.dqc[(int64_t)b * C * 12 + i];
   if (a.Ot) for (int i = tid; i < 240; i += T) DK[i] = a.dK[(int64_t)b * 240 + i];
   if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
-  float at_acc = 0.f, as_acc = 0.f, lnw_acc[12], lnb_acc[12];
+  double at_acc = 0.0, as_acc = 0.0;
+  float lnw_acc[12], lnb_acc[12];
   for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
     const int n0 = tile * NT;
@@ -629,7 +641,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
     __syncthreads();
     for (int r = tid; r < C * NT; r += T) {
       const int c = r / NT, nl = r - c * NT, n = n0 + nl;
-      float v1 = 0.f, v2 = 0.f, v3 = 0.f;
+      double v1 = 0.0, v2 = 0.0, v3 = 0.0;
       if (n < a.N) {
         const float* src = a.x + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
         float xv[12], xh[12], h[12], dh[12];
@@ -653,7 +665,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         for (int t = 0; t < 12; ++t) {
           const float dqc = a.Oc ? DQC[c * 12 + t] : 0.f, dqt = DQT[nl * 12 + t], dqs = DQS[nl * 12 + t];
           dh[t] = an * dqc + att * dqt + as * dqs;
-          v1 = fmaf(dqc, h[t], v1); v2 = fmaf(dqt, h[t], v2); v3 = fmaf(dqs, h[t], v3);
+          v1 += (double)dqc * h[t]; v2 += (double)dqt * h[t]; v3 += (double)dqs * h[t];
         }
         float out[12];
         if (do_ln) {
@@ -678,7 +690,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         d2.x += out[8]; d2.y += out[9]; d2.z += out[10]; d2.w += out[11];
         st4(d, d0); st4(d + 4, d1); st4(d + 8, d2);
       }
-      V1[r] = v1; V2[r] = v2; V3[r] = v3;
+      V1[r] = (float)v1; V2[r] = (float)v2; V3[r] = (float)v3;
     }
     __syncthreads();
     if (a.Oc) for (int nl = tid; nl < NT; nl += T) {
@@ -695,7 +707,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
     }
   }
   const int blk = b * a.J + blockIdx.x;
-  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = at_acc; a.pa_s[(int64_t)blk * C + tid] = as_acc; }
+  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = (float)at_acc; a.pa_s[(int64_t)blk * C + tid] = (float)as_acc; }
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
   for (int t = 0; t < 12; ++t) {
@@ -715,7 +727,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
 
 // ---------------------------------------------------------------------------------------
 struct BwdLayout {
-  int NT, T, J, nblk, nwblk, nbias, NT4, J4, nblk4, ntile4, nfin;
+  int NT, T, RBT, S, J, nblk, nwblk, nbias, NT4, J4, nblk4, ntile4, nfin;
   int64_t WGT;  // floats of weight-gradient partial per thread block
   int64_t off_job[NJOBS];
   int64_t o_G, o_wg, o_bias, o_ln, o_dMc, o_dPt, o_delta, o_dSnz, o_dqd, o_dqs, o_dK, o_dqc, o_caw, o_Wc, o_Wg,
@@ -723,15 +735,22 @@ struct BwdLayout {
   WJob jobs[NJOBS];
 };
 
+// blocks per sample so that the grid is about two full waves of `slots` resident thread blocks
+static int pick_J(int B, int ntile, int slots) {
+  int J = (2 * slots) / B;
+  if (J < 1) J = 1;
+  return J > ntile ? ntile : J;
+}
+
 static int bwd_layout(Plan& p, BwdLayout& L) {
   // weight-gradient jobs as lists of 4x4 blocks
-  int start = 0;
-  int64_t woff = 0;
   for (int q = 0; q < NJOBS; ++q) { L.jobs[q] = WJob{0, 0, 1, 1, 1, nullptr, 0}; L.off_job[q] = 0; }
+  int64_t woff = 0;
+  int nw = 0;
   auto add = [&](int q, int Oa, int Kb, bool in_wg) {
     WJob& jb = L.jobs[q];
-    jb.Oa = Oa; jb.Kb = Kb; jb.nkb = (Kb + 3) / 4; jb.nblk = ((Oa + 3) / 4) * jb.nkb; jb.start = start;
-    start += jb.nblk;
+    jb.Oa = Oa; jb.Kb = Kb; jb.nkb = (Kb + 3) / 4; jb.nblk = ((Oa + 3) / 4) * jb.nkb;
+    nw += jb.nblk;
     if (in_wg) { L.off_job[q] = woff; woff += rup4l((int64_t)Oa * Kb); }
   };
   if (p.flags & MSGAT_F_RES) add(JOB_RES, p.O, p.C, true);
@@ -742,35 +761,47 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
     add(JOB_CONV + 2 * i, p.Ot, K, true);
     add(JOB_CONV + 2 * i + 1, p.Ot, K, true);
   }
-  L.nwblk = start;
+  L.nwblk = nw;
   L.WGT = woff;
   L.nbias = p.O + (p.n_conv > 1 ? (p.n_conv - 1) * p.Ot : 0);
-  int T = ((start + RB - 1) / RB + 31) & ~31;
-  if (T < 160) T = 160;
+  int T, RBT;
+  if (nw <= 1024) { RBT = 2; T = nw > 512 ? 512 : 256; }
+  else if (nw <= 1536) { RBT = 4; T = 384; }
+  else return -30;
   if (T < ((L.nbias + 31) & ~31)) T = (L.nbias + 31) & ~31;
   if (T < ((p.C + 31) & ~31)) T = (p.C + 31) & ~31;
-  if (T > 384) return -30;
-  L.T = T;
-  int NT = 8;
-  while (NT > 1 && bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) NT >>= 1;
+  if (T > (RBT == 2 ? 512 : 384)) return -30;
+  L.T = T; L.RBT = RBT;
+  int S = nw ? (RBT * T) / nw : 1;
+  if (S < 1) S = 1;
+  if (S > 8) S = 8;
+  L.S = S;
+  int start = 0;
+  for (int q = 0; q < NJOBS; ++q) { L.jobs[q].start = start; start += L.jobs[q].nblk * S; }
+  int NT = 16;
+  while (NT > 4 && bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) NT >>= 1;
   if (bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) return -31;
   L.NT = NT; p.NTb = NT; p.ntile_b = (p.N + NT - 1) / NT;
-  int J = (2 * 148 + p.B - 1) / p.B;
-  if (J > p.ntile_b) J = p.ntile_b;
-  L.J = J; L.nblk = J * p.B;
+  {
+    int64_t smem = bwd_smem_floats(p, NT, T) * 4 + 1024;
+    int occ = (int)(227 * 1024 / smem);
+    if (occ > 2048 / T) occ = 2048 / T;
+    if (occ > 65536 / (T * 128)) occ = 65536 / (T * 128);
+    if (occ < 1) occ = 1;
+    L.J = pick_J(p.B, p.ntile_b, 148 * occ);
+  }
+  L.nblk = L.J * p.B;
   L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
-  int J4 = (4 * 148 + p.B - 1) / p.B;
-  if (J4 > L.ntile4) J4 = L.ntile4;
-  L.J4 = J4; L.nblk4 = J4 * p.B;
+  L.J4 = pick_J(p.B, L.ntile4, 148 * 4); L.nblk4 = L.J4 * p.B;
   L.nfin = (p.N + 127) / 128;
   int64_t o = 0;
   const int64_t BN = (int64_t)p.B * p.N;
   const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
   L.o_G = o; o += need_mask ? rup4l(BN * 12 * p.O) : 0;
-  L.o_wg = o; o += rup4l((int64_t)L.nblk * L.WGT);
+  L.o_wg = o; o += rup4l((int64_t)L.nblk * L.S * L.WGT);
   L.o_bias = o; o += rup4l((int64_t)L.nblk * L.nbias);
   L.o_ln = o; o += rup4l((int64_t)(L.nblk + L.nblk4) * 24);
-  L.o_dMc = o; o += rup4l((int64_t)L.nblk * p.Oc * p.C);
+  L.o_dMc = o; o += rup4l((int64_t)L.nblk * L.S * p.Oc * p.C);
   L.o_dPt = o; o += rup4l((int64_t)L.nblk * 144);
   L.o_delta = o; o += rup4l(BN);
   L.o_dSnz = o; o += rup4l((int64_t)p.B * p.nnz);
@@ -831,12 +862,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dx = dx;
     a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
     size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
-    switch (L.NT) {
-      case 8: MSGAT_LAUNCH(k_bwd_main<8>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
-      case 4: MSGAT_LAUNCH(k_bwd_main<4>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
-      case 2: MSGAT_LAUNCH(k_bwd_main<2>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
-      default: MSGAT_LAUNCH(k_bwd_main<1>, dim3(L.J, p.B), dim3(L.T), smem, stream, a); break;
+    a.S = L.S;
+#define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
+    if (L.RBT == 2) {
+      if (L.NT == 16) BWD_CASE(16, 2); else if (L.NT == 8) BWD_CASE(8, 2); else BWD_CASE(4, 2);
+    } else {
+      if (L.NT == 16) BWD_CASE(16, 4); else if (L.NT == 8) BWD_CASE(8, 4); else BWD_CASE(4, 4);
     }
+#undef BWD_CASE
   }
   if (p.Os) {
     launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
@@ -849,7 +882,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   }
   if (p.Oc || p.Ot) {
     BSmallArgs a;
-    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = L.J * L.S;
     a.dMc_part = scratch + L.o_dMc; a.dPt_part = scratch + L.o_dPt; a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
     a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w; a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
     a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
@@ -881,14 +914,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     const float* wg = scratch + L.o_wg;
     const float* bp = scratch + L.o_bias;
     if (p.flags & MSGAT_F_RES) {
-      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, L.nblk, L.WGT, 1, 0);
+      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, L.nblk * L.S, L.WGT, 1, 0);
       add(g->res_b, bp, p.O, L.nblk, L.nbias, 1, 0);
     }
-    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, L.nblk, L.WGT, 1, 0);
+    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, L.nblk * L.S, L.WGT, 1, 0);
     for (int i = 0; i < p.n_conv; ++i) {
       const int K = i == 0 ? p.C : p.Ot;
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, L.nblk, L.WGT, 2, 0);
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, L.nblk, L.WGT, 2, 1);
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, L.nblk * L.S, L.WGT, 2, 0);
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, L.nblk * L.S, L.WGT, 2, 1);
       add(g->conv_b[i], i + 1 == p.n_conv ? bp + p.Oc : bp + p.O + i * p.Ot, p.Ot, L.nblk, L.nbias, 1, 0);
     }
     if (p.flags & MSGAT_F_LN) {

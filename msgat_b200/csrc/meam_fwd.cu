@@ -18,7 +18,8 @@ struct PrepArgs {
   const float* x; int64_t x_sb, x_sc;
   int C, N, Oc, Ot, Os, Cz, s_pre, do_ln, ntile;
   const float *ln_w, *ln_b, *sa_alpha, *ta_alpha, *ca_alpha, *Wt1, *Wt2, *sa_W;
-  float *qs, *qt, *Z, *pqc, *pK;
+  float *qs, *qt, *Z;
+  double *pqc, *pK;  // per-tile partial sums kept in fp64: they feed softmaxes whose scores reach O(100)
 };
 
 template <int NT>
@@ -71,25 +72,25 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_prep(PrepArgs a) {
   }
   // per-tile partial of the channel query q_c[c,t] = sum_n alpha[n] h[c,n,t]  (attention.py:92)
   if (a.Oc) {
-    float* dst = a.pqc + ((int64_t)b * a.ntile + tile) * a.C * 12;
+    double* dst = a.pqc + ((int64_t)b * a.ntile + tile) * a.C * 12;
     for (int i = threadIdx.x; i < a.C * 12; i += blockDim.x) {
       const int c = i / 12, t = i - c * 12;
-      float s = 0.f;
+      double s = 0.0;
       for (int nl = 0; nl < NT; ++nl)
-        if (n0 + nl < a.N) s = fmaf(__ldg(a.ca_alpha + n0 + nl), H[c * PS + nl * 12 + t], s);
+        if (n0 + nl < a.N) s += (double)__ldg(a.ca_alpha + n0 + nl) * (double)H[c * PS + nl * 12 + t];
       dst[i] = s;
     }
   }
   __syncthreads();
   // per-tile partial of the temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T  (attention.py:65)
   if (a.Ot) {
-    float* dst = a.pK + ((int64_t)b * a.ntile + tile) * 240;
+    double* dst = a.pK + ((int64_t)b * a.ntile + tile) * 240;
     for (int i = threadIdx.x; i < 240; i += blockDim.x) {
       const int t = i / 20, r = i - t * 20;
       const float* W = (r < 10) ? a.Wt1 + (int64_t)r * a.N : a.Wt2 + (int64_t)(r - 10) * a.N;
-      float s = 0.f;
+      double s = 0.0;
       for (int nl = 0; nl < NT; ++nl)
-        if (n0 + nl < a.N) s = fmaf(__ldg(W + n0 + nl), QT[nl * 12 + t], s);
+        if (n0 + nl < a.N) s += (double)__ldg(W + n0 + nl) * (double)QT[nl * 12 + t];
       dst[i] = s;
     }
   }
@@ -98,32 +99,36 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_prep(PrepArgs a) {
 // ---------------------------------------------------------------------------------------
 struct SmallArgs {
   int C, Oc, Ot, cmix, ntile;
-  const float *pqc, *pK, *Wc, *ca_w;
+  const double *pqc, *pK;
+  const float *Wc, *ca_w;
   float *qc, *Pc, *Mc, *K, *Pt;
 };
 
+// All of this is O(C^2) work per sample; it runs in fp64 because the scores of the channel and
+// temporal softmaxes are sums over all N nodes and reach O(100) with trained weights, where an
+// fp32 score carries 1e-5 of relative error straight into the attention matrix.
 MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.x;
-  float* qc = reinterpret_cast<float*>(smem_raw);  // [C][12]
-  float* tmp = qc + C * 12;                        // [C][12]
-  float* S = tmp + C * 12;                         // [C][C]
-  float* K = S + C * C;                            // [12][20]
-  float* St = K + 240;                             // [144]
+  double* qc = reinterpret_cast<double*>(smem_raw);  // [C][12]
+  double* tmp = qc + C * 12;                         // [C][12]
+  double* S = tmp + C * 12;                          // [C][C]
+  double* K = S + C * C;                             // [12][20]
+  double* St = K + 240;                              // [144]
   if (a.Oc) {
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
-      float s = 0.f;
+      double s = 0.0;
       for (int tl = 0; tl < a.ntile; ++tl) s += a.pqc[((int64_t)b * a.ntile + tl) * C * 12 + i];
       qc[i] = s;
-      a.qc[(int64_t)b * C * 12 + i] = s;
+      a.qc[(int64_t)b * C * 12 + i] = (float)s;
     }
   }
   if (a.Ot) {
     for (int i = threadIdx.x; i < 240; i += blockDim.x) {
-      float s = 0.f;
+      double s = 0.0;
       for (int tl = 0; tl < a.ntile; ++tl) s += a.pK[((int64_t)b * a.ntile + tl) * 240 + i];
       K[i] = s;
-      a.K[(int64_t)b * 240 + i] = s;
+      a.K[(int64_t)b * 240 + i] = (float)s;
     }
   }
   __syncthreads();
@@ -131,58 +136,58 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
     // S = (qc Wc) qc^T, softmax over the last axis (attention.py:93)
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
       const int c = i / 12, t2 = i - c * 12;
-      float s = 0.f;
-      for (int t = 0; t < 12; ++t) s = fmaf(qc[c * 12 + t], __ldg(a.Wc + t * 12 + t2), s);
+      double s = 0.0;
+      for (int t = 0; t < 12; ++t) s += qc[c * 12 + t] * (double)__ldg(a.Wc + t * 12 + t2);
       tmp[i] = s;
     }
     __syncthreads();
     for (int i = threadIdx.x; i < C * C; i += blockDim.x) {
       const int c = i / C, j = i - c * C;
-      float s = 0.f;
-      for (int t = 0; t < 12; ++t) s = fmaf(tmp[c * 12 + t], qc[j * 12 + t], s);
+      double s = 0.0;
+      for (int t = 0; t < 12; ++t) s += tmp[c * 12 + t] * qc[j * 12 + t];
       S[i] = s;
     }
     __syncthreads();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      float m = -INFINITY;
-      for (int j = 0; j < C; ++j) m = fmaxf(m, S[c * C + j]);
-      float l = 0.f;
-      for (int j = 0; j < C; ++j) { float e = expf(S[c * C + j] - m); S[c * C + j] = e; l += e; }
-      float inv = 1.0f / l;
+      double m = -INFINITY;
+      for (int j = 0; j < C; ++j) m = fmax(m, S[c * C + j]);
+      double l = 0.0;
+      for (int j = 0; j < C; ++j) { double e = exp(S[c * C + j] - m); S[c * C + j] = e; l += e; }
+      const double inv = 1.0 / l;
       for (int j = 0; j < C; ++j) S[c * C + j] *= inv;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < C * C; i += blockDim.x) a.Pc[(int64_t)b * C * C + i] = S[i];
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) a.Pc[(int64_t)b * C * C + i] = (float)S[i];
     // fold the 1x1 conv of CACN (msgat.py:94) into the attention: Mc = W1 Pc
     for (int i = threadIdx.x; i < a.Oc * C; i += blockDim.x) {
       const int o = i / C, j = i - o * C;
-      float s;
+      double s;
       if (a.cmix) {
-        s = 0.f;
-        for (int c = 0; c < C; ++c) s = fmaf(__ldg(a.ca_w + o * C + c), S[c * C + j], s);
+        s = 0.0;
+        for (int c = 0; c < C; ++c) s += (double)__ldg(a.ca_w + o * C + c) * S[c * C + j];
       } else {
         s = S[o * C + j];
       }
-      a.Mc[(int64_t)b * a.Oc * C + i] = s;
+      a.Mc[(int64_t)b * a.Oc * C + i] = (float)s;
     }
   }
   if (a.Ot) {
     // temporal scores K1 K2^T, softmax over the last axis (attention.py:65)
     for (int i = threadIdx.x; i < 144; i += blockDim.x) {
       const int t = i / 12, j = i - t * 12;
-      float s = 0.f;
-      for (int r = 0; r < 10; ++r) s = fmaf(K[t * 20 + r], K[j * 20 + 10 + r], s);
+      double s = 0.0;
+      for (int r = 0; r < 10; ++r) s += K[t * 20 + r] * K[j * 20 + 10 + r];
       St[i] = s;
     }
     __syncthreads();
     if (threadIdx.x < 12) {
       const int t = threadIdx.x;
-      float m = -INFINITY;
-      for (int j = 0; j < 12; ++j) m = fmaxf(m, St[t * 12 + j]);
-      float e[12], l = 0.f;
-      for (int j = 0; j < 12; ++j) { e[j] = expf(St[t * 12 + j] - m); l += e[j]; }
-      float inv = 1.0f / l;
-      for (int j = 0; j < 12; ++j) a.Pt[(int64_t)b * 144 + t * 12 + j] = e[j] * inv;
+      double m = -INFINITY;
+      for (int j = 0; j < 12; ++j) m = fmax(m, St[t * 12 + j]);
+      double e[12], l = 0.0;
+      for (int j = 0; j < 12; ++j) { e[j] = exp(St[t * 12 + j] - m); l += e[j]; }
+      const double inv = 1.0 / l;
+      for (int j = 0; j < 12; ++j) a.Pt[(int64_t)b * 144 + t * 12 + j] = (float)(e[j] * inv);
     }
   }
 }
@@ -370,7 +375,7 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.sa_alpha = prm->sa_alpha; a.ta_alpha = prm->ta_alpha;
     a.ca_alpha = prm->ca_alpha; a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.sa_W = prm->sa_W;
     a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
-    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
+    a.pqc = reinterpret_cast<double*>(scratch + p.o_pqc); a.pK = reinterpret_cast<double*>(scratch + p.o_pK);
     constexpr int NT = 16;
     size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
     MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B), dim3(256), smem, stream, a);
@@ -378,9 +383,10 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
   if (p.Oc || p.Ot) {
     SmallArgs a;
     a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = p.ntile_p;
-    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK; a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w;
+    a.pqc = reinterpret_cast<const double*>(scratch + p.o_pqc); a.pK = reinterpret_cast<const double*>(scratch + p.o_pK);
+    a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w;
     a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
-    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 4;
+    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 8;
     MSGAT_LAUNCH(k_small, dim3(p.B), dim3(256), smem, stream, a);
   }
   if (p.Os) launch_sstats(p, prm, adj, saved, stream);
@@ -395,17 +401,22 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
     a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr; a.nnz = p.nnz;
     a.out = out;
-    int J = (2 * 148 + p.B - 1) / p.B;
+    const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
+    size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
+    const int nthr = pick_threads(chunks * p.NTa * 3, 512);
+    int occ = (int)(227 * 1024 / (smem + 1024));
+    if (occ > 2048 / nthr) occ = 2048 / nthr;
+    if (occ > 65536 / (nthr * 128)) occ = 65536 / (nthr * 128);
+    if (occ < 1) occ = 1;
+    int J = (2 * 148 * occ) / p.B;  // about two full waves of resident blocks
     if (J > p.ntile_a) J = p.ntile_a;
     if (J < 1) J = 1;
     a.J = J;
-    const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
-    size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
     switch (p.NTa) {
-      case 16: MSGAT_LAUNCH(k_apply<16>, dim3(J, p.B), dim3(pick_threads(chunks * 48, 512)), smem, stream, a); break;
-      case 8: MSGAT_LAUNCH(k_apply<8>, dim3(J, p.B), dim3(pick_threads(chunks * 24, 512)), smem, stream, a); break;
-      case 4: MSGAT_LAUNCH(k_apply<4>, dim3(J, p.B), dim3(pick_threads(chunks * 12, 512)), smem, stream, a); break;
-      default: MSGAT_LAUNCH(k_apply<2>, dim3(J, p.B), dim3(pick_threads(chunks * 6, 512)), smem, stream, a); break;
+      case 16: MSGAT_LAUNCH(k_apply<16>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
+      case 8: MSGAT_LAUNCH(k_apply<8>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
+      case 4: MSGAT_LAUNCH(k_apply<4>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
+      default: MSGAT_LAUNCH(k_apply<2>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
     }
   }
   return 0;

@@ -81,8 +81,8 @@ static inline int make_plan(const msgat_meam_desc* d, int nnz, Plan* p) {
   o = (o + 3) & ~(int64_t)3;
   p->saved_total = o;
   int64_t s = 0;
-  p->o_pqc = s; s += rup4l((int64_t)d->B * p->ntile_p * d->C * 12);
-  p->o_pK = s; s += rup4l((int64_t)d->B * p->ntile_p * 240);
+  p->o_pqc = s; s += rup4l(2 * (int64_t)d->B * p->ntile_p * d->C * 12);  // fp64 partials
+  p->o_pK = s; s += rup4l(2 * (int64_t)d->B * p->ntile_p * 240);
   p->fwd_scratch = s;
   return 0;
 }

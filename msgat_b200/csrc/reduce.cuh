@@ -13,8 +13,8 @@ MSGAT_KERNEL k_reduce(ReduceArgs a) {
   while (idx >= a.starts[q + 1]) ++q;
   const RJob& jb = a.j[q];
   const int e = idx - a.starts[q];
-  float s = 0.f;
-  for (int p = 0; p < jb.nparts; ++p) s += jb.src[(int64_t)p * jb.pstride + e];
-  jb.dst[(int64_t)e * jb.dmul + jb.doff] = s;
+  double s = 0.0;  // partials of cancellation-heavy scalars (alpha, Wc ...) are summed in fp64
+  for (int p = 0; p < jb.nparts; ++p) s += (double)jb.src[(int64_t)p * jb.pstride + e];
+  jb.dst[(int64_t)e * jb.dmul + jb.doff] = (float)s;
 }
 
