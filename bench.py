@@ -118,7 +118,7 @@ def cpu_reference_arm(args, shape, steps, warmup):
         opt.zero_grad()
         loss.backward()
         opt.step()
-        float(loss)
+        float(loss.detach())
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     dt = sum(times) / len(times)
@@ -131,7 +131,7 @@ def algorithmic_bytes(kernel: str, B: int, N: int):
     """HBM bytes one launch of `kernel` must move: activations read
     and written once, fp32, nothing else spilled.  kernel = "name<..>@C<in>O<out>"."""
     name, _, tag = kernel.partition("@")
-    name = name.split("<")[0]
+    name = name.strip("()").split("<")[0]
     try:
         C = int(tag[1:tag.index("O")]); O = int(tag[tag.index("O") + 1:])
     except ValueError:

@@ -225,7 +225,7 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   const int nparts = a.J * d->B;
   auto add = [&](float* dst, const float* src, int n) {
     if (!dst) return;
-    r.j[nj] = RJob{dst, src, n, nparts, 1, 0, (int64_t)a.pstride};
+    r.j[nj] = RJob{dst, src, n, nparts, 1, 0, (int64_t)a.pstride, 0};
     r.starts[nj] = tot; tot += n; ++nj;
   };
   add(d_fc_w, scratch, nW);
@@ -233,7 +233,7 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   add(d_ln_w, scratch + nW + d->Tout, 12);
   add(d_ln_b, scratch + nW + d->Tout + 12, 12);
   r.starts[nj] = tot; r.njobs = nj;
-  if (tot > 0) MSGAT_LAUNCH(k_reduce, dim3((tot + 127) / 128), dim3(128), 0, stream, r);
+  if (tot > 0) LAUNCH_REDUCE(tot, stream, r);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { msgat_set_error("head_backward: %s", cudaGetErrorString(e)); return -100; }
   return 0;

@@ -40,7 +40,8 @@ struct BwdArgs {
   const float *Mc, *Pt, *Z, *pw;
   const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
   WJob jobs[NJOBS];
-  float *bias_part, *ln_part, *dPt_part, *delta, *dSnz, *dx;
+  float *bias_part, *ln_part, *delta, *dSnz, *dx;
+  double* dPt_part;
   int nbias, arena_floats, S;
 };
 
@@ -116,7 +117,7 @@ static int bwd_arena_floats(const Plan& p, int nthreads) {
     v = 2 * p.Ot * rup4(K); a = v > a ? v : a;                // untransposed taps (conv^T)
   }
   if (p.Os && (p.flags & MSGAT_F_SMIX)) { v = p.Os * rup4(p.C); a = v > a ? v : a; }
-  if (p.Ot) { v = (nthreads / 9) * 144; a = v > a ? v : a; }
+  if (p.Ot) { v = (nthreads / 9) * 288; a = v > a ? v : a; }  // fp64 dPt group partials
   v = (nthreads / 32) * 24; a = v > a ? v : a;
   return rup4(a);
 }
@@ -275,14 +276,14 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             o16[12] += g.w * h.x; o16[13] += g.w * h.y; o16[14] += g.w * h.z; o16[15] += g.w * h.w;
           }
           for (int i = 0; i < 4; ++i)
-            for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
+            for (int j = 0; j < 4; ++j) reinterpret_cast<double*>(AR)[grp * 144 + (tb + i) * 12 + ib + j] = o16[i * 4 + j];
         }
         // dh[c,n,i] += sum_t Pt[t][i] dOt[c,n,t]
         tile_temporal(DH, dOt, PS, C, NT, Pt, true, true);
         __syncthreads();
         if (tid < 144) {
           double s = 0.0;
-          for (int g2 = 0; g2 < ngr; ++g2) s += (double)AR[g2 * 144 + tid];
+          for (int g2 = 0; g2 < ngr; ++g2) s += reinterpret_cast<const double*>(AR)[g2 * 144 + tid];
           pt_acc += s;
         }
         __syncthreads();
@@ -398,7 +399,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   __syncthreads();
   wgrad_flush<RBT>(acc, a.jobs, blk, a.S);
   if (tid < a.nbias) a.bias_part[(int64_t)blk * a.nbias + tid] = bacc;
-  if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = (float)pt_acc;
+  if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
   {
     const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
     for (int t = 0; t < 12; ++t) {
@@ -421,7 +422,8 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
 //   dWg    += q[n,:]^T dU[n,:]
 struct SFinArgs {
   int N, nnz;
-  const float *qs, *Wg, *E, *delta, *dSnz, *dq_dense;
+  const float *qs, *Wg, *delta, *dSnz, *dq_dense;
+  const double* E;
   const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
   float *dqs, *Wg_part;
 };
@@ -435,16 +437,17 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
   const float* ds = a.dSnz + (int64_t)b * a.nnz;
   for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = a.Wg[i];
   __syncthreads();
-  float q[12], dU[12], dq[12];
-  for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.f; dq[t] = 0.f; }
+  float q[12], dq[12];
+  double dU[12];  // sum_e dSnz q_i and delta E nearly cancel
+  for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.0; dq[t] = 0.f; }
   if (n < a.N) {
     const int64_t g = (int64_t)b * a.N + n;
-    const float dl = a.delta[g];
+    const double dl = (double)a.delta[g];
     for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * a.E[g * 12 + t]; dq[t] = a.dq_dense[g * 12 + t]; }
     for (int e = a.row_ptr[n]; e < a.row_ptr[n + 1]; ++e) {
-      const float w = ds[e];
+      const double w = (double)ds[e];
       const float* qi = qb + (int64_t)a.col_idx[e] * 12;
-      for (int t = 0; t < 12; ++t) dU[t] = fmaf(w, qi[t], dU[t]);
+      for (int t = 0; t < 12; ++t) dU[t] = fma(w, (double)qi[t], dU[t]);
     }
     for (int k = a.csc_ptr[n]; k < a.csc_ptr[n + 1]; ++k) {
       const float w = ds[a.csc_eid[k]];
@@ -456,12 +459,12 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
       }
     }
     for (int t = 0; t < 12; ++t) {
-      float s = 0.f;
-      for (int t2 = 0; t2 < 12; ++t2) s = fmaf(dU[t2], WG[t * 12 + t2], s);
-      a.dqs[g * 12 + t] = dq[t] + s;
+      double s = 0.0;
+      for (int t2 = 0; t2 < 12; ++t2) s = fma(dU[t2], (double)WG[t * 12 + t2], s);
+      a.dqs[g * 12 + t] = (float)((double)dq[t] + s);
     }
   }
-  for (int t = 0; t < 12; ++t) { QD[threadIdx.x * 24 + t] = q[t]; QD[threadIdx.x * 24 + 12 + t] = dU[t]; }
+  for (int t = 0; t < 12; ++t) { QD[threadIdx.x * 24 + t] = q[t]; QD[threadIdx.x * 24 + 12 + t] = (float)dU[t]; }
   __syncthreads();
   for (int i = threadIdx.x; i < 144; i += blockDim.x) {
     const int t = i / 12, t2 = i - t * 12;
@@ -474,7 +477,8 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
 // ---------------------------------------------------------------------------------------
 struct BSmallArgs {
   int C, Oc, Ot, cmix, J, Jm;
-  const float *dMc_part, *dPt_part, *Pc, *qc, *Wc, *ca_w, *Pt, *K;
+  const float *dMc_part, *Pc, *qc, *Wc, *ca_w, *Pt, *K;
+  const double* dPt_part;
   float *caw_part, *Wc_part, *dqc, *dK;
 };
 
@@ -597,7 +601,8 @@ struct FixArgs {
   const float* x; int64_t x_sb, x_sc;
   int C, N, Oc, Ot, Os, flags, ntile, J;
   const float *ln_w, *ln_b, *ca_alpha, *ta_alpha, *sa_alpha, *Wt1, *Wt2, *dqc, *dK, *dqs;
-  float *dx, *pa_n, *pa_t, *pa_s, *ln_part;
+  float *dx, *pa_n, *ln_part;
+  double *pa_t, *pa_s;
 };
 
 template <int NT>
@@ -611,8 +616,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   float* DQT = sp; sp += P;
   float* DQS = sp; sp += P;
   float* V1 = sp; sp += C * NT;
-  float* V2 = sp; sp += C * NT;
-  float* V3 = sp; sp += C * NT;
+  double* V2 = reinterpret_cast<double*>(sp); sp += 2 * C * NT;  // offset so far is even: 8-byte aligned
+  double* V3 = reinterpret_cast<double*>(sp); sp += 2 * C * NT;
   float* DK = sp; sp += 240;
   float* LW = sp; sp += 24;
   float* RED = sp;  // [T/32][24]
@@ -690,7 +695,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         d2.x += out[8]; d2.y += out[9]; d2.z += out[10]; d2.w += out[11];
         st4(d, d0); st4(d + 4, d1); st4(d + 8, d2);
       }
-      V1[r] = (float)v1; V2[r] = (float)v2; V3[r] = (float)v3;
+      V1[r] = (float)v1; V2[r] = v2; V3[r] = v3;
     }
     __syncthreads();
     if (a.Oc) for (int nl = tid; nl < NT; nl += T) {
@@ -701,13 +706,13 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
       }
     }
     for (int c = tid; c < C; c += T) {  // a thread owns channel c for the whole kernel (needs T >= C)
-      float s2 = 0.f, s3 = 0.f;
+      double s2 = 0.0, s3 = 0.0;
       for (int nl = 0; nl < NT; ++nl) { s2 += V2[c * NT + nl]; s3 += V3[c * NT + nl]; }
       at_acc += s2; as_acc += s3;
     }
   }
   const int blk = b * a.J + blockIdx.x;
-  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = (float)at_acc; a.pa_s[(int64_t)blk * C + tid] = (float)as_acc; }
+  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = at_acc; a.pa_s[(int64_t)blk * C + tid] = as_acc; }
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
   for (int t = 0; t < 12; ++t) {
@@ -802,7 +807,7 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   L.o_bias = o; o += rup4l((int64_t)L.nblk * L.nbias);
   L.o_ln = o; o += rup4l((int64_t)(L.nblk + L.nblk4) * 24);
   L.o_dMc = o; o += rup4l((int64_t)L.nblk * L.S * p.Oc * p.C);
-  L.o_dPt = o; o += rup4l((int64_t)L.nblk * 144);
+  L.o_dPt = o; o += rup4l(2 * (int64_t)L.nblk * 144);  // fp64
   L.o_delta = o; o += rup4l(BN);
   L.o_dSnz = o; o += rup4l((int64_t)p.B * p.nnz);
   L.o_dqd = o; o += rup4l(BN * 12);
@@ -812,8 +817,8 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   L.o_caw = o; o += rup4l((int64_t)p.B * p.Oc * p.C);
   L.o_Wc = o; o += rup4l((int64_t)p.B * 144);
   L.o_Wg = o; o += rup4l((int64_t)p.B * L.nfin * 144);
-  L.o_pat = o; o += rup4l((int64_t)L.nblk4 * p.C);
-  L.o_pas = o; o += rup4l((int64_t)L.nblk4 * p.C);
+  L.o_pat = o; o += rup4l(2 * (int64_t)L.nblk4 * p.C);  // fp64 partials of the alpha gradients
+  L.o_pas = o; o += rup4l(2 * (int64_t)L.nblk4 * p.C);
   L.o_pan = o; o += rup4l(BN);
   L.total = o;
   return 0;
@@ -858,7 +863,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
       if (q == JOB_MC) { a.jobs[q].out = scratch + L.o_dMc; a.jobs[q].blk_stride = (int64_t)p.Oc * p.C; }
       else { a.jobs[q].out = scratch + L.o_wg + L.off_job[q]; a.jobs[q].blk_stride = L.WGT; }
     }
-    a.bias_part = scratch + L.o_bias; a.ln_part = scratch + L.o_ln; a.dPt_part = scratch + L.o_dPt;
+    a.bias_part = scratch + L.o_bias; a.ln_part = scratch + L.o_ln; a.dPt_part = reinterpret_cast<double*>(scratch + L.o_dPt);
     a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dx = dx;
     a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
     size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
@@ -874,7 +879,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   if (p.Os) {
     launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
     SFinArgs a;
-    a.N = p.N; a.nnz = p.nnz; a.qs = saved + p.o_qs; a.Wg = prm->sa_Wg; a.E = saved + p.o_E;
+    a.N = p.N; a.nnz = p.nnz; a.qs = saved + p.o_qs; a.Wg = prm->sa_Wg; a.E = reinterpret_cast<const double*>(saved + p.o_E);
     a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dq_dense = scratch + L.o_dqd;
     a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
     a.dqs = scratch + L.o_dqs; a.Wg_part = scratch + L.o_Wg;
@@ -883,7 +888,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   if (p.Oc || p.Ot) {
     BSmallArgs a;
     a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = L.J * L.S;
-    a.dMc_part = scratch + L.o_dMc; a.dPt_part = scratch + L.o_dPt; a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
+    a.dMc_part = scratch + L.o_dMc; a.dPt_part = reinterpret_cast<const double*>(scratch + L.o_dPt); a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
     a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w; a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
     a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
     size_t smem = ((size_t)p.C * 48 + 2 * (size_t)p.C * p.C + (size_t)p.Oc * p.C + 528) * 4;
@@ -898,17 +903,17 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.flags = p.flags; a.ntile = L.ntile4; a.J = L.J4;
     a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.ca_alpha = prm->ca_alpha; a.ta_alpha = prm->ta_alpha; a.sa_alpha = prm->sa_alpha;
     a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK; a.dqs = scratch + L.o_dqs;
-    a.dx = dx; a.pa_n = scratch + L.o_pan; a.pa_t = scratch + L.o_pat; a.pa_s = scratch + L.o_pas;
+    a.dx = dx; a.pa_n = scratch + L.o_pan; a.pa_t = reinterpret_cast<double*>(scratch + L.o_pat); a.pa_s = reinterpret_cast<double*>(scratch + L.o_pas);
     a.ln_part = scratch + L.o_ln + (int64_t)L.nblk * 24;
-    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 3 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
+    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 5 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
     MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B), dim3(256), smem, stream, a);
   }
   {
     ReduceArgs r;
     int nj = 0, tot = 0;
-    auto add = [&](float* dst, const float* src, int n, int nparts, int64_t pstride, int dmul, int doff) {
+    auto add = [&](float* dst, const float* src, int n, int nparts, int64_t pstride, int dmul, int doff, int f64 = 0) {
       if (!dst || n <= 0 || nj >= MAX_RJOBS) return;
-      r.j[nj] = RJob{dst, src, n, nparts, dmul, doff, pstride};
+      r.j[nj] = RJob{dst, src, n, nparts, dmul, doff, pstride, f64};
       r.starts[nj] = tot; tot += n; ++nj;
     };
     const float* wg = scratch + L.o_wg;
@@ -936,13 +941,13 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
       add(g->ca_Wc, scratch + L.o_Wc, 144, p.B, 144, 1, 0);
       add(g->ca_alpha, scratch + L.o_pan, p.N, p.B, p.N, 1, 0);
     }
-    if (p.Ot) add(g->ta_alpha, scratch + L.o_pat, p.C, L.nblk4, p.C, 1, 0);
+    if (p.Ot) add(g->ta_alpha, scratch + L.o_pat, p.C, L.nblk4, p.C, 1, 0, 1);
     if (p.Os) {
-      add(g->sa_alpha, scratch + L.o_pas, p.C, L.nblk4, p.C, 1, 0);
+      add(g->sa_alpha, scratch + L.o_pas, p.C, L.nblk4, p.C, 1, 0, 1);
       add(g->sa_Wg, scratch + L.o_Wg, 144, p.B * L.nfin, 144, 1, 0);
     }
     r.starts[nj] = tot; r.njobs = nj;
-    if (tot > 0) MSGAT_LAUNCH(k_reduce, dim3((tot + 127) / 128), dim3(128), 0, stream, r);
+    if (tot > 0) LAUNCH_REDUCE(tot, stream, r);
   }
   return 0;
 }

@@ -184,6 +184,11 @@ static inline float __shfl_xor_sync(unsigned, float v, int m) {
   uint64_t r = emu::shfl_idx(u, (emu::cur()->lin & 31) ^ m);
   u = (uint32_t)r; memcpy(&v, &u, 4); return v;
 }
+static inline double __shfl_xor_sync(unsigned, double v, int m) {
+  uint64_t u; memcpy(&u, &v, 8);
+  uint64_t r = emu::shfl_idx(u, (emu::cur()->lin & 31) ^ m);
+  memcpy(&v, &r, 8); return v;
+}
 static inline float __shfl_sync(unsigned, float v, int src) {
   uint32_t u; memcpy(&u, &v, 4);
   uint64_t r = emu::shfl_idx(u, src);
