@@ -143,6 +143,11 @@ int msgat_head_backward(const msgat_head_desc *d, const float *x, const float *l
                         float *dx, float *d_ln_w, float *d_ln_b, float *d_fc_w, float *d_fc_b,
                         float *d_gate, float *scratch, void *stream);
 
+/* Self-test of the tcgen05 (kind::tf32) building block of the tensor-core path; see
+ * csrc/tc_probe.cu.  mode 0: D[256,N] = A[K,256]^T B[K,N]; mode 1: D[128,N] = A[Ra,P] B[Rb,P]^T. */
+int msgat_tc_probe(int mode, const float *A, const float *B, float *D, int K, int N, int Ra, int Rb, int P,
+                   void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -56,7 +56,7 @@ class HeadDesc(C.Structure):
 EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_launch_count", "msgat_profile",
            "msgat_profile_report", "msgat_adj_count", "msgat_adj_fill",
            "msgat_meam_sizes", "msgat_meam_forward", "msgat_meam_backward", "msgat_head_forward",
-           "msgat_head_scratch_floats", "msgat_head_backward"]
+           "msgat_head_scratch_floats", "msgat_head_backward", "msgat_tc_probe"]
 
 _LIB = None
 _DEBUG_BACKEND = False  # set only by tests/emu (kernel-logic debugging on the GPU-less build box)

@@ -148,6 +148,14 @@ int msgat_profile_report(char* buf, long long cap) {
 #endif
 }
 
+#ifdef MSGAT_EMU
+/* the host-fiber debug build has no tensor cores: tc_*.cu is not part of it */
+int msgat_tc_probe(int, const float*, const float*, float*, int, int, int, int, int, void*) {
+  msgat_set_error("tcgen05 kernels need the sm_100a build");
+  return -200;
+}
+#endif
+
 int msgat_device_check(void) {
 #ifdef MSGAT_EMU
   return 0;

@@ -16,6 +16,7 @@
 //                the per-sample reductions are complete, pushed through the LayerNorm backward
 //                (linear in its incoming gradient) and added to dx; alpha gradients
 //   k_reduce     sums every partial into the caller's gradient tensors
+#include <stdlib.h>
 #include "kernels.h"
 #include "tile_ops.cuh"
 
@@ -43,6 +44,7 @@ struct BwdArgs {
   float *bias_part, *ln_part, *delta, *dSnz, *dx;
   double* dPt_part;
   int nbias, arena_floats, S;
+  int skip_wgrad;  // weight gradients come from the tensor-core kernel (tc_wgrad.cu) instead
 };
 
 // acc[r] (+)= A[oa..oa+3][p] . B[kb..kb+3][p] over the tile's positions, for the blocks of job jb
@@ -117,7 +119,7 @@ static int bwd_arena_floats(const Plan& p, int nthreads) {
     v = 2 * p.Ot * rup4(K); a = v > a ? v : a;                // untransposed taps (conv^T)
   }
   if (p.Os && (p.flags & MSGAT_F_SMIX)) { v = p.Os * rup4(p.C); a = v > a ? v : a; }
-  if (p.Ot) { v = (nthreads / 9) * 288; a = v > a ? v : a; }  // fp64 dPt group partials
+  if (p.Ot) { v = (nthreads / 9) * 144; a = v > a ? v : a; }
   v = (nthreads / 32) * 24; a = v > a ? v : a;
   return rup4(a);
 }
@@ -188,7 +190,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
     }
     __syncthreads();
     // ---- S1: residual weight gradient (msgat.py:116,131) and the row sums behind three biases
-    if (has_res) wgrad_accum<RBT>(acc, a.jobs[JOB_RES], G, OT, PS, PQ, -1, a.S);
+    if (has_res && !a.skip_wgrad) wgrad_accum<RBT>(acc, a.jobs[JOB_RES], G, OT, PS, PQ, -1, a.S);
     if (tid < a.O) {
       const float* q = G + tid * PS;
       float s = 0.f;
@@ -204,7 +206,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       if (a.Oc) mix_item(d, G, PS, a.Oc, AR, RC, c0, nl, t0);
       for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
     }
-    if (a.Oc) wgrad_accum<RBT>(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1, a.S);
+    if (a.Oc && !a.skip_wgrad) wgrad_accum<RBT>(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1, a.S);
     __syncthreads();
     // ---- S3: temporal branch
     if (a.Ot) {
@@ -234,8 +236,10 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       for (int i = a.n_conv - 1; i >= 0; --i) {
         const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
         const float* in = i == 0 ? OT : Y[i - 1];
-        wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i], a.S);
-        wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1, a.S);
+        if (!a.skip_wgrad) {
+          wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i], a.S);
+          wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1, a.S);
+        }
         if (i + 1 < a.n_conv) {
           const int row = tid - a.O - i * a.Ot;
           if (row >= 0 && row < a.Ot) {
@@ -276,14 +280,14 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             o16[12] += g.w * h.x; o16[13] += g.w * h.y; o16[14] += g.w * h.z; o16[15] += g.w * h.w;
           }
           for (int i = 0; i < 4; ++i)
-            for (int j = 0; j < 4; ++j) reinterpret_cast<double*>(AR)[grp * 144 + (tb + i) * 12 + ib + j] = o16[i * 4 + j];
+            for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
         }
         // dh[c,n,i] += sum_t Pt[t][i] dOt[c,n,t]
         tile_temporal(DH, dOt, PS, C, NT, Pt, true, true);
         __syncthreads();
         if (tid < 144) {
           double s = 0.0;
-          for (int g2 = 0; g2 < ngr; ++g2) s += reinterpret_cast<const double*>(AR)[g2 * 144 + tid];
+          for (int g2 = 0; g2 < ngr; ++g2) s += (double)AR[g2 * 144 + tid];
           pt_acc += s;
         }
         __syncthreads();
@@ -327,7 +331,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
           for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DOS + (c0 + j) * PS + nl * 12 + t0, e[j]);
         }
       }
-      if (smix) wgrad_accum<RBT>(acc, a.jobs[JOB_WS], GZ, H, PS, PQ, -1, a.S);
+      if (smix && !a.skip_wgrad) wgrad_accum<RBT>(acc, a.jobs[JOB_WS], GZ, H, PS, PQ, -1, a.S);
       __syncthreads();
       // dA[n,i] at the adjacency non-zeros, delta[n] = sum_i A[n,i] dA[n,i]; one warp per row
       const float* GA = DOS ? DOS : Gs;
@@ -397,7 +401,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   }
   // ---- flush the per-block partials
   __syncthreads();
-  wgrad_flush<RBT>(acc, a.jobs, blk, a.S);
+  if (!a.skip_wgrad) wgrad_flush<RBT>(acc, a.jobs, blk, a.S);
   if (tid < a.nbias) a.bias_part[(int64_t)blk * a.nbias + tid] = bacc;
   if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
   {
@@ -838,6 +842,11 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   int rc = bwd_layout(p, L);
   if (rc) { msgat_set_error("MEAM backward: unsupported shape (code %d)", rc); return rc; }
   const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
+  bool tc_w = false;
+#ifndef MSGAT_EMU
+  tc_w = tc_wgrad_supported(p);
+#endif
+  const int Jw = tc_w ? tc_wgrad_blocks_per_sample(p) : L.J * L.S;  // weight-gradient partials per sample
   const float* G = dout;
   if (need_mask) {
     if (!out) { msgat_set_error("MEAM backward: forward output needed for the ReLU mask"); return -32; }
@@ -868,6 +877,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
     size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
     a.S = L.S;
+    a.skip_wgrad = tc_w ? 1 : 0;
 #define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
     if (L.RBT == 2) {
       if (L.NT == 16) BWD_CASE(16, 2); else if (L.NT == 8) BWD_CASE(8, 2); else BWD_CASE(4, 2);
@@ -876,6 +886,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     }
 #undef BWD_CASE
   }
+#ifndef MSGAT_EMU
+  if (tc_w) {
+    float* wg = scratch + L.o_wg;
+    launch_tc_wgrad(p, prm, adj, x, G, saved, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
+                    wg + L.off_job[JOB_CONV + 1], wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT,
+                    scratch + L.o_dMc, (int64_t)p.Oc * p.C, stream);
+  }
+#endif
   if (p.Os) {
     launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
     SFinArgs a;
@@ -887,7 +905,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   }
   if (p.Oc || p.Ot) {
     BSmallArgs a;
-    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = L.J * L.S;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = Jw;
     a.dMc_part = scratch + L.o_dMc; a.dPt_part = reinterpret_cast<const double*>(scratch + L.o_dPt); a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
     a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w; a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
     a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
@@ -919,14 +937,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     const float* wg = scratch + L.o_wg;
     const float* bp = scratch + L.o_bias;
     if (p.flags & MSGAT_F_RES) {
-      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, L.nblk * L.S, L.WGT, 1, 0);
+      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, p.B * Jw, L.WGT, 1, 0);
       add(g->res_b, bp, p.O, L.nblk, L.nbias, 1, 0);
     }
-    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, L.nblk * L.S, L.WGT, 1, 0);
+    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, p.B * Jw, L.WGT, 1, 0);
     for (int i = 0; i < p.n_conv; ++i) {
       const int K = i == 0 ? p.C : p.Ot;
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, L.nblk * L.S, L.WGT, 2, 0);
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, L.nblk * L.S, L.WGT, 2, 1);
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, p.B * Jw, L.WGT, 2, 0);
+      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, p.B * Jw, L.WGT, 2, 1);
       add(g->conv_b[i], i + 1 == p.n_conv ? bp + p.Oc : bp + p.O + i * p.Ot, p.Ot, L.nblk, L.nbias, 1, 0);
     }
     if (p.flags & MSGAT_F_LN) {

@@ -204,6 +204,7 @@ struct ApplyArgs {
   const int32_t *row_ptr, *col_idx;
   int nnz;
   float* out;
+  float* Y1;  // optional [B,Ot,N,12]: output of the first conv of a two-conv chain
 };
 
 template <int NT>
@@ -291,6 +292,9 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
         mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
         for (int j = 0; j < 4; ++j)
           if (o0 + j < a.Ot) st4(dst + (o0 + j) * PS + nl * 12 + t0, acc[j]);
+        if (a.Y1 && i == 0 && n0 + nl < a.N)
+          for (int j = 0; j < 4; ++j)
+            if (o0 + j < a.Ot) st4(a.Y1 + (((int64_t)b * a.Ot + o0 + j) * a.N + n0 + nl) * 12 + t0, acc[j]);
       }
       __syncthreads();
       cin = dst;
@@ -390,6 +394,9 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     MSGAT_LAUNCH(k_small, dim3(p.B), dim3(256), smem, stream, a);
   }
   if (p.Os) launch_sstats(p, prm, adj, saved, stream);
+#ifndef MSGAT_EMU
+  if (tc_apply_supported(p)) return launch_tc_apply(p, prm, adj, x, out, saved, stream);
+#endif
   {
     ApplyArgs a;
     a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
@@ -401,6 +408,7 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
     a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr; a.nnz = p.nnz;
     a.out = out;
+    a.Y1 = (p.precision == MSGAT_PREC_TF32 && p.n_conv == 2) ? saved + p.o_Y1 : nullptr;
     const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
     size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
     const int nthr = pick_threads(chunks * p.NTa * 3, 512);

@@ -1,0 +1,299 @@
+// tc_wgrad.cu -- every weight gradient of a MEAM as tcgen05 (kind::tf32) GEMMs whose
+// contraction runs over the positions (node, t):
+//   dWres[o,c]   = sum_p G[o,p]   X[c,p]          residual 1x1 conv            (msgat.py:116,131)
+//   dMc[o,c]     = sum_p G_c[o,p] H[c,p]          folded channel attention     (attention.py:94, msgat.py:94), per sample
+//   dW1now/past  = sum_p dA_now/past[k,p] H[c,p]  first conv behind the temporal attention (msgat.py:71-72, attention.py:66)
+//   dWs[o,c]     = sum_p GZ[o,p]  H[c,p]          GACN.W commuted in front of the aggregation (msgat.py:27)
+//   dW2now/past  = sum_p G_t[o,p] Y1[k,p] / Y1[k,p-d2]   second conv
+// with G the masked upstream gradient [cacn | tacn | gacn], H = LayerNorm_T(X), Y1 the first
+// conv's output (saved by the forward), GZ the transposed sparse aggregation of G_s, and
+//   dY1[k,t] = sum_o W2now[o,k] G_t[o,t] + W2past[o,k] G_t[o,t+d2],
+//   dA_now[k,i] = sum_t Pt[t,i] dY1[k,t],  dA_past[k,i] = sum_{t>=d1} Pt[t-d1,i] dY1[k,t].
+// Positions are contiguous in HBM, so every operand is K-major: tiles of 96 positions
+// (8 nodes) in the standard 128-byte swizzle, three MMA groups per tile, accumulators stay
+// in TMEM across all tiles of the CTA and are flushed once as per-CTA partials (k_reduce sums
+// them in a fixed order).
+#include "kernels.h"
+#include "tc_common.cuh"
+#include "tile_ops.cuh"
+
+#define TCW_NT 8
+#define TCW_P 96
+#define TCW_THREADS 512
+
+struct TcWgradArgs {
+  const float* x; int64_t x_sb, x_sc;
+  const float* G;   // masked dout [B,O,N,12]
+  int C, Cp, N, O, b, ntile, J, d1, d2, nnz, has_ln;
+  const float *ln_w, *ln_b, *c2_w, *Pt, *Y1, *pw;
+  const int32_t *csc_ptr, *csc_row, *csc_eid;
+  float *p_res, *p_ws, *p_c1past, *p_c1now, *p_c2past, *p_c2now;  // partial bases (block 0), row-major
+  int64_t wg_stride;                                             // floats between consecutive blocks
+  float* p_mc; int64_t mc_stride;
+};
+
+static inline int rup8(int v) { return (v + 7) & ~7; }
+static inline int rup16(int v) { return (v + 15) & ~15; }
+
+size_t tc_wgrad_smem(int C, int O, int b) {
+  const int Cp = rup8(C);
+  size_t rows = (size_t)O + 2 * Cp + 3 * b + 2 * b;
+  size_t s = rows * 128 * 3;
+  s += 16 * 1024;                                    // slack: M = 128 / N padded reads run past the last tile
+  s += ((size_t)2 * b * b + 144 * 2 + 24 + 8) * 4;   // W2 taps, Pt, Ptd, ln, mbarrier + TMEM slot
+  return s + 1024;
+}
+
+__global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int C = a.C, Cp = a.Cp, O = a.O, b = a.b, tid = threadIdx.x, warp = tid >> 5, bi = blockIdx.y;
+  const uint32_t cbG = (uint32_t)O * 128u, cbX = (uint32_t)(2 * Cp) * 128u, cbA = (uint32_t)(3 * b) * 128u, cbY = (uint32_t)(2 * b) * 128u;
+  unsigned char* TG = smem;             // [O][96]            G
+  unsigned char* TX = TG + 3 * cbG;     // [2Cp][96]          X rows 0..Cp, H rows Cp..2Cp
+  unsigned char* TA = TX + 3 * cbX;     // [3b][96]           dA_now | dA_past | GZ
+  unsigned char* TY = TA + 3 * cbA;     // [2b][96]           Y1 | shift_d2(Y1)
+  float* W2n = reinterpret_cast<float*>(TY + 3 * cbY + 16 * 1024);  // [o][k] tap 1
+  float* W2p = W2n + b * b;                                         // [o][k] tap 0
+  float* Pt = W2p + b * b;
+  float* Ptd = Pt + 144;
+  float* LW = Ptd + 144;
+  uint64_t& bar = *reinterpret_cast<uint64_t*>(LW + 24);
+  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(LW + 26);
+
+  // zero all operand tiles once: pad rows (C..Cp) and the slack must be finite
+  for (int i = tid; i < (int)((3 * (cbG + cbX + cbA + cbY) + 16 * 1024) / 16); i += TCW_THREADS)
+    reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i < b * b; i += TCW_THREADS) { W2n[i] = a.c2_w[i * 2 + 1]; W2p[i] = a.c2_w[i * 2]; }
+  for (int i = tid; i < 144; i += TCW_THREADS) {
+    const int t = i / 12, j = i - t * 12;
+    Pt[i] = a.Pt[(int64_t)bi * 144 + i];
+    Ptd[i] = t >= a.d1 ? a.Pt[(int64_t)bi * 144 + (t - a.d1) * 12 + j] : 0.f;
+  }
+  if (tid < 12) { LW[tid] = a.has_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = a.has_ln ? a.ln_b[tid] : 0.f; }
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tm = tmem_slot;
+  const int N1 = (2 * Cp + 15) & ~15, N2 = (Cp + 15) & ~15, N3 = 2 * b;
+  const uint32_t D1 = tm, D2 = tm + 160, D3 = tm + 256;
+  const uint32_t id1 = umma_idesc_tf32(128, N1, 0, 0), id2 = umma_idesc_tf32(128, N2, 0, 0), id3 = umma_idesc_tf32(128, N3, 0, 0);
+  const uint32_t sTG = smem_u32(TG), sTX = smem_u32(TX), sTA = smem_u32(TA), sTY = smem_u32(TY);
+  const float* xb = a.x + bi * a.x_sb;
+  const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
+  const float* Yb = a.Y1 + (int64_t)bi * b * a.N * 12;
+  const float* pwb = a.pw + (int64_t)bi * a.nnz;
+  uint32_t phase = 0;
+  int first = 1;
+
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+    const int n0 = tile * TCW_NT;
+    // ---- G tile
+    for (int i = tid; i < O * 24; i += TCW_THREADS) {
+      const int r = i / 24, p4 = (i - r * 24) * 4, n = n0 + p4 / 12;
+      float4 v = f4zero();
+      if (n < a.N) v = ld4(Gb + ((int64_t)r * a.N + n0) * 12 + p4);
+      st4(reinterpret_cast<float*>(TG + sw128_off(r, p4, cbG)), v);
+    }
+    // ---- X rows and their LayerNorm (msgat.py:122)
+    for (int r = tid; r < C * TCW_NT; r += TCW_THREADS) {
+      const int c = r / TCW_NT, nl = r - c * TCW_NT, n = n0 + nl;
+      float4 u = f4zero(), v = f4zero(), w = f4zero();
+      if (n < a.N) { const float* s = xb + c * a.x_sc + (int64_t)n * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
+      const int pp = nl * 12;
+      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp, cbX)), u);
+      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp + 4, cbX)), v);
+      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp + 8, cbX)), w);
+      if (n < a.N && a.has_ln) {
+        float mu = (u.x + u.y + u.z + u.w + v.x + v.y + v.z + v.w + w.x + w.y + w.z + w.w) * (1.0f / 12.0f);
+        u.x -= mu; u.y -= mu; u.z -= mu; u.w -= mu; v.x -= mu; v.y -= mu; v.z -= mu; v.w -= mu;
+        w.x -= mu; w.y -= mu; w.z -= mu; w.w -= mu;
+        const float rs = rsqrtf((dot4(u, u) + dot4(v, v) + dot4(w, w)) * (1.0f / 12.0f) + LN_EPS);
+        u.x = u.x * rs * LW[0] + LW[12]; u.y = u.y * rs * LW[1] + LW[13]; u.z = u.z * rs * LW[2] + LW[14]; u.w = u.w * rs * LW[3] + LW[15];
+        v.x = v.x * rs * LW[4] + LW[16]; v.y = v.y * rs * LW[5] + LW[17]; v.z = v.z * rs * LW[6] + LW[18]; v.w = v.w * rs * LW[7] + LW[19];
+        w.x = w.x * rs * LW[8] + LW[20]; w.y = w.y * rs * LW[9] + LW[21]; w.z = w.z * rs * LW[10] + LW[22]; w.w = w.w * rs * LW[11] + LW[23];
+      }
+      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp, cbX)), u);
+      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp + 4, cbX)), v);
+      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp + 8, cbX)), w);
+    }
+    // ---- Y1 rows and their causal shift
+    for (int r = tid; r < b * TCW_NT; r += TCW_THREADS) {
+      const int o = r / TCW_NT, nl = r - o * TCW_NT, n = n0 + nl;
+      float y[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) y[t] = 0.f;
+      if (n < a.N) {
+        const float* s = Yb + ((int64_t)o * a.N + n) * 12;
+        const float4 u = ld4(s), v = ld4(s + 4), w = ld4(s + 8);
+        y[0] = u.x; y[1] = u.y; y[2] = u.z; y[3] = u.w; y[4] = v.x; y[5] = v.y; y[6] = v.z; y[7] = v.w;
+        y[8] = w.x; y[9] = w.y; y[10] = w.z; y[11] = w.w;
+      }
+      const int pp = nl * 12;
+#pragma unroll
+      for (int t0 = 0; t0 < 12; t0 += 4) {
+        st4(reinterpret_cast<float*>(TY + sw128_off(o, pp + t0, cbY)), make_float4(y[t0], y[t0 + 1], y[t0 + 2], y[t0 + 3]));
+        float4 s;
+        s.x = t0 >= a.d2 ? y[t0 - a.d2 < 0 ? 0 : t0 - a.d2] : 0.f;
+        s.y = t0 + 1 >= a.d2 ? y[t0 + 1 - a.d2 < 0 ? 0 : t0 + 1 - a.d2] : 0.f;
+        s.z = t0 + 2 >= a.d2 ? y[t0 + 2 - a.d2 < 0 ? 0 : t0 + 2 - a.d2] : 0.f;
+        s.w = t0 + 3 >= a.d2 ? y[t0 + 3 - a.d2 < 0 ? 0 : t0 + 3 - a.d2] : 0.f;
+        st4(reinterpret_cast<float*>(TY + sw128_off(b + o, pp + t0, cbY)), s);
+      }
+    }
+    // ---- GZ[o][i] = sum_n A[n,i] g_s[o][n]  (transpose of attention.py:36 through the CSC view)
+    for (int it = tid; it < b * 24; it += TCW_THREADS) {
+      const int o = it / 24, p4 = (it - o * 24) * 4, nl = p4 / 12, t0 = p4 - nl * 12, n = n0 + nl;
+      float4 d = f4zero();
+      if (n < a.N) {
+        const int k1 = a.csc_ptr[n + 1];
+        for (int k = a.csc_ptr[n]; k < k1; ++k)
+          fma4(d, pwb[a.csc_eid[k]], ld4(Gb + ((int64_t)(2 * b + o) * a.N + a.csc_row[k]) * 12 + t0));
+      }
+      st4(reinterpret_cast<float*>(TA + sw128_off(2 * b + o, p4, cbA)), d);
+    }
+    __syncthreads();
+    // ---- dY1 (transpose of the second conv), then dA_now / dA_past (transpose of the temporal mix)
+    for (int r = tid; r < b * TCW_NT; r += TCW_THREADS) {
+      const int k = r / TCW_NT, nl = r - k * TCW_NT, pp = nl * 12;
+      float dy[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) dy[t] = 0.f;
+      for (int o = 0; o < b; ++o) {
+        const float wn = W2n[o * b + k], wp = W2p[o * b + k];
+        float g[12];
+#pragma unroll
+        for (int t0 = 0; t0 < 12; t0 += 4) {
+          const float4 v = ld4(reinterpret_cast<const float*>(TG + sw128_off(b + o, pp + t0, cbG)));
+          g[t0] = v.x; g[t0 + 1] = v.y; g[t0 + 2] = v.z; g[t0 + 3] = v.w;
+        }
+#pragma unroll
+        for (int t = 0; t < 12; ++t) {
+          dy[t] = fmaf(wn, g[t], dy[t]);
+          if (t + a.d2 < 12) dy[t] = fmaf(wp, g[t + a.d2 < 12 ? t + a.d2 : 11], dy[t]);
+        }
+      }
+      float an[12], ap[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) {
+        float s = 0.f, q = 0.f;
+#pragma unroll
+        for (int t = 0; t < 12; ++t) { s = fmaf(Pt[t * 12 + i], dy[t], s); q = fmaf(Ptd[t * 12 + i], dy[t], q); }
+        an[i] = s; ap[i] = q;
+      }
+#pragma unroll
+      for (int t0 = 0; t0 < 12; t0 += 4) {
+        st4(reinterpret_cast<float*>(TA + sw128_off(k, pp + t0, cbA)), make_float4(an[t0], an[t0 + 1], an[t0 + 2], an[t0 + 3]));
+        st4(reinterpret_cast<float*>(TA + sw128_off(b + k, pp + t0, cbA)), make_float4(ap[t0], ap[t0 + 1], ap[t0 + 2], ap[t0 + 3]));
+      }
+    }
+    fence_smem_to_async();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after_sync();
+      for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
+        const uint32_t cbo = (uint32_t)(k8 >> 2), ko = (uint32_t)(k8 & 3) * 32u;
+        const uint32_t acc = (first && k8 == 0) ? 0u : 1u;
+        umma_tf32(D1, umma_desc(sTG + cbo * cbG + ko, 0u, 1024u, 2), umma_desc(sTX + cbo * cbX + ko, 0u, 1024u, 2), id1, acc);
+        umma_tf32(D2, umma_desc(sTA + cbo * cbA + ko, 0u, 1024u, 2),
+                  umma_desc(sTX + cbo * cbX + (uint32_t)(Cp / 8) * 1024u + ko, 0u, 1024u, 2), id2, acc);
+        umma_tf32(D3, umma_desc(sTG + cbo * cbG + (uint32_t)(b / 8) * 1024u + ko, 0u, 1024u, 2),
+                  umma_desc(sTY + cbo * cbY + ko, 0u, 1024u, 2), id3, acc);
+      }
+      umma_commit(smem_u32(&bar));
+    }
+    first = 0;
+    mbar_wait(smem_u32(&bar), phase); phase ^= 1;
+    tc_fence_after_sync();
+  }
+  // ---- flush: TMEM lane = output row, columns = input channel
+  {
+    const int blk = bi * a.J + blockIdx.x;
+    const int row = (warp & 3) * 32 + (tid & 31);
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const int half = warp >> 2;  // the four warpgroups split the column groups
+    float* wres = a.p_res + (int64_t)blk * a.wg_stride;
+    float* wmc = a.p_mc + (int64_t)blk * a.mc_stride;
+    int cg = 0;
+    for (int c0 = 0; c0 < N1; c0 += 8, ++cg) {
+      float v[8];
+      if ((cg & 3) != half) continue;
+      tmem_ld8(D1 + lane_base + c0, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = c0 + j;
+        if (c < C && row < O) wres[row * C + c] = v[j];
+        if (c >= Cp && c < Cp + C && row < b) wmc[row * C + c - Cp] = v[j];
+      }
+    }
+    float* w1n = a.p_c1now + (int64_t)blk * a.wg_stride;
+    float* w1p = a.p_c1past + (int64_t)blk * a.wg_stride;
+    float* wws = a.p_ws + (int64_t)blk * a.wg_stride;
+    cg = 0;
+    for (int c0 = 0; c0 < N2; c0 += 8, ++cg) {
+      float v[8];
+      if ((cg & 3) != half) continue;
+      tmem_ld8(D2 + lane_base + c0, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = c0 + j;
+        if (c >= C) continue;
+        if (row < b) w1n[row * C + c] = v[j];
+        else if (row < 2 * b) w1p[(row - b) * C + c] = v[j];
+        else if (row < 3 * b) wws[(row - 2 * b) * C + c] = v[j];
+      }
+    }
+    float* w2n = a.p_c2now + (int64_t)blk * a.wg_stride;
+    float* w2p = a.p_c2past + (int64_t)blk * a.wg_stride;
+    cg = 0;
+    for (int c0 = 0; c0 < N3; c0 += 8, ++cg) {
+      float v[8];
+      if ((cg & 3) != half) continue;
+      tmem_ld8(D3 + lane_base + c0, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = c0 + j;
+        if (row >= b) continue;
+        if (c < b) w2n[row * b + c] = v[j];
+        else w2p[row * b + c - b] = v[j];
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tm, 512);
+}
+
+bool tc_wgrad_supported(const Plan& p) {
+  const int full = MSGAT_F_RES | MSGAT_F_CMIX | MSGAT_F_SMIX;
+  const int b = p.Oc;
+  return p.precision == MSGAT_PREC_TF32 && (p.flags & full) == full && p.n_conv == 2 && p.Oc == p.Ot && p.Ot == p.Os &&
+         b % 8 == 0 && b >= 8 && b <= 24 && p.C >= 1 && p.C <= 72 && p.O <= 72 &&
+         p.dil[0] >= 1 && p.dil[0] < 12 && p.dil[1] >= 1 && p.dil[1] < 12;
+}
+
+int tc_wgrad_blocks_per_sample(const Plan& p) {
+  const int ntile = (p.N + TCW_NT - 1) / TCW_NT;
+  int J = 148 / p.B;
+  if (J > ntile) J = ntile;
+  return J < 1 ? 1 : J;
+}
+
+int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
+                    const float* saved, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
+                    float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream) {
+  TcWgradArgs a;
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
+  a.C = p.C; a.Cp = rup8(p.C); a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TCW_NT - 1) / TCW_NT;
+  a.J = tc_wgrad_blocks_per_sample(p);
+  a.d1 = p.dil[0]; a.d2 = p.dil[1]; a.nnz = p.nnz; a.has_ln = (p.flags & MSGAT_F_LN) ? 1 : 0;
+  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.c2_w = prm->conv_w[1];
+  a.Pt = saved + p.o_Pt; a.Y1 = saved + p.o_Y1; a.pw = saved + p.o_pw;
+  a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+  a.p_res = p_res; a.p_ws = p_ws; a.p_c1past = p_c1past; a.p_c1now = p_c1now; a.p_c2past = p_c2past; a.p_c2now = p_c2now;
+  a.wg_stride = wg_stride; a.p_mc = p_mc; a.mc_stride = mc_stride;
+  MSGAT_LAUNCH(k_tc_wgrad, dim3(a.J, p.B), dim3(TCW_THREADS), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
+  return 0;
+}
