@@ -210,11 +210,11 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
     __syncthreads();
     // ---- S3: temporal branch
     if (a.Ot) {
-      tile_temporal(OT, H, PS, C, NT, Pt, false, false);
+      // forward temporal mix and intermediate conv outputs are inputs of weight gradients only
+      if (!a.skip_wgrad) tile_temporal(OT, H, PS, C, NT, Pt, false, false);
       __syncthreads();
-      // recompute the intermediate conv outputs (inputs of the later convs' weight gradients)
       const float* cin = OT;
-      for (int i = 0; i + 1 < a.n_conv; ++i) {
+      for (int i = 0; i + 1 < a.n_conv && !a.skip_wgrad; ++i) {
         const int K = i == 0 ? C : a.Ot, WOt = (a.Ot + 3) & ~3;
         float *cvA = AR, *cvP = AR + K * WOt, *cvB = AR + 2 * K * WOt;
         stage_wT(cvA, a.conv_w[i], a.Ot, K, WOt, 2, 1);

@@ -135,7 +135,7 @@ struct SColArgs {
 
 MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][16]: U[12], m, pad, w = delta / l as one fp64 in slots 14-15
+  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][20]: U[12], m, pad, w = delta / l as one fp64 in slots 14-15; the 80-byte pitch keeps the 8 row lanes on distinct banks
   const int b = blockIdx.y, rl = threadIdx.x / SS_LANES, cl = threadIdx.x % SS_LANES;
   const int i = blockIdx.x * SS_ROWS + rl;
   const bool live = i < a.N;
@@ -150,16 +150,16 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     // stage the U rows of this chunk (written by k_sstats) with their (m, delta / l)
     for (int k = threadIdx.x; k < len * 3; k += blockDim.x) {
       const int r = k / 3, c4 = (k - r * 3) * 4;
-      st4(UR + r * 16 + c4, ld4(Ub + (int64_t)(n0 + r) * 12 + c4));
+      st4(UR + r * 20 + c4, ld4(Ub + (int64_t)(n0 + r) * 12 + c4));
     }
     for (int r = threadIdx.x; r < len; r += blockDim.x) {
       const int64_t g = (int64_t)b * a.N + n0 + r;
-      UR[r * 16 + 12] = a.m[g];
-      *reinterpret_cast<double*>(UR + r * 16 + 14) = (double)a.delta[g] / a.l[g];
+      UR[r * 20 + 12] = a.m[g];
+      *reinterpret_cast<double*>(UR + r * 20 + 14) = (double)a.delta[g] / a.l[g];
     }
     __syncthreads();
     for (int r = cl; r < len; r += SS_LANES) {
-      const float* u = UR + r * 16;
+      const float* u = UR + r * 20;
       float4 u0 = ld4(u), u1 = ld4(u + 4), u2 = ld4(u + 8), u3 = ld4(u + 12);
       float s = qi[0] * u0.x;
       s = fmaf(qi[1], u0.y, s); s = fmaf(qi[2], u0.z, s); s = fmaf(qi[3], u0.w, s);
@@ -189,7 +189,7 @@ int launch_scol(const Plan& p, const float* Wg, const float* saved, const float*
   SColArgs a;
   a.N = p.N; a.qs = saved + p.o_qs; a.U = saved + p.o_U; a.m = saved + p.o_m; a.l = reinterpret_cast<const double*>(saved + p.o_l); a.delta = delta; a.dq = dq;
   dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B);
-  size_t smem = (SS_CHUNK * 16) * sizeof(float);
+  size_t smem = (SS_CHUNK * 20) * sizeof(float);
   MSGAT_LAUNCH(k_scol, grid, dim3(256), smem, stream, a);
   return 0;
 }

@@ -15,6 +15,7 @@
 // A tile is 16 nodes = 192 positions = two M = 128 blocks (the second one half used); operands
 // sit in shared memory in the 128-byte-swizzle / 32-byte-atom layout MN-major TF32 needs
 // (tc_common.cuh), accumulators in TMEM (448 of 512 columns).
+#include <stdlib.h>
 #include "kernels.h"
 #include "tc_common.cuh"
 #include "tile_ops.cuh"
@@ -251,6 +252,8 @@ __global__ void __launch_bounds__(TCF_THREADS, 1) k_tc_apply(TcApplyArgs a) {
 }
 
 bool tc_apply_supported(const Plan& p) {
+  const char* off = getenv("MSGAT_TC_DISABLE");  // test switch: bit 0 = apply kernel
+  if (off && (atoi(off) & 1)) return false;
   const int full = MSGAT_F_LN | MSGAT_F_RES | MSGAT_F_RELU | MSGAT_F_CMIX | MSGAT_F_SMIX;
   const int b = p.Oc;
   return p.precision == MSGAT_PREC_TF32 && (p.flags & full) == full && p.n_conv == 2 && p.s_pre && p.Oc == p.Ot &&

@@ -13,6 +13,7 @@
 // (8 nodes) in the standard 128-byte swizzle, three MMA groups per tile, accumulators stay
 // in TMEM across all tiles of the CTA and are flushed once as per-CTA partials (k_reduce sums
 // them in a fixed order).
+#include <stdlib.h>
 #include "kernels.h"
 #include "tc_common.cuh"
 #include "tile_ops.cuh"
@@ -267,6 +268,8 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
 }
 
 bool tc_wgrad_supported(const Plan& p) {
+  const char* off = getenv("MSGAT_TC_DISABLE");  // test switch: bit 1 = weight-gradient kernel
+  if (off && (atoi(off) & 2)) return false;
   const int full = MSGAT_F_RES | MSGAT_F_CMIX | MSGAT_F_SMIX;
   const int b = p.Oc;
   return p.precision == MSGAT_PREC_TF32 && (p.flags & full) == full && p.n_conv == 2 && p.Oc == p.Ot && p.Ot == p.Os &&
