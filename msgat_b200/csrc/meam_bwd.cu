@@ -807,10 +807,14 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   const int64_t BN = (int64_t)p.B * p.N;
   const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
   L.o_G = o; o += need_mask ? rup4l(BN * 12 * p.O) : 0;
-  L.o_wg = o; o += rup4l((int64_t)L.nblk * L.S * L.WGT);
+  int64_t nwp = (int64_t)L.nblk * L.S;  // weight-gradient partials: k_bwd_main's blocks or the tensor-core kernel's
+#ifndef MSGAT_EMU
+  { const int64_t t = (int64_t)p.B * tc_wgrad_blocks_per_sample(p); if (t > nwp) nwp = t; }
+#endif
+  L.o_wg = o; o += rup4l(nwp * L.WGT);
   L.o_bias = o; o += rup4l((int64_t)L.nblk * L.nbias);
   L.o_ln = o; o += rup4l((int64_t)(L.nblk + L.nblk4) * 24);
-  L.o_dMc = o; o += rup4l((int64_t)L.nblk * L.S * p.Oc * p.C);
+  L.o_dMc = o; o += rup4l(nwp * p.Oc * p.C);
   L.o_dPt = o; o += rup4l(2 * (int64_t)L.nblk * 144);  // fp64
   L.o_delta = o; o += rup4l(BN);
   L.o_dSnz = o; o += rup4l((int64_t)p.B * p.nnz);

@@ -408,7 +408,7 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
     a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr; a.nnz = p.nnz;
     a.out = out;
-    a.Y1 = (p.precision == MSGAT_PREC_TF32 && p.n_conv == 2) ? saved + p.o_Y1 : nullptr;
+    a.Y1 = (p.n_conv == 2) ? saved + p.o_Y1 : nullptr;
     const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
     size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
     const int nthr = pick_threads(chunks * p.NTa * 3, 512);

@@ -74,7 +74,7 @@ static inline int make_plan(const msgat_meam_desc* d, int nnz, Plan* p) {
   p->o_E = o; o += rup4l(2 * BN * 12);   // fp64: E = softmax(S) q
   p->o_U = o; o += d->Os ? rup4l(BN * 12) : 0;
   // output of the first conv of a two-conv chain, kept for the tensor-core weight-gradient kernel
-  p->o_Y1 = o; o += (d->precision == MSGAT_PREC_TF32 && d->n_conv == 2) ? rup4l(BN * 12 * d->Ot) : 0;
+  p->o_Y1 = o; o += (d->n_conv == 2) ? rup4l(BN * 12 * d->Ot) : 0;
   p->o_pw = o; o += rup4l((int64_t)d->B * nnz);
   p->o_qc = o; o += rup4l((int64_t)d->B * d->C * 12);
   p->o_Pc = o; o += rup4l((int64_t)d->B * d->C * d->C);

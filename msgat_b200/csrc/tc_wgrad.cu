@@ -9,18 +9,26 @@
 // conv's output (saved by the forward), GZ the transposed sparse aggregation of G_s, and
 //   dY1[k,t] = sum_o W2now[o,k] G_t[o,t] + W2past[o,k] G_t[o,t+d2],
 //   dA_now[k,i] = sum_t Pt[t,i] dY1[k,t],  dA_past[k,i] = sum_{t>=d1} Pt[t-d1,i] dY1[k,t].
-// Positions are contiguous in HBM, so every operand is K-major: tiles of 96 positions
-// (8 nodes) in the standard 128-byte swizzle, three MMA groups per tile, accumulators stay
-// in TMEM across all tiles of the CTA and are flushed once as per-CTA partials (k_reduce sums
-// them in a fixed order).
+//
+// Error-compensated TF32 ("3xTF32"): every operand v is staged twice, hi = rna_tf32(v) and
+// lo = v - hi (exact in fp32), and each product is issued as hi*hi + hi*lo + lo*hi with fp32
+// accumulation in TMEM; the dropped lo*lo term is 2^-24 relative.  That gives fp32-grade
+// gradients from the tensor cores, so the kernel serves the fp32 path too.
+//
+// Positions are contiguous in HBM, so every operand is K-major.  A tile is 4 nodes = 48
+// positions in the unswizzled core-matrix layout (8 rows x 4 positions = 128 contiguous bytes,
+// tc_common.cuh:core_off); accumulators stay in TMEM across all tiles of the CTA and are
+// flushed once as per-CTA partials (k_reduce sums them in a fixed order).
 #include <stdlib.h>
 #include "kernels.h"
 #include "tc_common.cuh"
 #include "tile_ops.cuh"
 
-#define TCW_NT 8
-#define TCW_P 96
+#define TCW_NT 4
+#define TCW_P 48
+#define TCW_GS (TCW_P * 32)  // bytes of one 8-row group of a tile
 #define TCW_THREADS 512
+#define TCW_SLACK (28 * 1024)
 
 struct TcWgradArgs {
   const float* x; int64_t x_sb, x_sc;
@@ -34,28 +42,45 @@ struct TcWgradArgs {
 };
 
 static inline int rup8(int v) { return (v + 7) & ~7; }
-static inline int rup16(int v) { return (v + 15) & ~15; }
+
+static inline size_t tcw_tiles_bytes(int C, int O, int b) {
+  const int Cp = rup8(C);
+  return (size_t)(rup8(O) + 2 * Cp + 3 * b + 2 * b) / 8 * TCW_GS;  // one precision part (hi or lo)
+}
 
 size_t tc_wgrad_smem(int C, int O, int b) {
-  const int Cp = rup8(C);
-  size_t rows = (size_t)O + 2 * Cp + 3 * b + 2 * b;
-  size_t s = rows * 128 * 3;
-  s += 16 * 1024;                                    // slack: M = 128 / N padded reads run past the last tile
+  size_t s = 2 * tcw_tiles_bytes(C, O, b) + TCW_SLACK;
   s += ((size_t)2 * b * b + 144 * 2 + 24 + 8) * 4;   // W2 taps, Pt, Ptd, ln, mbarrier + TMEM slot
   return s + 1024;
+}
+
+TC_DEV float tf32_rna(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+// v -> hi tile and lo tile at the same offset
+TC_DEV void st_split(unsigned char* hi, unsigned char* lo, uint32_t off, float4 v) {
+  float4 h = make_float4(tf32_rna(v.x), tf32_rna(v.y), tf32_rna(v.z), tf32_rna(v.w));
+  st4(reinterpret_cast<float*>(hi + off), h);
+  st4(reinterpret_cast<float*>(lo + off), make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
 }
 
 __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int C = a.C, Cp = a.Cp, O = a.O, b = a.b, tid = threadIdx.x, warp = tid >> 5, bi = blockIdx.y;
-  const uint32_t cbG = (uint32_t)O * 128u, cbX = (uint32_t)(2 * Cp) * 128u, cbA = (uint32_t)(3 * b) * 128u, cbY = (uint32_t)(2 * b) * 128u;
-  unsigned char* TG = smem;             // [O][96]            G
-  unsigned char* TX = TG + 3 * cbG;     // [2Cp][96]          X rows 0..Cp, H rows Cp..2Cp
-  unsigned char* TA = TX + 3 * cbX;     // [3b][96]           dA_now | dA_past | GZ
-  unsigned char* TY = TA + 3 * cbA;     // [2b][96]           Y1 | shift_d2(Y1)
-  float* W2n = reinterpret_cast<float*>(TY + 3 * cbY + 16 * 1024);  // [o][k] tap 1
-  float* W2p = W2n + b * b;                                         // [o][k] tap 0
+  const int Op = (O + 7) & ~7;
+  const uint32_t GS = TCW_GS;
+  const uint32_t szG = (uint32_t)(Op / 8) * GS, szX = (uint32_t)(2 * Cp / 8) * GS, szA = (uint32_t)(3 * b / 8) * GS,
+                 szY = (uint32_t)(2 * b / 8) * GS;
+  const uint32_t part = szG + szX + szA + szY;  // hi part, then the lo part in the same order
+  unsigned char* TG = smem;             // [O][48]            G
+  unsigned char* TX = TG + szG;         // [2Cp][48]          X rows 0..Cp, H rows Cp..2Cp
+  unsigned char* TA = TX + szX;         // [3b][48]           dA_now | dA_past | GZ
+  unsigned char* TY = TA + szA;         // [2b][48]           Y1 | shift_d2(Y1)
+  float* W2n = reinterpret_cast<float*>(smem + 2 * part + TCW_SLACK);  // [o][k] tap 1
+  float* W2p = W2n + b * b;                                            // [o][k] tap 0
   float* Pt = W2p + b * b;
   float* Ptd = Pt + 144;
   float* LW = Ptd + 144;
@@ -63,7 +88,7 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(LW + 26);
 
   // zero all operand tiles once: pad rows (C..Cp) and the slack must be finite
-  for (int i = tid; i < (int)((3 * (cbG + cbX + cbA + cbY) + 16 * 1024) / 16); i += TCW_THREADS)
+  for (int i = tid; i < (int)((2 * part + TCW_SLACK) / 16); i += TCW_THREADS)
     reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int i = tid; i < b * b; i += TCW_THREADS) { W2n[i] = a.c2_w[i * 2 + 1]; W2p[i] = a.c2_w[i * 2]; }
   for (int i = tid; i < 144; i += TCW_THREADS) {
@@ -89,24 +114,27 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   uint32_t phase = 0;
   int first = 1;
 
+  // Work items put the row-within-group index in the low 3 bits: 8 consecutive threads fill one
+  // 128-byte core matrix, a warp four consecutive ones -> conflict-free shared-memory stores.
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
     const int n0 = tile * TCW_NT;
     // ---- G tile
-    for (int i = tid; i < O * 24; i += TCW_THREADS) {
-      const int r = i / 24, p4 = (i - r * 24) * 4, n = n0 + p4 / 12;
+    for (int i = tid; i < Op * 12; i += TCW_THREADS) {
+      const int r = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, n = n0 + p4 / 12;
       float4 v = f4zero();
-      if (n < a.N) v = ld4(Gb + ((int64_t)r * a.N + n0) * 12 + p4);
-      st4(reinterpret_cast<float*>(TG + sw128_off(r, p4, cbG)), v);
+      if (r < O && n < a.N) v = ld4(Gb + ((int64_t)r * a.N + n0) * 12 + p4);
+      st_split(TG, TG + part, core_off(r, p4, GS), v);
     }
     // ---- X rows and their LayerNorm (msgat.py:122)
-    for (int r = tid; r < C * TCW_NT; r += TCW_THREADS) {
-      const int c = r / TCW_NT, nl = r - c * TCW_NT, n = n0 + nl;
+    for (int i = tid; i < Cp * TCW_NT; i += TCW_THREADS) {
+      const int c = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, n = n0 + nl;
+      if (c >= C) continue;
       float4 u = f4zero(), v = f4zero(), w = f4zero();
       if (n < a.N) { const float* s = xb + c * a.x_sc + (int64_t)n * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
       const int pp = nl * 12;
-      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp, cbX)), u);
-      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp + 4, cbX)), v);
-      st4(reinterpret_cast<float*>(TX + sw128_off(c, pp + 8, cbX)), w);
+      st_split(TX, TX + part, core_off(c, pp, GS), u);
+      st_split(TX, TX + part, core_off(c, pp + 4, GS), v);
+      st_split(TX, TX + part, core_off(c, pp + 8, GS), w);
       if (n < a.N && a.has_ln) {
         float mu = (u.x + u.y + u.z + u.w + v.x + v.y + v.z + v.w + w.x + w.y + w.z + w.w) * (1.0f / 12.0f);
         u.x -= mu; u.y -= mu; u.z -= mu; u.w -= mu; v.x -= mu; v.y -= mu; v.z -= mu; v.w -= mu;
@@ -116,13 +144,13 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
         v.x = v.x * rs * LW[4] + LW[16]; v.y = v.y * rs * LW[5] + LW[17]; v.z = v.z * rs * LW[6] + LW[18]; v.w = v.w * rs * LW[7] + LW[19];
         w.x = w.x * rs * LW[8] + LW[20]; w.y = w.y * rs * LW[9] + LW[21]; w.z = w.z * rs * LW[10] + LW[22]; w.w = w.w * rs * LW[11] + LW[23];
       }
-      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp, cbX)), u);
-      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp + 4, cbX)), v);
-      st4(reinterpret_cast<float*>(TX + sw128_off(Cp + c, pp + 8, cbX)), w);
+      st_split(TX, TX + part, core_off(Cp + c, pp, GS), u);
+      st_split(TX, TX + part, core_off(Cp + c, pp + 4, GS), v);
+      st_split(TX, TX + part, core_off(Cp + c, pp + 8, GS), w);
     }
     // ---- Y1 rows and their causal shift
-    for (int r = tid; r < b * TCW_NT; r += TCW_THREADS) {
-      const int o = r / TCW_NT, nl = r - o * TCW_NT, n = n0 + nl;
+    for (int i = tid; i < b * TCW_NT; i += TCW_THREADS) {
+      const int o = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, n = n0 + nl;
       float y[12];
 #pragma unroll
       for (int t = 0; t < 12; ++t) y[t] = 0.f;
@@ -135,30 +163,30 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
       const int pp = nl * 12;
 #pragma unroll
       for (int t0 = 0; t0 < 12; t0 += 4) {
-        st4(reinterpret_cast<float*>(TY + sw128_off(o, pp + t0, cbY)), make_float4(y[t0], y[t0 + 1], y[t0 + 2], y[t0 + 3]));
+        st_split(TY, TY + part, core_off(o, pp + t0, GS), make_float4(y[t0], y[t0 + 1], y[t0 + 2], y[t0 + 3]));
         float4 s;
         s.x = t0 >= a.d2 ? y[t0 - a.d2 < 0 ? 0 : t0 - a.d2] : 0.f;
         s.y = t0 + 1 >= a.d2 ? y[t0 + 1 - a.d2 < 0 ? 0 : t0 + 1 - a.d2] : 0.f;
         s.z = t0 + 2 >= a.d2 ? y[t0 + 2 - a.d2 < 0 ? 0 : t0 + 2 - a.d2] : 0.f;
         s.w = t0 + 3 >= a.d2 ? y[t0 + 3 - a.d2 < 0 ? 0 : t0 + 3 - a.d2] : 0.f;
-        st4(reinterpret_cast<float*>(TY + sw128_off(b + o, pp + t0, cbY)), s);
+        st_split(TY, TY + part, core_off(b + o, pp + t0, GS), s);
       }
     }
     // ---- GZ[o][i] = sum_n A[n,i] g_s[o][n]  (transpose of attention.py:36 through the CSC view)
-    for (int it = tid; it < b * 24; it += TCW_THREADS) {
-      const int o = it / 24, p4 = (it - o * 24) * 4, nl = p4 / 12, t0 = p4 - nl * 12, n = n0 + nl;
+    for (int i = tid; i < b * 12; i += TCW_THREADS) {
+      const int o = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, nl = p4 / 12, t0 = p4 - nl * 12, n = n0 + nl;
       float4 d = f4zero();
       if (n < a.N) {
         const int k1 = a.csc_ptr[n + 1];
         for (int k = a.csc_ptr[n]; k < k1; ++k)
           fma4(d, pwb[a.csc_eid[k]], ld4(Gb + ((int64_t)(2 * b + o) * a.N + a.csc_row[k]) * 12 + t0));
       }
-      st4(reinterpret_cast<float*>(TA + sw128_off(2 * b + o, p4, cbA)), d);
+      st_split(TA, TA + part, core_off(2 * b + o, p4, GS), d);
     }
     __syncthreads();
     // ---- dY1 (transpose of the second conv), then dA_now / dA_past (transpose of the temporal mix)
-    for (int r = tid; r < b * TCW_NT; r += TCW_THREADS) {
-      const int k = r / TCW_NT, nl = r - k * TCW_NT, pp = nl * 12;
+    for (int i = tid; i < b * TCW_NT; i += TCW_THREADS) {
+      const int k = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, pp = nl * 12;
       float dy[12];
 #pragma unroll
       for (int t = 0; t < 12; ++t) dy[t] = 0.f;
@@ -167,8 +195,9 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
         float g[12];
 #pragma unroll
         for (int t0 = 0; t0 < 12; t0 += 4) {
-          const float4 v = ld4(reinterpret_cast<const float*>(TG + sw128_off(b + o, pp + t0, cbG)));
-          g[t0] = v.x; g[t0 + 1] = v.y; g[t0 + 2] = v.z; g[t0 + 3] = v.w;
+          const uint32_t off = core_off(b + o, pp + t0, GS);
+          const float4 vh = ld4(reinterpret_cast<const float*>(TG + off)), vl = ld4(reinterpret_cast<const float*>(TG + part + off));
+          g[t0] = vh.x + vl.x; g[t0 + 1] = vh.y + vl.y; g[t0 + 2] = vh.z + vl.z; g[t0 + 3] = vh.w + vl.w;
         }
 #pragma unroll
         for (int t = 0; t < 12; ++t) {
@@ -178,30 +207,36 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
       }
       float an[12], ap[12];
 #pragma unroll
-      for (int i = 0; i < 12; ++i) {
+      for (int j = 0; j < 12; ++j) {
         float s = 0.f, q = 0.f;
 #pragma unroll
-        for (int t = 0; t < 12; ++t) { s = fmaf(Pt[t * 12 + i], dy[t], s); q = fmaf(Ptd[t * 12 + i], dy[t], q); }
-        an[i] = s; ap[i] = q;
+        for (int t = 0; t < 12; ++t) { s = fmaf(Pt[t * 12 + j], dy[t], s); q = fmaf(Ptd[t * 12 + j], dy[t], q); }
+        an[j] = s; ap[j] = q;
       }
 #pragma unroll
       for (int t0 = 0; t0 < 12; t0 += 4) {
-        st4(reinterpret_cast<float*>(TA + sw128_off(k, pp + t0, cbA)), make_float4(an[t0], an[t0 + 1], an[t0 + 2], an[t0 + 3]));
-        st4(reinterpret_cast<float*>(TA + sw128_off(b + k, pp + t0, cbA)), make_float4(ap[t0], ap[t0 + 1], ap[t0 + 2], ap[t0 + 3]));
+        st_split(TA, TA + part, core_off(k, pp + t0, GS), make_float4(an[t0], an[t0 + 1], an[t0 + 2], an[t0 + 3]));
+        st_split(TA, TA + part, core_off(b + k, pp + t0, GS), make_float4(ap[t0], ap[t0 + 1], ap[t0 + 2], ap[t0 + 3]));
       }
     }
     fence_smem_to_async();
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
+      const uint32_t offH = (uint32_t)(Cp / 8) * GS, offT = (uint32_t)(b / 8) * GS;
       for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
-        const uint32_t cbo = (uint32_t)(k8 >> 2), ko = (uint32_t)(k8 & 3) * 32u;
+        const uint32_t ko = (uint32_t)k8 * 256u;
         const uint32_t acc = (first && k8 == 0) ? 0u : 1u;
-        umma_tf32(D1, umma_desc(sTG + cbo * cbG + ko, 0u, 1024u, 2), umma_desc(sTX + cbo * cbX + ko, 0u, 1024u, 2), id1, acc);
-        umma_tf32(D2, umma_desc(sTA + cbo * cbA + ko, 0u, 1024u, 2),
-                  umma_desc(sTX + cbo * cbX + (uint32_t)(Cp / 8) * 1024u + ko, 0u, 1024u, 2), id2, acc);
-        umma_tf32(D3, umma_desc(sTG + cbo * cbG + (uint32_t)(b / 8) * 1024u + ko, 0u, 1024u, 2),
-                  umma_desc(sTY + cbo * cbY + ko, 0u, 1024u, 2), id3, acc);
+        // K-major, no swizzle: LBO = next 4 positions (128 B), SBO = next 8 rows (GS)
+        const uint64_t gh = umma_desc(sTG + ko, 128u, GS, 0), gl = umma_desc(sTG + part + ko, 128u, GS, 0);
+        const uint64_t xh = umma_desc(sTX + ko, 128u, GS, 0), xl = umma_desc(sTX + part + ko, 128u, GS, 0);
+        umma_tf32(D1, gh, xh, id1, acc); umma_tf32(D1, gh, xl, id1, 1u); umma_tf32(D1, gl, xh, id1, 1u);
+        const uint64_t ah = umma_desc(sTA + ko, 128u, GS, 0), al = umma_desc(sTA + part + ko, 128u, GS, 0);
+        const uint64_t hh = umma_desc(sTX + offH + ko, 128u, GS, 0), hl = umma_desc(sTX + part + offH + ko, 128u, GS, 0);
+        umma_tf32(D2, ah, hh, id2, acc); umma_tf32(D2, ah, hl, id2, 1u); umma_tf32(D2, al, hh, id2, 1u);
+        const uint64_t th = umma_desc(sTG + offT + ko, 128u, GS, 0), tl = umma_desc(sTG + part + offT + ko, 128u, GS, 0);
+        const uint64_t yh = umma_desc(sTY + ko, 128u, GS, 0), yl = umma_desc(sTY + part + ko, 128u, GS, 0);
+        umma_tf32(D3, th, yh, id3, acc); umma_tf32(D3, th, yl, id3, 1u); umma_tf32(D3, tl, yh, id3, 1u);
       }
       umma_commit(smem_u32(&bar));
     }
@@ -214,13 +249,13 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
     const int blk = bi * a.J + blockIdx.x;
     const int row = (warp & 3) * 32 + (tid & 31);
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    const int half = warp >> 2;  // the four warpgroups split the column groups
+    const int quarter = warp >> 2;  // the four warpgroups split the column groups
     float* wres = a.p_res + (int64_t)blk * a.wg_stride;
     float* wmc = a.p_mc + (int64_t)blk * a.mc_stride;
     int cg = 0;
     for (int c0 = 0; c0 < N1; c0 += 8, ++cg) {
       float v[8];
-      if ((cg & 3) != half) continue;
+      if ((cg & 3) != quarter) continue;
       tmem_ld8(D1 + lane_base + c0, v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -235,7 +270,7 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
     cg = 0;
     for (int c0 = 0; c0 < N2; c0 += 8, ++cg) {
       float v[8];
-      if ((cg & 3) != half) continue;
+      if ((cg & 3) != quarter) continue;
       tmem_ld8(D2 + lane_base + c0, v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -251,7 +286,7 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
     cg = 0;
     for (int c0 = 0; c0 < N3; c0 += 8, ++cg) {
       float v[8];
-      if ((cg & 3) != half) continue;
+      if ((cg & 3) != quarter) continue;
       tmem_ld8(D3 + lane_base + c0, v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -272,7 +307,7 @@ bool tc_wgrad_supported(const Plan& p) {
   if (off && (atoi(off) & 2)) return false;
   const int full = MSGAT_F_RES | MSGAT_F_CMIX | MSGAT_F_SMIX;
   const int b = p.Oc;
-  return p.precision == MSGAT_PREC_TF32 && (p.flags & full) == full && p.n_conv == 2 && p.Oc == p.Ot && p.Ot == p.Os &&
+  return (p.flags & full) == full && p.n_conv == 2 && p.Oc == p.Ot && p.Ot == p.Os &&
          b % 8 == 0 && b >= 8 && b <= 24 && p.C >= 1 && p.C <= 72 && p.O <= 72 &&
          p.dil[0] >= 1 && p.dil[0] < 12 && p.dil[1] >= 1 && p.dil[1] < 12;
 }
