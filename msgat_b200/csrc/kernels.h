@@ -18,7 +18,7 @@ bool tc_apply_supported(const Plan& p);
 bool tc_wgrad_supported(const Plan& p);
 int tc_wgrad_blocks_per_sample(const Plan& p);
 int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
-                    const float* saved, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
+                    const float* saved, const float* tcA, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream);
 int launch_tc_apply(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
                     float* saved, void* stream);

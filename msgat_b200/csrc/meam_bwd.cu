@@ -44,6 +44,7 @@ struct BwdArgs {
   float *bias_part, *ln_part, *delta, *dSnz, *dx;
   double* dPt_part;
   int nbias, arena_floats, S;
+  float* tcA;  // [B,3b,N,12] dA_now | dA_past | GZ for the tensor-core weight-gradient kernel (null: not used)
   int skip_wgrad;  // weight gradients come from the tensor-core kernel (tc_wgrad.cu) instead
 };
 
@@ -236,6 +237,31 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       for (int i = a.n_conv - 1; i >= 0; --i) {
         const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
         const float* in = i == 0 ? OT : Y[i - 1];
+        if (a.tcA && i == 0) {
+          // dy = dY1 here.  The first conv sits behind the temporal mix, which commutes with it:
+          // y1 = Pt a_now + Pt(t-d1) a_past with a = W1 h, so the weight gradients contract
+          // dA_now[k,j] = sum_t Pt[t,j] dY1[k,t] and dA_past[k,j] = sum_{t>=d1} Pt[t-d1,j] dY1[k,t] with h.
+          const int d1 = a.dil[0];
+          for (int r = tid; r < a.Ot * NT; r += T) {
+            const int k = r / NT, nl = r - k * NT, n = n0 + nl;
+            if (n >= a.N) continue;
+            const float* q = dy + k * PS + nl * 12;
+            float v[12], an[12], ap[12];
+            for (int t = 0; t < 12; ++t) v[t] = q[t];
+            for (int j = 0; j < 12; ++j) {
+              float s1 = 0.f, s2 = 0.f;
+              for (int t = 0; t < 12; ++t) s1 = fmaf(Pt[t * 12 + j], v[t], s1);
+              for (int t = d1; t < 12; ++t) s2 = fmaf(Pt[(t - d1) * 12 + j], v[t], s2);
+              an[j] = s1; ap[j] = s2;
+            }
+            float* o1 = a.tcA + (((int64_t)b * 3 * a.Ot + k) * a.N + n) * 12;
+            float* o2 = a.tcA + (((int64_t)b * 3 * a.Ot + a.Ot + k) * a.N + n) * 12;
+            st4(o1, make_float4(an[0], an[1], an[2], an[3])); st4(o1 + 4, make_float4(an[4], an[5], an[6], an[7]));
+            st4(o1 + 8, make_float4(an[8], an[9], an[10], an[11]));
+            st4(o2, make_float4(ap[0], ap[1], ap[2], ap[3])); st4(o2 + 4, make_float4(ap[4], ap[5], ap[6], ap[7]));
+            st4(o2 + 8, make_float4(ap[8], ap[9], ap[10], ap[11]));
+          }
+        }
         if (!a.skip_wgrad) {
           wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 0], dy, in, PS, PQ, a.dil[i], a.S);
           wgrad_accum<RBT>(acc, a.jobs[JOB_CONV + 2 * i + 1], dy, in, PS, PQ, -1, a.S);
@@ -312,6 +338,9 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
           }
         }
         for (int j = 0; j < 4; ++j) if (o0 + j < a.Os) st4(GZ + (o0 + j) * PS + nl * 12 + t0, d[j]);
+        if (a.tcA && n < a.N)
+          for (int j = 0; j < 4; ++j)
+            if (o0 + j < a.Os) st4(a.tcA + (((int64_t)b * 3 * a.Os + 2 * a.Os + o0 + j) * a.N + n) * 12 + t0, d[j]);
       }
       __syncthreads();
       for (int it = tid; it < chC * PQ; it += T) {
@@ -740,7 +769,7 @@ struct BwdLayout {
   int64_t WGT;  // floats of weight-gradient partial per thread block
   int64_t off_job[NJOBS];
   int64_t o_G, o_wg, o_bias, o_ln, o_dMc, o_dPt, o_delta, o_dSnz, o_dqd, o_dqs, o_dK, o_dqc, o_caw, o_Wc, o_Wg,
-      o_pat, o_pas, o_pan, total;
+      o_pat, o_pas, o_pan, o_tcA, total;
   WJob jobs[NJOBS];
 };
 
@@ -828,6 +857,10 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   L.o_pat = o; o += rup4l(2 * (int64_t)L.nblk4 * p.C);  // fp64 partials of the alpha gradients
   L.o_pas = o; o += rup4l(2 * (int64_t)L.nblk4 * p.C);
   L.o_pan = o; o += rup4l(BN);
+  L.o_tcA = o;
+#ifndef MSGAT_EMU
+  if (tc_wgrad_supported(p)) o += rup4l(BN * 12 * 3 * p.Ot);
+#endif
   L.total = o;
   return 0;
 }
@@ -882,6 +915,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
     a.S = L.S;
     a.skip_wgrad = tc_w ? 1 : 0;
+    a.tcA = tc_w ? scratch + L.o_tcA : nullptr;
 #define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
     if (L.RBT == 2) {
       if (L.NT == 16) BWD_CASE(16, 2); else if (L.NT == 8) BWD_CASE(8, 2); else BWD_CASE(4, 2);
@@ -893,7 +927,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
 #ifndef MSGAT_EMU
   if (tc_w) {
     float* wg = scratch + L.o_wg;
-    launch_tc_wgrad(p, prm, adj, x, G, saved, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
+    launch_tc_wgrad(p, prm, adj, x, G, saved, scratch + L.o_tcA, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
                     wg + L.off_job[JOB_CONV + 1], wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT,
                     scratch + L.o_dMc, (int64_t)p.Oc * p.C, stream);
   }

@@ -7,6 +7,7 @@
 //   dW2now/past  = sum_p G_t[o,p] Y1[k,p] / Y1[k,p-d2]   second conv
 // with G the masked upstream gradient [cacn | tacn | gacn], H = LayerNorm_T(X), Y1 the first
 // conv's output (saved by the forward), GZ the transposed sparse aggregation of G_s, and
+// (both computed and written to HBM by k_bwd_main, which has them in shared memory anyway)
 //   dY1[k,t] = sum_o W2now[o,k] G_t[o,t] + W2past[o,k] G_t[o,t+d2],
 //   dA_now[k,i] = sum_t Pt[t,i] dY1[k,t],  dA_past[k,i] = sum_{t>=d1} Pt[t-d1,i] dY1[k,t].
 //
@@ -33,9 +34,8 @@
 struct TcWgradArgs {
   const float* x; int64_t x_sb, x_sc;
   const float* G;   // masked dout [B,O,N,12]
-  int C, Cp, N, O, b, ntile, J, d1, d2, nnz, has_ln;
-  const float *ln_w, *ln_b, *c2_w, *Pt, *Y1, *pw;
-  const int32_t *csc_ptr, *csc_row, *csc_eid;
+  int C, Cp, N, O, b, ntile, J, d2, has_ln;
+  const float *ln_w, *ln_b, *Y1, *tcA;
   float *p_res, *p_ws, *p_c1past, *p_c1now, *p_c2past, *p_c2now;  // partial bases (block 0), row-major
   int64_t wg_stride;                                             // floats between consecutive blocks
   float* p_mc; int64_t mc_stride;
@@ -50,7 +50,7 @@ static inline size_t tcw_tiles_bytes(int C, int O, int b) {
 
 size_t tc_wgrad_smem(int C, int O, int b) {
   size_t s = 2 * tcw_tiles_bytes(C, O, b) + TCW_SLACK;
-  s += ((size_t)2 * b * b + 144 * 2 + 24 + 8) * 4;   // W2 taps, Pt, Ptd, ln, mbarrier + TMEM slot
+  s += (24 + 8) * 4;   // ln, mbarrier + TMEM slot
   return s + 1024;
 }
 
@@ -79,23 +79,13 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   unsigned char* TX = TG + szG;         // [2Cp][48]          X rows 0..Cp, H rows Cp..2Cp
   unsigned char* TA = TX + szX;         // [3b][48]           dA_now | dA_past | GZ
   unsigned char* TY = TA + szA;         // [2b][48]           Y1 | shift_d2(Y1)
-  float* W2n = reinterpret_cast<float*>(smem + 2 * part + TCW_SLACK);  // [o][k] tap 1
-  float* W2p = W2n + b * b;                                            // [o][k] tap 0
-  float* Pt = W2p + b * b;
-  float* Ptd = Pt + 144;
-  float* LW = Ptd + 144;
+  float* LW = reinterpret_cast<float*>(smem + 2 * part + TCW_SLACK);
   uint64_t& bar = *reinterpret_cast<uint64_t*>(LW + 24);
   uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(LW + 26);
 
   // zero all operand tiles once: pad rows (C..Cp) and the slack must be finite
   for (int i = tid; i < (int)((2 * part + TCW_SLACK) / 16); i += TCW_THREADS)
     reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int i = tid; i < b * b; i += TCW_THREADS) { W2n[i] = a.c2_w[i * 2 + 1]; W2p[i] = a.c2_w[i * 2]; }
-  for (int i = tid; i < 144; i += TCW_THREADS) {
-    const int t = i / 12, j = i - t * 12;
-    Pt[i] = a.Pt[(int64_t)bi * 144 + i];
-    Ptd[i] = t >= a.d1 ? a.Pt[(int64_t)bi * 144 + (t - a.d1) * 12 + j] : 0.f;
-  }
   if (tid < 12) { LW[tid] = a.has_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = a.has_ln ? a.ln_b[tid] : 0.f; }
   if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
@@ -110,7 +100,7 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   const float* xb = a.x + bi * a.x_sb;
   const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
   const float* Yb = a.Y1 + (int64_t)bi * b * a.N * 12;
-  const float* pwb = a.pw + (int64_t)bi * a.nnz;
+  const float* Ab = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
   uint32_t phase = 0;
   int first = 1;
 
@@ -172,52 +162,12 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
         st_split(TY, TY + part, core_off(b + o, pp + t0, GS), s);
       }
     }
-    // ---- GZ[o][i] = sum_n A[n,i] g_s[o][n]  (transpose of attention.py:36 through the CSC view)
-    for (int i = tid; i < b * 12; i += TCW_THREADS) {
-      const int o = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, nl = p4 / 12, t0 = p4 - nl * 12, n = n0 + nl;
-      float4 d = f4zero();
-      if (n < a.N) {
-        const int k1 = a.csc_ptr[n + 1];
-        for (int k = a.csc_ptr[n]; k < k1; ++k)
-          fma4(d, pwb[a.csc_eid[k]], ld4(Gb + ((int64_t)(2 * b + o) * a.N + a.csc_row[k]) * 12 + t0));
-      }
-      st_split(TA, TA + part, core_off(2 * b + o, p4, GS), d);
-    }
-    __syncthreads();
-    // ---- dY1 (transpose of the second conv), then dA_now / dA_past (transpose of the temporal mix)
-    for (int i = tid; i < b * TCW_NT; i += TCW_THREADS) {
-      const int k = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, pp = nl * 12;
-      float dy[12];
-#pragma unroll
-      for (int t = 0; t < 12; ++t) dy[t] = 0.f;
-      for (int o = 0; o < b; ++o) {
-        const float wn = W2n[o * b + k], wp = W2p[o * b + k];
-        float g[12];
-#pragma unroll
-        for (int t0 = 0; t0 < 12; t0 += 4) {
-          const uint32_t off = core_off(b + o, pp + t0, GS);
-          const float4 vh = ld4(reinterpret_cast<const float*>(TG + off)), vl = ld4(reinterpret_cast<const float*>(TG + part + off));
-          g[t0] = vh.x + vl.x; g[t0 + 1] = vh.y + vl.y; g[t0 + 2] = vh.z + vl.z; g[t0 + 3] = vh.w + vl.w;
-        }
-#pragma unroll
-        for (int t = 0; t < 12; ++t) {
-          dy[t] = fmaf(wn, g[t], dy[t]);
-          if (t + a.d2 < 12) dy[t] = fmaf(wp, g[t + a.d2 < 12 ? t + a.d2 : 11], dy[t]);
-        }
-      }
-      float an[12], ap[12];
-#pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        float s = 0.f, q = 0.f;
-#pragma unroll
-        for (int t = 0; t < 12; ++t) { s = fmaf(Pt[t * 12 + j], dy[t], s); q = fmaf(Ptd[t * 12 + j], dy[t], q); }
-        an[j] = s; ap[j] = q;
-      }
-#pragma unroll
-      for (int t0 = 0; t0 < 12; t0 += 4) {
-        st_split(TA, TA + part, core_off(k, pp + t0, GS), make_float4(an[t0], an[t0 + 1], an[t0 + 2], an[t0 + 3]));
-        st_split(TA, TA + part, core_off(b + k, pp + t0, GS), make_float4(ap[t0], ap[t0 + 1], ap[t0 + 2], ap[t0 + 3]));
-      }
+    // ---- dA_now | dA_past | GZ rows, written by k_bwd_main (meam_bwd.cu) for this kernel
+    for (int i = tid; i < 3 * b * 12; i += TCW_THREADS) {
+      const int r = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, n = n0 + p4 / 12;
+      float4 v = f4zero();
+      if (n < a.N) v = ld4(Ab + ((int64_t)r * a.N + n0) * 12 + p4);
+      st_split(TA, TA + part, core_off(r, p4, GS), v);
     }
     fence_smem_to_async();
     __syncthreads();
@@ -320,16 +270,14 @@ int tc_wgrad_blocks_per_sample(const Plan& p) {
 }
 
 int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
-                    const float* saved, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
+                    const float* saved, const float* tcA, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream) {
   TcWgradArgs a;
   a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
   a.C = p.C; a.Cp = rup8(p.C); a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TCW_NT - 1) / TCW_NT;
   a.J = tc_wgrad_blocks_per_sample(p);
-  a.d1 = p.dil[0]; a.d2 = p.dil[1]; a.nnz = p.nnz; a.has_ln = (p.flags & MSGAT_F_LN) ? 1 : 0;
-  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.c2_w = prm->conv_w[1];
-  a.Pt = saved + p.o_Pt; a.Y1 = saved + p.o_Y1; a.pw = saved + p.o_pw;
-  a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+  a.d2 = p.dil[1]; a.has_ln = (p.flags & MSGAT_F_LN) ? 1 : 0;
+  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.Y1 = saved + p.o_Y1; a.tcA = tcA;
   a.p_res = p_res; a.p_ws = p_ws; a.p_c1past = p_c1past; a.p_c1now = p_c1now; a.p_c2past = p_c2past; a.p_c2now = p_c2now;
   a.wg_stride = wg_stride; a.p_mc = p_mc; a.mc_stride = mc_stride;
   MSGAT_LAUNCH(k_tc_wgrad, dim3(a.J, p.B), dim3(TCW_THREADS), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
