@@ -189,7 +189,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=__import__("datetime").timedelta(seconds=180))
     torch.manual_seed(0)
     adj = synthetic.make_adjacency(args.config)
     model = getattr(models, args.model)(n_components=shape["M"], in_channels=shape["C"], in_timesteps=12,
@@ -255,13 +255,16 @@ def main():
     # per-kernel device time (CUDA events recorded by the library on the launch stream)
     roof = None
     kernels = {}
+    # every rank runs the profiled steps (they contain the gradient all-reduce); rank 0 records
+    torch.cuda.synchronize()
     if rank == 0:
-        torch.cuda.synchronize()
         _lib.profile(True)
-        for _ in range(args.profile_steps):
-            step(*devb)
-        torch.cuda.synchronize()
+    for _ in range(args.profile_steps):
+        step(*devb)
+    torch.cuda.synchronize()
+    if rank == 0:
         _lib.profile(False)
+    if rank == 0:
         rep = _lib.profile_report()
         total = sum(v[1] for v in rep.values()) or 1.0
         top = max(rep.items(), key=lambda kv: kv[1][1])

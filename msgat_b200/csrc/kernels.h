@@ -15,6 +15,9 @@ int64_t meam_backward_scratch(Plan& p);
 void msgat_set_error(const char* fmt, ...);
 // tensor-core (tcgen05 kind::tf32) kernels, tc_*.cu: MSGAT_PREC_TF32 on the layer-2 MEAM shape
 bool tc_apply_supported(const Plan& p);
+bool tc_apply3_supported(const Plan& p);
+int launch_tc_apply3(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
+                     float* saved, void* stream);
 bool tc_wgrad_supported(const Plan& p);
 int tc_wgrad_blocks_per_sample(const Plan& p);
 int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,

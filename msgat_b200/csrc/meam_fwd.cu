@@ -396,6 +396,7 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
   if (p.Os) launch_sstats(p, prm, adj, saved, stream);
 #ifndef MSGAT_EMU
   if (tc_apply_supported(p)) return launch_tc_apply(p, prm, adj, x, out, saved, stream);
+  if (tc_apply3_supported(p)) return launch_tc_apply3(p, prm, adj, x, out, saved, stream);
 #endif
   {
     ApplyArgs a;

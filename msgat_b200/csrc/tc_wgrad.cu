@@ -63,7 +63,8 @@ TC_DEV float tf32_rna(float x) {
 TC_DEV void st_split(unsigned char* hi, unsigned char* lo, uint32_t off, float4 v) {
   float4 h = make_float4(tf32_rna(v.x), tf32_rna(v.y), tf32_rna(v.z), tf32_rna(v.w));
   st4(reinterpret_cast<float*>(hi + off), h);
-  st4(reinterpret_cast<float*>(lo + off), make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+  // lo is rounded (not truncated by the tensor core) to TF32: residual 2^-23 |v|, unbiased
+  st4(reinterpret_cast<float*>(lo + off), make_float4(tf32_rna(v.x - h.x), tf32_rna(v.y - h.y), tf32_rna(v.z - h.z), tf32_rna(v.w - h.w)));
 }
 
 __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
