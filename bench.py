@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's)")
     ap.add_argument("--model", default="msgat72")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32"])
-    ap.add_argument("--cpu-sample", type=int, default=1, help="samples per step of the CPU baseline")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="samples per step of the CPU baseline (0: the full per-GPU batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
     return ap.parse_args()
@@ -105,7 +105,7 @@ def cpu_reference_arm(args, shape, steps, warmup):
     from oracle import msgat_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    Bs = max(1, args.cpu_sample)
+    Bs = args.cpu_sample if args.cpu_sample > 0 else (args.batch or shape["B"])
     adj = synthetic.make_adjacency(args.config)
     p = O.init_params(args.model, shape["M"], shape["C"], adj)
     train = [v.requires_grad_(True) for k, v in p.items() if k != "adj"]
@@ -142,7 +142,10 @@ def algorithmic_bytes(kernel: str, B: int, N: int):
     table = {
         "k_prep": (C + Cz + 2) * A,
         "k_apply": (C + Cz + O) * A,
-        "k_bwd_main": (2 * C + O + b + Cz) * A,
+        "k_tc_apply": (C + Cz + O + b) * A,            # + Y1 kept for the weight gradients
+        "k_tc_apply3": (C + Cz + O + b) * A,
+        "k_bwd_main": (2 * C + O + Cz + 3 * b) * A,    # x, dout, Z gather, dx + dA_now/dA_past/GZ handed to k_tc_wgrad
+        "k_tc_wgrad": (C + O + b + 3 * b) * A,         # x, dout, Y1, dA_now/dA_past/GZ
         "k_bwd_fix": 3 * C * A,
         "k_relu_mask": 3 * O * A,
         "k_head_fwd": C * A,
@@ -277,8 +280,13 @@ def main():
         ab = algorithmic_bytes(top[0], Bper, shape["N"])
         avg_ms = top[1][1] / top[1][0]
         ach = None if ab is None else ab / (avg_ms * 1e-3) / 1e9
+        traffic = None  # dram read+write bytes per launch from the committed ncu --set full capture
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                traffic = json.load(f).get(f"{args.config}:{args.precision}", {}).get(top[0])
         roof = {"kernel": top[0], "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": None if ach is None else ach / peak, "traffic": None, "peak_source": src,
+                "frac": None if ach is None else ach / peak, "traffic": traffic, "peak_source": src,
                 "algorithmic_bytes_per_launch": ab, "avg_launch_ms": avg_ms, "share_of_device_time": top[1][1] / total,
                 "my_kernels_ms_per_step": total / args.profile_steps}
     if rank != 0:

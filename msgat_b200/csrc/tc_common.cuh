@@ -42,6 +42,7 @@ TC_DEV uint32_t sw128b32_off(int r, int p, uint32_t cb) {
 TC_DEV void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
+TC_DEV void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 TC_DEV void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 // Spins on the phase parity; a wait that can never complete traps instead of hanging the device.
 TC_DEV void mbar_wait(uint32_t bar, uint32_t parity) {

@@ -16,20 +16,24 @@
 // accumulation in TMEM; the dropped lo*lo term is 2^-24 relative.  That gives fp32-grade
 // gradients from the tensor cores, so the kernel serves the fp32 path too.
 //
-// Positions are contiguous in HBM, so every operand is K-major.  A tile is 4 nodes = 48
+// Positions are contiguous in HBM, so every operand is K-major.  A tile is 2 nodes = 24
 // positions in the unswizzled core-matrix layout (8 rows x 4 positions = 128 contiguous bytes,
-// tc_common.cuh:core_off); accumulators stay in TMEM across all tiles of the CTA and are
+// tc_common.cuh:core_off), double-buffered so that staging tile i+1 (global loads, LayerNorm,
+// hi/lo split) overlaps the MMAs of tile i; accumulators stay in TMEM across all tiles of the CTA and are
 // flushed once as per-CTA partials (k_reduce sums them in a fixed order).
 #include <stdlib.h>
 #include "kernels.h"
 #include "tc_common.cuh"
 #include "tile_ops.cuh"
 
-#define TCW_NT 4
-#define TCW_P 48
+#define TCW_NT 2
+#define TCW_P (TCW_NT * 12)
+#define TCW_P4 (TCW_P / 4)
 #define TCW_GS (TCW_P * 32)  // bytes of one 8-row group of a tile
-#define TCW_THREADS 512
-#define TCW_SLACK (28 * 1024)
+#define TCW_THREADS 512      // staging (producer) threads; warp 16 issues the MMAs
+#define TCW_ALL (TCW_THREADS + 32)
+#define TCW_STAGES 2         // operand tiles are double-buffered: staging tile i+1 overlaps the MMAs of tile i
+#define TCW_SLACK (16 * TCW_GS)  // an M=128 operand descriptor reads 16 row groups from its base
 
 struct TcWgradArgs {
   const float* x; int64_t x_sb, x_sc;
@@ -49,8 +53,8 @@ static inline size_t tcw_tiles_bytes(int C, int O, int b) {
 }
 
 size_t tc_wgrad_smem(int C, int O, int b) {
-  size_t s = 2 * tcw_tiles_bytes(C, O, b) + TCW_SLACK;
-  s += (24 + 8) * 4;   // ln, mbarrier + TMEM slot
+  size_t s = TCW_STAGES * 2 * tcw_tiles_bytes(C, O, b) + TCW_SLACK;
+  s += (24 + 12) * 4;  // ln, four mbarriers + TMEM slot
   return s + 1024;
 }
 
@@ -67,7 +71,7 @@ TC_DEV void st_split(unsigned char* hi, unsigned char* lo, uint32_t off, float4 
   st4(reinterpret_cast<float*>(lo + off), make_float4(tf32_rna(v.x - h.x), tf32_rna(v.y - h.y), tf32_rna(v.z - h.z), tf32_rna(v.w - h.w)));
 }
 
-__global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
+__global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int C = a.C, Cp = a.Cp, O = a.O, b = a.b, tid = threadIdx.x, warp = tid >> 5, bi = blockIdx.y;
@@ -76,19 +80,22 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   const uint32_t szG = (uint32_t)(Op / 8) * GS, szX = (uint32_t)(2 * Cp / 8) * GS, szA = (uint32_t)(3 * b / 8) * GS,
                  szY = (uint32_t)(2 * b / 8) * GS;
   const uint32_t part = szG + szX + szA + szY;  // hi part, then the lo part in the same order
-  unsigned char* TG = smem;             // [O][48]            G
-  unsigned char* TX = TG + szG;         // [2Cp][48]          X rows 0..Cp, H rows Cp..2Cp
-  unsigned char* TA = TX + szX;         // [3b][48]           dA_now | dA_past | GZ
-  unsigned char* TY = TA + szA;         // [2b][48]           Y1 | shift_d2(Y1)
-  float* LW = reinterpret_cast<float*>(smem + 2 * part + TCW_SLACK);
-  uint64_t& bar = *reinterpret_cast<uint64_t*>(LW + 24);
-  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(LW + 26);
+  // stage s at smem + s * 2 * part: [O][P] G, [2Cp][P] X rows 0..Cp | H rows Cp..2Cp,
+  // [3b][P] dA_now | dA_past | GZ, [2b][P] Y1 | shift_d2(Y1); hi part then lo part
+  float* LW = reinterpret_cast<float*>(smem + TCW_STAGES * 2 * part + TCW_SLACK);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(LW + 24);   // stage drained: the MMAs that read it retired
+  uint64_t* full = reinterpret_cast<uint64_t*>(LW + 28);   // stage staged: one arrival per producer warp
+  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(LW + 32);
 
   // zero all operand tiles once: pad rows (C..Cp) and the slack must be finite
-  for (int i = tid; i < (int)((2 * part + TCW_SLACK) / 16); i += TCW_THREADS)
+  for (int i = tid; i < (int)((TCW_STAGES * 2 * part + TCW_SLACK) / 16); i += TCW_ALL)
     reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   if (tid < 12) { LW[tid] = a.has_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = a.has_ln ? a.ln_b[tid] : 0.f; }
-  if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
+  if (tid == 0) {
+    mbar_init(smem_u32(&bars[0]), 1); mbar_init(smem_u32(&bars[1]), 1);
+    mbar_init(smem_u32(&full[0]), TCW_THREADS / 32); mbar_init(smem_u32(&full[1]), TCW_THREADS / 32);
+    mbar_fence_init();
+  }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
   tc_fence_before_sync();
   __syncthreads();
@@ -97,106 +104,161 @@ __global__ void __launch_bounds__(TCW_THREADS, 1) k_tc_wgrad(TcWgradArgs a) {
   const int N1 = (2 * Cp + 15) & ~15, N2 = (Cp + 15) & ~15, N3 = 2 * b;
   const uint32_t D1 = tm, D2 = tm + 160, D3 = tm + 256;
   const uint32_t id1 = umma_idesc_tf32(128, N1, 0, 0), id2 = umma_idesc_tf32(128, N2, 0, 0), id3 = umma_idesc_tf32(128, N3, 0, 0);
-  const uint32_t sTG = smem_u32(TG), sTX = smem_u32(TX), sTA = smem_u32(TA), sTY = smem_u32(TY);
   const float* xb = a.x + bi * a.x_sb;
   const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
   const float* Yb = a.Y1 + (int64_t)bi * b * a.N * 12;
   const float* Ab = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
-  uint32_t phase = 0;
-  int first = 1;
+  const int ntl = (a.ntile - (int)blockIdx.x + a.J - 1) / a.J;   // tiles of this CTA (>= 1)
 
-  // Work items put the row-within-group index in the low 3 bits: 8 consecutive threads fill one
-  // 128-byte core matrix, a warp four consecutive ones -> conflict-free shared-memory stores.
-  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+  if (warp == TCW_THREADS / 32) {
+    // ---- MMA warp: one thread waits for a staged tile, issues its 27 MMAs and commits them to the
+    // stage's "drained" barrier.  Nothing else waits on this thread, so the producers run ahead.
+    if ((tid & 31) == 0) {
+      const uint32_t s0 = smem_u32(smem);
+      const uint32_t offH = (uint32_t)(Cp / 8) * GS, offT = (uint32_t)(b / 8) * GS;
+      // K-major, no swizzle: LBO = next 4 positions (128 B), SBO = next 8 rows (GS); stage 0, k = 0
+      const uint64_t gh0 = umma_desc(s0, 128u, GS, 0), gl0 = umma_desc(s0 + part, 128u, GS, 0);
+      const uint64_t xh0 = umma_desc(s0 + szG, 128u, GS, 0), xl0 = umma_desc(s0 + part + szG, 128u, GS, 0);
+      const uint64_t ah0 = umma_desc(s0 + szG + szX, 128u, GS, 0), al0 = umma_desc(s0 + part + szG + szX, 128u, GS, 0);
+      const uint64_t hh0 = umma_desc(s0 + szG + offH, 128u, GS, 0), hl0 = umma_desc(s0 + part + szG + offH, 128u, GS, 0);
+      const uint64_t th0 = umma_desc(s0 + offT, 128u, GS, 0), tl0 = umma_desc(s0 + part + offT, 128u, GS, 0);
+      const uint64_t yh0 = umma_desc(s0 + szG + szX + szA, 128u, GS, 0), yl0 = umma_desc(s0 + part + szG + szX + szA, 128u, GS, 0);
+      for (int it = 0; it < ntl; ++it) {
+        const int st = it & 1;
+        mbar_wait(smem_u32(&full[st]), (uint32_t)((it >> 1) & 1));
+        tc_fence_after_sync();
+        for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
+          const uint64_t d = (uint64_t)(((uint32_t)st * 2u * part + (uint32_t)k8 * 256u) >> 4);   // start-address field, 16-byte units
+          const uint32_t acc = (it == 0 && k8 == 0) ? 0u : 1u;
+          umma_tf32(D1, gh0 + d, xh0 + d, id1, acc); umma_tf32(D1, gh0 + d, xl0 + d, id1, 1u); umma_tf32(D1, gl0 + d, xh0 + d, id1, 1u);
+          umma_tf32(D2, ah0 + d, hh0 + d, id2, acc); umma_tf32(D2, ah0 + d, hl0 + d, id2, 1u); umma_tf32(D2, al0 + d, hh0 + d, id2, 1u);
+          umma_tf32(D3, th0 + d, yh0 + d, id3, acc); umma_tf32(D3, th0 + d, yl0 + d, id3, 1u); umma_tf32(D3, tl0 + d, yh0 + d, id3, 1u);
+        }
+        umma_commit(smem_u32(&bars[st]));
+      }
+    }
+  } else {
+  int it = 0;
+
+  // Work assignment, fixed for the whole kernel, every item one float4 (4 positions of one row):
+  //  * G and dA rows: flat items on warps 8..15 (row-within-group in the low 3 bits, so 8
+  //    consecutive threads fill one 128-byte core matrix and a warp four consecutive ones);
+  //  * X (+LayerNorm) and Y1 (+causal shift) rows: warp items of (8 rows) x (one node), lane =
+  //    row + 8 * quad with 24 lanes live; the LayerNorm statistics and the shifted taps move
+  //    between the three quads of a row by shuffles.  Items 0..15 go to warps 0..15, items
+  //    16..23 to warps 0..7, which evens out the instruction count per warp (the slowest warp
+  //    sets the time of a tile: everything meets at the barrier below).
+  const int lane = tid & 31;
+  const int ql = lane >> 3, rl = lane & 7;
+  uint32_t g_off[2], w_off[2], w_off2[2];
+  int g_go[2], g_nl[2], w_nl[2], w_kind[2];
+  int64_t w_go[2];
+  bool g_on[2], a_on[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int gi = tid - 256 + 256 * k;
+    const int r = (gi & 7) + 8 * (gi / (8 * TCW_P4)), p4 = ((gi >> 3) % TCW_P4) * 4;
+    g_on[k] = tid >= 256 && gi < Op * TCW_P4 && r < O;
+    a_on[k] = tid >= 256 && gi < 3 * b * TCW_P4;
+    g_off[k] = core_off(r, p4, GS); g_go[k] = r * a.N * 12 + p4; g_nl[k] = p4 / 12;
+    if (tid >= 256 && gi < Op * TCW_P4 && r >= O) g_on[k] = false;   // pad rows O..Op stay zero
+    const int nX = (Cp / 8) * TCW_NT, nY = (b / 8) * TCW_NT;
+    const int j = warp + 16 * k;
+    w_kind[k] = 0; w_off[k] = w_off2[k] = 0; w_go[k] = 0; w_nl[k] = 0;
+    if ((k == 0 || warp < 8) && ql < 3) {
+      if (j < nX) {
+        const int c = (j / TCW_NT) * 8 + rl, nl = j % TCW_NT;
+        if (c < C) {
+          w_kind[k] = 1; w_nl[k] = nl; w_go[k] = (int64_t)c * a.x_sc + nl * 12 + 4 * ql;
+          w_off[k] = szG + core_off(c, nl * 12 + 4 * ql, GS); w_off2[k] = szG + core_off(Cp + c, nl * 12 + 4 * ql, GS);
+        }
+      } else if (j < nX + nY) {
+        const int o = ((j - nX) / TCW_NT) * 8 + rl, nl = (j - nX) % TCW_NT;
+        w_kind[k] = 2; w_nl[k] = nl; w_go[k] = ((int64_t)o * a.N + nl) * 12 + 4 * ql;
+        w_off[k] = szG + szX + szA + core_off(o, nl * 12 + 4 * ql, GS);
+        w_off2[k] = szG + szX + szA + core_off(b + o, nl * 12 + 4 * ql, GS);
+      }
+    }
+  }
+  const float4 lw4 = a.has_ln && ql < 3 ? ld4(a.ln_w + 4 * ql) : make_float4(1.f, 1.f, 1.f, 1.f);
+  const float4 lb4 = a.has_ln && ql < 3 ? ld4(a.ln_b + 4 * ql) : f4zero();
+  const int qd = a.d2 >> 2, rd = a.d2 & 3;   // causal shift = qd whole quads + rd positions
+  // The global loads of tile i+1 are issued before tile i is staged (register prefetch): their
+  // latency hides behind the staging arithmetic and the wait for the stage to drain.
+  float4 pg[2], pa[2], pw[2];
+  auto prefetch = [&](int tile) {
     const int n0 = tile * TCW_NT;
-    // ---- G tile
-    for (int i = tid; i < Op * 12; i += TCW_THREADS) {
-      const int r = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, n = n0 + p4 / 12;
-      float4 v = f4zero();
-      if (r < O && n < a.N) v = ld4(Gb + ((int64_t)r * a.N + n0) * 12 + p4);
-      st_split(TG, TG + part, core_off(r, p4, GS), v);
-    }
-    // ---- X rows and their LayerNorm (msgat.py:122)
-    for (int i = tid; i < Cp * TCW_NT; i += TCW_THREADS) {
-      const int c = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, n = n0 + nl;
-      if (c >= C) continue;
-      float4 u = f4zero(), v = f4zero(), w = f4zero();
-      if (n < a.N) { const float* s = xb + c * a.x_sc + (int64_t)n * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
-      const int pp = nl * 12;
-      st_split(TX, TX + part, core_off(c, pp, GS), u);
-      st_split(TX, TX + part, core_off(c, pp + 4, GS), v);
-      st_split(TX, TX + part, core_off(c, pp + 8, GS), w);
-      if (n < a.N && a.has_ln) {
-        float mu = (u.x + u.y + u.z + u.w + v.x + v.y + v.z + v.w + w.x + w.y + w.z + w.w) * (1.0f / 12.0f);
-        u.x -= mu; u.y -= mu; u.z -= mu; u.w -= mu; v.x -= mu; v.y -= mu; v.z -= mu; v.w -= mu;
-        w.x -= mu; w.y -= mu; w.z -= mu; w.w -= mu;
-        const float rs = rsqrtf((dot4(u, u) + dot4(v, v) + dot4(w, w)) * (1.0f / 12.0f) + LN_EPS);
-        u.x = u.x * rs * LW[0] + LW[12]; u.y = u.y * rs * LW[1] + LW[13]; u.z = u.z * rs * LW[2] + LW[14]; u.w = u.w * rs * LW[3] + LW[15];
-        v.x = v.x * rs * LW[4] + LW[16]; v.y = v.y * rs * LW[5] + LW[17]; v.z = v.z * rs * LW[6] + LW[18]; v.w = v.w * rs * LW[7] + LW[19];
-        w.x = w.x * rs * LW[8] + LW[20]; w.y = w.y * rs * LW[9] + LW[21]; w.z = w.z * rs * LW[10] + LW[22]; w.w = w.w * rs * LW[11] + LW[23];
-      }
-      st_split(TX, TX + part, core_off(Cp + c, pp, GS), u);
-      st_split(TX, TX + part, core_off(Cp + c, pp + 4, GS), v);
-      st_split(TX, TX + part, core_off(Cp + c, pp + 8, GS), w);
-    }
-    // ---- Y1 rows and their causal shift
-    for (int i = tid; i < b * TCW_NT; i += TCW_THREADS) {
-      const int o = (i & 7) + 8 * (i / (8 * TCW_NT)), nl = (i >> 3) % TCW_NT, n = n0 + nl;
-      float y[12];
+    const bool in = tile < a.ntile;
 #pragma unroll
-      for (int t = 0; t < 12; ++t) y[t] = 0.f;
-      if (n < a.N) {
-        const float* s = Yb + ((int64_t)o * a.N + n) * 12;
-        const float4 u = ld4(s), v = ld4(s + 4), w = ld4(s + 8);
-        y[0] = u.x; y[1] = u.y; y[2] = u.z; y[3] = u.w; y[4] = v.x; y[5] = v.y; y[6] = v.z; y[7] = v.w;
-        y[8] = w.x; y[9] = w.y; y[10] = w.z; y[11] = w.w;
-      }
-      const int pp = nl * 12;
-#pragma unroll
-      for (int t0 = 0; t0 < 12; t0 += 4) {
-        st_split(TY, TY + part, core_off(o, pp + t0, GS), make_float4(y[t0], y[t0 + 1], y[t0 + 2], y[t0 + 3]));
-        float4 s;
-        s.x = t0 >= a.d2 ? y[t0 - a.d2 < 0 ? 0 : t0 - a.d2] : 0.f;
-        s.y = t0 + 1 >= a.d2 ? y[t0 + 1 - a.d2 < 0 ? 0 : t0 + 1 - a.d2] : 0.f;
-        s.z = t0 + 2 >= a.d2 ? y[t0 + 2 - a.d2 < 0 ? 0 : t0 + 2 - a.d2] : 0.f;
-        s.w = t0 + 3 >= a.d2 ? y[t0 + 3 - a.d2 < 0 ? 0 : t0 + 3 - a.d2] : 0.f;
-        st_split(TY, TY + part, core_off(b + o, pp + t0, GS), s);
-      }
+    for (int k = 0; k < 2; ++k) {
+      pg[k] = pa[k] = pw[k] = f4zero();
+      const bool gin = in && n0 + g_nl[k] < a.N;
+      if (g_on[k] && gin) pg[k] = ld4(Gb + g_go[k] + (int64_t)n0 * 12);
+      if (a_on[k] && gin) pa[k] = ld4(Ab + g_go[k] + (int64_t)n0 * 12);
+      if (w_kind[k] && in && n0 + w_nl[k] < a.N) pw[k] = ld4((w_kind[k] == 1 ? xb : Yb) + w_go[k] + (int64_t)n0 * 12);
     }
-    // ---- dA_now | dA_past | GZ rows, written by k_bwd_main (meam_bwd.cu) for this kernel
-    for (int i = tid; i < 3 * b * 12; i += TCW_THREADS) {
-      const int r = (i & 7) + 8 * (i / 96), p4 = ((i >> 3) % 12) * 4, n = n0 + p4 / 12;
-      float4 v = f4zero();
-      if (n < a.N) v = ld4(Ab + ((int64_t)r * a.N + n0) * 12 + p4);
-      st_split(TA, TA + part, core_off(r, p4, GS), v);
+  };
+  prefetch(blockIdx.x);
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J, ++it) {
+    const int n0 = tile * TCW_NT, st = it & 1;
+    unsigned char* SB = smem + (size_t)st * 2 * part;   // stage base: G | X,H | dA,GZ | Y1,shift
+    unsigned char* TG = SB;
+    unsigned char* TX = TG + szG;
+    unsigned char* TA = TX + szX;
+    unsigned char* TY = TA + szA;
+    const float4 cg[2] = {pg[0], pg[1]}, ca[2] = {pa[0], pa[1]}, cw[2] = {pw[0], pw[1]};
+    prefetch(tile + a.J);
+    // the MMAs that read this stage two tiles ago must have retired before it is overwritten
+    if (it >= TCW_STAGES) mbar_wait(smem_u32(&bars[st]), (uint32_t)(((it >> 1) - 1) & 1));
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      // ---- X rows and their LayerNorm (msgat.py:122); Y1 rows and their causal shift.
+      // Whole warps take this branch or skip it (the item index depends on the warp only).
+      if ((k == 0 || warp < 8) && warp + 16 * k < (Cp / 8 + b / 8) * TCW_NT) {
+        const bool isx = warp + 16 * k < (Cp / 8) * TCW_NT;
+        const float4 v = cw[k];
+        if (w_kind[k]) st_split(SB, SB + part, w_off[k], v);
+        float4 o2;
+        if (isx) {
+          float sum = v.x + v.y + v.z + v.w;
+          sum += __shfl_xor_sync(0xffffffffu, sum, 8); sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+          const float mu = sum * (1.0f / 12.0f);
+          float4 d = make_float4(v.x - mu, v.y - mu, v.z - mu, v.w - mu);
+          float ss = ql < 3 ? dot4(d, d) : 0.f;
+          ss += __shfl_xor_sync(0xffffffffu, ss, 8); ss += __shfl_xor_sync(0xffffffffu, ss, 16);
+          const float rs = rsqrtf(ss * (1.0f / 12.0f) + LN_EPS);
+          o2 = v;
+          if (a.has_ln && n0 + w_nl[k] < a.N)
+            o2 = make_float4(d.x * rs * lw4.x + lb4.x, d.y * rs * lw4.y + lb4.y, d.z * rs * lw4.z + lb4.z, d.w * rs * lw4.w + lb4.w);
+        } else {
+          // shifted quad = y[4 ql + e - d2]: from quad (ql - qd) and, if rd > 0, the one before it
+          const int sb_ = lane - 8 * qd, sa_ = sb_ - 8;
+          float4 B, A;
+          B.x = __shfl_sync(0xffffffffu, v.x, sb_ & 31); B.y = __shfl_sync(0xffffffffu, v.y, sb_ & 31);
+          B.z = __shfl_sync(0xffffffffu, v.z, sb_ & 31); B.w = __shfl_sync(0xffffffffu, v.w, sb_ & 31);
+          A.x = __shfl_sync(0xffffffffu, v.x, sa_ & 31); A.y = __shfl_sync(0xffffffffu, v.y, sa_ & 31);
+          A.z = __shfl_sync(0xffffffffu, v.z, sa_ & 31); A.w = __shfl_sync(0xffffffffu, v.w, sa_ & 31);
+          if (sb_ < 0) B = f4zero();
+          if (sa_ < 0) A = f4zero();
+          o2 = rd == 0 ? B : rd == 1 ? make_float4(A.w, B.x, B.y, B.z) : rd == 2 ? make_float4(A.z, A.w, B.x, B.y)
+                                                                             : make_float4(A.y, A.z, A.w, B.x);
+        }
+        if (w_kind[k]) st_split(SB, SB + part, w_off2[k], o2);
+      }
+      // ---- G rows; dA_now | dA_past | GZ rows, written by k_bwd_main (meam_bwd.cu) for this kernel
+      if (g_on[k]) st_split(TG, TG + part, g_off[k], cg[k]);
+      if (a_on[k]) st_split(TA, TA + part, g_off[k], ca[k]);
     }
     fence_smem_to_async();
-    __syncthreads();
-    if (tid == 0) {
-      tc_fence_after_sync();
-      const uint32_t offH = (uint32_t)(Cp / 8) * GS, offT = (uint32_t)(b / 8) * GS;
-      for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
-        const uint32_t ko = (uint32_t)k8 * 256u;
-        const uint32_t acc = (first && k8 == 0) ? 0u : 1u;
-        // K-major, no swizzle: LBO = next 4 positions (128 B), SBO = next 8 rows (GS)
-        const uint64_t gh = umma_desc(sTG + ko, 128u, GS, 0), gl = umma_desc(sTG + part + ko, 128u, GS, 0);
-        const uint64_t xh = umma_desc(sTX + ko, 128u, GS, 0), xl = umma_desc(sTX + part + ko, 128u, GS, 0);
-        umma_tf32(D1, gh, xh, id1, acc); umma_tf32(D1, gh, xl, id1, 1u); umma_tf32(D1, gl, xh, id1, 1u);
-        const uint64_t ah = umma_desc(sTA + ko, 128u, GS, 0), al = umma_desc(sTA + part + ko, 128u, GS, 0);
-        const uint64_t hh = umma_desc(sTX + offH + ko, 128u, GS, 0), hl = umma_desc(sTX + part + offH + ko, 128u, GS, 0);
-        umma_tf32(D2, ah, hh, id2, acc); umma_tf32(D2, ah, hl, id2, 1u); umma_tf32(D2, al, hh, id2, 1u);
-        const uint64_t th = umma_desc(sTG + offT + ko, 128u, GS, 0), tl = umma_desc(sTG + part + offT + ko, 128u, GS, 0);
-        const uint64_t yh = umma_desc(sTY + ko, 128u, GS, 0), yl = umma_desc(sTY + part + ko, 128u, GS, 0);
-        umma_tf32(D3, th, yh, id3, acc); umma_tf32(D3, th, yl, id3, 1u); umma_tf32(D3, tl, yh, id3, 1u);
-      }
-      umma_commit(smem_u32(&bar));
-    }
-    first = 0;
-    mbar_wait(smem_u32(&bar), phase); phase ^= 1;
-    tc_fence_after_sync();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(smem_u32(&full[st]));
   }
+  }
+  // the last commit covers every MMA issued before it
+  mbar_wait(smem_u32(&bars[(ntl - 1) & 1]), (uint32_t)(((ntl - 1) >> 1) & 1));
+  tc_fence_after_sync();
   // ---- flush: TMEM lane = output row, columns = input channel
-  {
+  if (warp < TCW_THREADS / 32) {
     const int blk = bi * a.J + blockIdx.x;
     const int row = (warp & 3) * 32 + (tid & 31);
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
@@ -281,6 +343,6 @@ int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj
   a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.Y1 = saved + p.o_Y1; a.tcA = tcA;
   a.p_res = p_res; a.p_ws = p_ws; a.p_c1past = p_c1past; a.p_c1now = p_c1now; a.p_c2past = p_c2past; a.p_c2now = p_c2now;
   a.wg_stride = wg_stride; a.p_mc = p_mc; a.mc_stride = mc_stride;
-  MSGAT_LAUNCH(k_tc_wgrad, dim3(a.J, p.B), dim3(TCW_THREADS), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
+  MSGAT_LAUNCH(k_tc_wgrad, dim3(a.J, p.B), dim3(TCW_ALL), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
   return 0;
 }
