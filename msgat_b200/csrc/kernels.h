@@ -23,5 +23,10 @@ int tc_wgrad_blocks_per_sample(const Plan& p);
 int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
                     const float* saved, const float* tcA, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream);
+bool tc_dgrad_supported(const Plan& p);
+int tc_dgrad_blocks_per_sample(const Plan& p);
+int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
+                    const float* saved, float* tcA, float* dx, float* delta, float* dSnz, float* bias_part, int nbias,
+                    float* ln_part, double* dPt_part, void* stream);
 int launch_tc_apply(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
                     float* saved, void* stream);

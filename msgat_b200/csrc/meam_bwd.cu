@@ -828,6 +828,9 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
     if (occ < 1) occ = 1;
     L.J = pick_J(p.B, p.ntile_b, 148 * occ);
   }
+#ifndef MSGAT_EMU
+  if (tc_dgrad_supported(p)) L.J = tc_dgrad_blocks_per_sample(p);   // the tensor-core data-gradient kernel writes the per-block partials
+#endif
   L.nblk = L.J * p.B;
   L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
   L.J4 = pick_J(p.B, L.ntile4, 148 * 4); L.nblk4 = L.J4 * p.B;
@@ -879,9 +882,10 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   int rc = bwd_layout(p, L);
   if (rc) { msgat_set_error("MEAM backward: unsupported shape (code %d)", rc); return rc; }
   const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
-  bool tc_w = false;
+  bool tc_w = false, tc_d = false;
 #ifndef MSGAT_EMU
   tc_w = tc_wgrad_supported(p);
+  tc_d = tc_dgrad_supported(p);
 #endif
   const int Jw = tc_w ? tc_wgrad_blocks_per_sample(p) : L.J * L.S;  // weight-gradient partials per sample
   const float* G = dout;
@@ -894,7 +898,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
                  (float4*)(scratch + L.o_G), n4);
     G = scratch + L.o_G;
   }
-  {
+#ifndef MSGAT_EMU
+  if (tc_d) {
+    rc = launch_tc_dgrad(p, prm, adj, x, G, saved, scratch + L.o_tcA, dx, scratch + L.o_delta, scratch + L.o_dSnz, scratch + L.o_bias,
+                         L.nbias, scratch + L.o_ln, reinterpret_cast<double*>(scratch + L.o_dPt), stream);
+    if (rc) return rc;
+  }
+#endif
+  if (!tc_d) {
     BwdArgs a;
     a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
     a.C = p.C; a.N = p.N; a.O = p.O; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre;

@@ -16,7 +16,7 @@ struct Plan {
   int NTa, ntile_a;  // apply kernel
   int NTb, ntile_b;  // backward main kernel
   // saved layout (float offsets)
-  int64_t o_qs, o_qt, o_Z, o_m, o_l, o_E, o_U, o_Y1, o_pw, o_qc, o_Pc, o_Mc, o_K, o_Pt, saved_total;
+  int64_t o_qs, o_qt, o_Z, o_m, o_l, o_E, o_U, o_Y1, o_A2, o_pw, o_qc, o_Pc, o_Mc, o_K, o_Pt, saved_total;
   // forward scratch
   int64_t o_pqc, o_pK, fwd_scratch;
 };
@@ -75,6 +75,8 @@ static inline int make_plan(const msgat_meam_desc* d, int nnz, Plan* p) {
   p->o_U = o; o += d->Os ? rup4l(BN * 12) : 0;
   // output of the first conv of a two-conv chain, kept for the tensor-core weight-gradient kernel
   p->o_Y1 = o; o += (d->n_conv == 2) ? rup4l(BN * 12 * d->Ot) : 0;
+  // first-conv taps a_now | a_past = W1 h before the temporal mix, kept for dPt in the tensor-core data-gradient kernel
+  p->o_A2 = o; o += (d->n_conv == 2 && d->C >= 8) ? rup4l(BN * 12 * 2 * d->Ot) : 0;
   p->o_pw = o; o += rup4l((int64_t)d->B * nnz);
   p->o_qc = o; o += rup4l((int64_t)d->B * d->C * 12);
   p->o_Pc = o; o += rup4l((int64_t)d->B * d->C * d->C);

@@ -1,0 +1,458 @@
+// tc_dgrad.cu -- the node-local data gradients of a layer-2 MEAM on tcgen05 (3xTF32, see
+// tc_fwd3.cu), the backward counterpart of k_tc_apply3 and the replacement of k_bwd_main for
+// that shape.  With G the masked upstream gradient [cacn | tacn | gacn] (O = 3b rows) and
+// positions p = (node, t) on the TMEM lanes:
+//   D_x[p, c]  = sum_o G[o,p] Wres[o,c]                               d(residual)          msgat.py:116,131
+//   D_y[p, k'] = sum_o G_t[o,p] [W2now | W2past][o,k']                second conv, transposed  msgat.py:71-72
+//   dY1[k,t]   = D_y[(n,t),k] + D_y[(n,t+d2), b+k]
+//   dA_now[k,i] = sum_t Pt[t,i] dY1[k,t],  dA_past[k,i] = sum_{t>=d1} Pt[t-d1,i] dY1[k,t]    attention.py:66 transposed
+//   GZ[o,i]    = sum_n A[n,i] G_s[o,n]                                sparse transposed aggregation  attention.py:36
+//   D_h[p, c]  = sum_o G_c[o,p] Mc[o,c] + sum_j [dA_now;dA_past;GZ][j,p] [W1now;W1past;Ws][j,c]
+//   dx         = LayerNorm_T^T(D_h) + D_x   (masked by x > 0 when x is a ReLU output)       msgat.py:122
+// plus everything k_bwd_main hands on: dA_now/dA_past/GZ for k_tc_wgrad, bias / LayerNorm-affine /
+// dPt partials, and the spatial attention's dS at the adjacency non-zeros with its row sums delta.
+// dPt[t,i] = sum_{k,n} dY1[k,n,t] a_now[k,n,i] + dY1[k,n,t+d1] a_past[k,n,i] uses the first-conv
+// taps a = W1 h kept by the forward (saved A2).
+//
+// Tile = 8 nodes = 96 positions (one M = 128 block).  The G tile and later the [dA|GZ] tile are
+// the MN-major A operand (hi, lo); the four weight matrices are resident B operands.  Row-wise
+// work (temporal mixes, LayerNorm backward) goes through shared-memory staging rows of 12.
+#include <stdlib.h>
+#include "kernels.h"
+#include "tc_common.cuh"
+#include "tile_ops.cuh"
+
+#define TD_NT 8
+#define TD_P 96
+#define TD_THREADS 512
+#define TD_PITCH 100
+#define TD_NGR 32      // 9-thread groups of the dPt contraction
+
+struct TcDgradArgs {
+  const float* x; int64_t x_sb, x_sc;
+  const float* G;
+  int C, N, O, b, ntile, J, d1, d2, nnz, x_is_relu, nbias;
+  const float *ln_w, *ln_b, *res_w, *c1_w, *c2_w, *sa_W;
+  const float *Mc, *Pt, *Z, *pw, *A2;
+  const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
+  float *dx, *tcA, *delta, *dSnz, *bias_part, *ln_part;
+  double* dPt_part;
+};
+
+static inline size_t td_pre_floats(int b) { const size_t a = (size_t)2 * b * TD_PITCH, c = (size_t)TD_NGR * 144; return a > c ? a : c; }
+
+static size_t tc_dgrad_smem(int O, int b) {
+  size_t s = 0;
+  s += 2 * (size_t)3 * O * 128;            // GH, GL: G tile, then [dA_now | dA_past | GZ]; later the D_h staging rows
+  s += 4 * (size_t)3 * O * 128;            // WXH, WXL (Wres), W3H, W3L ([W1now; W1past; Ws])
+  s += 2 * (size_t)3 * b * 128;            // WMH, WML (Mc of the sample)
+  s += 2 * (size_t)2 * b * 128;            // W2H, W2L
+  s += td_pre_floats(b) * 4;               // PRE: D_y rows, later the dPt group partials
+  s += (size_t)b * TD_PITCH * 4;           // DY: dY1 rows
+  s += (144 * 2 + 24 + 16 + 16 * 24 + 8) * 4;
+  return s + 1024;
+}
+
+TC_DEV float td_rna(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+TC_DEV void td_split4(unsigned char* hi, unsigned char* lo, uint32_t off, float4 v) {
+  float4 h = make_float4(td_rna(v.x), td_rna(v.y), td_rna(v.z), td_rna(v.w));
+  st4(reinterpret_cast<float*>(hi + off), h);
+  st4(reinterpret_cast<float*>(lo + off), make_float4(td_rna(v.x - h.x), td_rna(v.y - h.y), td_rna(v.z - h.z), td_rna(v.w - h.w)));
+}
+TC_DEV void td_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float v) {
+  const float h = td_rna(v);
+  *reinterpret_cast<float*>(hi + off) = h;
+  *reinterpret_cast<float*>(lo + off) = td_rna(v - h);
+}
+// acc (+)= Ah Bh + Ah Bl + Al Bh for one k-step; MN-major operands, 128 B swizzle with 32 B atoms
+TC_DEV void td_mma3(uint32_t d, uint32_t ah, uint32_t al, uint32_t cba, uint32_t bh, uint32_t bl, uint32_t cbb, uint32_t idesc,
+                    uint32_t acc) {
+  const uint64_t dah = umma_desc(ah, cba, 512u, 1), dal = umma_desc(al, cba, 512u, 1);
+  const uint64_t dbh = umma_desc(bh, cbb, 512u, 1), dbl = umma_desc(bl, cbb, 512u, 1);
+  umma_tf32(d, dah, dbh, idesc, acc);
+  umma_tf32(d, dah, dbl, idesc, 1u);
+  umma_tf32(d, dal, dbh, idesc, 1u);
+}
+
+__global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int C = a.C, b = a.b, O = a.O, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, bi = blockIdx.y;
+  const uint32_t cbO = (uint32_t)O * 128u, cbM = (uint32_t)b * 128u;
+  unsigned char* GH = smem;
+  unsigned char* GL = GH + 3 * cbO;
+  unsigned char* WXH = GL + 3 * cbO;
+  unsigned char* WXL = WXH + 3 * cbO;
+  unsigned char* W3H = WXL + 3 * cbO;
+  unsigned char* W3L = W3H + 3 * cbO;
+  unsigned char* WMH = W3L + 3 * cbO;
+  unsigned char* WML = WMH + 3 * cbM;
+  unsigned char* W2H = WML + 3 * cbM;
+  unsigned char* W2L = W2H + 2 * cbM;
+  float* PRE = reinterpret_cast<float*>(W2L + 2 * cbM);   // [2b][TD_PITCH]
+  float* DY = PRE + (2 * b * TD_PITCH > TD_NGR * 144 ? 2 * b * TD_PITCH : TD_NGR * 144);   // [b][TD_PITCH]
+  float* Pt = DY + b * TD_PITCH;                          // [144]
+  float* Ptd = Pt + 144;                                  // Pt shifted down by d1 rows
+  float* LW = Ptd + 144;                                  // [24]
+  float* DL = LW + 24;                                    // [16] delta halves
+  float* RED = DL + 16;                                   // [16][24] final LayerNorm-affine reduction
+  uint64_t& bar = *reinterpret_cast<uint64_t*>(RED + 16 * 24);
+  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(RED + 16 * 24 + 2);
+  float* STG = reinterpret_cast<float*>(GH);              // [C][TD_PITCH] D_h rows, aliases the A tile once it is consumed
+
+  // ---- one-time staging: weights as B operands [K][N] (N contiguous), hi / lo, zero padded
+  for (int i = tid; i < O * 96; i += TD_THREADS) {
+    const int k = i / 96, n = i - k * 96;
+    const uint32_t off = sw128b32_off(k, n, cbO);
+    td_split1(WXH, WXL, off, n < C ? a.res_w[k * C + n] : 0.f);
+    float w = 0.f;
+    if (n < C) {
+      if (k < b) w = a.c1_w[(k * C + n) * 2 + 1];
+      else if (k < 2 * b) w = a.c1_w[((k - b) * C + n) * 2 + 0];
+      else w = a.sa_W[(k - 2 * b) * C + n];
+    }
+    td_split1(W3H, W3L, off, w);
+  }
+  for (int i = tid; i < b * 96; i += TD_THREADS) {
+    const int k = i / 96, n = i - k * 96;
+    td_split1(WMH, WML, sw128b32_off(k, n, cbM), n < C ? a.Mc[((int64_t)bi * b + k) * C + n] : 0.f);
+  }
+  for (int i = tid; i < b * 64; i += TD_THREADS) {
+    const int k = i / 64, n = i - k * 64;   // k = output channel o of the second conv (contraction), n = its input channel (+ b: past tap)
+    float w = 0.f;
+    if (n < b) w = a.c2_w[(k * b + n) * 2 + 1];
+    else if (n < 2 * b) w = a.c2_w[(k * b + (n - b)) * 2 + 0];
+    td_split1(W2H, W2L, sw128b32_off(k, n, cbM), w);
+  }
+  for (int i = tid; i < 144; i += TD_THREADS) {
+    const int t = i / 12, j = i - t * 12;
+    Pt[i] = a.Pt[(int64_t)bi * 144 + i];
+    Ptd[i] = t >= a.d1 ? a.Pt[(int64_t)bi * 144 + (t - a.d1) * 12 + j] : 0.f;
+  }
+  if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 256);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tm = tmem_slot;
+  const uint32_t Dx = tm, Dh = tm + 96, Dy = tm + 192;
+  const uint32_t sGH = smem_u32(GH), sGL = smem_u32(GL), sWXH = smem_u32(WXH), sWXL = smem_u32(WXL), sW3H = smem_u32(W3H),
+                 sW3L = smem_u32(W3L), sWMH = smem_u32(WMH), sWML = smem_u32(WML), sW2H = smem_u32(W2H), sW2L = smem_u32(W2L);
+  const uint32_t idescC = umma_idesc_tf32(128, (C + 15) & ~15, 1, 1), idescY = umma_idesc_tf32(128, 2 * b, 1, 1);
+  uint32_t phase = 0;
+  const int l = tid & 127, quarter = warp >> 2;   // l = TMEM lane = position; the 4 warpgroups split the column groups
+  const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+  const float* xb = a.x + bi * a.x_sb;
+  const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
+  const float* Gs = Gb + (int64_t)2 * b * a.N * 12;
+  const float* pwb = a.pw + (int64_t)bi * a.nnz;
+  const float* Zb = a.Z + (int64_t)bi * b * a.N * 12;
+  const float* A2b = a.A2 + (int64_t)bi * 2 * b * a.N * 12;
+  float* tcAb = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
+  const int blk = bi * a.J + blockIdx.x;
+
+  float bsG[2] = {0.f, 0.f}, bsY = 0.f, lnw_acc[12], lnb_acc[12];
+  double pt_acc = 0.0;
+#pragma unroll
+  for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
+
+  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+    const int n0 = tile * TD_NT;
+    // ---- 1. G rows -> the A tile (hi / lo); row sums for the bias gradients
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = tid + q * TD_THREADS;
+      if (r < O * TD_NT) {
+        const int o = r / TD_NT, nl = r - o * TD_NT, n = n0 + nl, pp = nl * 12;
+        float4 u = f4zero(), v = f4zero(), w = f4zero();
+        if (n < a.N) { const float* s = Gb + ((int64_t)o * a.N + n) * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
+        bsG[q] += ((u.x + u.y) + (u.z + u.w)) + ((v.x + v.y) + (v.z + v.w)) + ((w.x + w.y) + (w.z + w.w));
+        td_split4(GH, GL, sw128b32_off(o, pp, cbO), u);
+        td_split4(GH, GL, sw128b32_off(o, pp + 4, cbO), v);
+        td_split4(GH, GL, sw128b32_off(o, pp + 8, cbO), w);
+      }
+    }
+    fence_smem_to_async();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after_sync();
+      for (int ks = 0; ks < O / 8; ++ks)
+        td_mma3(Dx, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sWXH + ks * 1024u, sWXL + ks * 1024u, cbO, idescC, ks > 0);
+      for (int ks = 0; ks < b / 8; ++ks)
+        td_mma3(Dh, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sWMH + ks * 1024u, sWML + ks * 1024u, cbM, idescC, ks > 0);
+      for (int ks = 0; ks < b / 8; ++ks)
+        td_mma3(Dy, sGH + (b / 8 + ks) * 1024u, sGL + (b / 8 + ks) * 1024u, cbO, sW2H + ks * 1024u, sW2L + ks * 1024u, cbM, idescY, ks > 0);
+      umma_commit(smem_u32(&bar));
+    }
+    // ---- while the tensor core runs: dS at the adjacency non-zeros and its row sums (attention.py:35-36
+    // transposed): dSnz[e] = A[n,i_e] sum_{o,t} G_s[o,n,t] Z[o,i_e,t]; two warps share the edges of a node
+    {
+      const int nl = warp >> 1, par = warp & 1, n = n0 + nl;
+      float dl = 0.f;
+      if (n < a.N) {
+        const int e1 = a.row_ptr[n + 1];
+        for (int e = a.row_ptr[n] + par; e < e1; e += 2) {
+          const float* zr = Zb + (int64_t)a.col_idx[e] * 12;
+          float s = 0.f;
+          for (int pr = lane; pr < b * 3; pr += 32) {
+            const int cz = pr / 3, q4 = (pr - cz * 3) * 4;
+            s += dot4(ld4(Gs + ((int64_t)cz * a.N + n) * 12 + q4), ld4(zr + (int64_t)cz * a.N * 12 + q4));
+          }
+          s = warp_sum(s);
+          const float dsn = pwb[e] * s;
+          dl += dsn;
+          if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + e] = dsn;
+        }
+      }
+      if (lane == 0) DL[warp] = dl;
+    }
+    mbar_wait(smem_u32(&bar), phase); phase ^= 1;
+    tc_fence_after_sync();
+    // ---- 2. D_y -> staging rows PRE[2b][.]
+    {
+      int g = 0;
+      for (int c0 = 0; c0 < 2 * b; c0 += 8, ++g) {
+        if ((g & 3) != quarter) continue;   // warp-uniform
+        float v[8];
+        tmem_ld8(Dy + lane_base + c0, v);
+        if (l < TD_P) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) PRE[(c0 + j) * TD_PITCH + l] = v[j];
+        }
+      }
+    }
+    __syncthreads();
+    if (tid < TD_NT && n0 + tid < a.N) a.delta[(int64_t)bi * a.N + n0 + tid] = DL[2 * tid] + DL[2 * tid + 1];
+    // ---- 3. rows of 12: dY1, dA_now / dA_past (two threads per row), GZ gather -> the A tile again
+    if (tid < 2 * b * TD_NT) {
+      const int item = tid >> 1, half = tid & 1, k = item / TD_NT, nl = item - k * TD_NT, n = n0 + nl, pp = nl * 12;
+      const float* pn = PRE + k * TD_PITCH + pp;
+      const float* pq = PRE + (b + k) * TD_PITCH + pp;
+      float v[12], o12[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) v[t] = pn[t] + (t + a.d2 < 12 ? pq[t + a.d2 < 12 ? t + a.d2 : 0] : 0.f);
+      const float* P = half ? Ptd : Pt;
+#pragma unroll
+      for (int j = 0; j < 12; ++j) {
+        float s = 0.f;
+#pragma unroll
+        for (int t = 0; t < 12; ++t) s = fmaf(P[t * 12 + j], v[t], s);
+        o12[j] = s;
+      }
+      if (!half) {
+        float* dy = DY + k * TD_PITCH + pp;
+        float s = 0.f;
+#pragma unroll
+        for (int t = 0; t < 12; ++t) { dy[t] = v[t]; s += v[t]; }
+        bsY += s;
+      }
+      const int row = half * b + k;
+      const float4 u0 = make_float4(o12[0], o12[1], o12[2], o12[3]), u1 = make_float4(o12[4], o12[5], o12[6], o12[7]),
+                   u2 = make_float4(o12[8], o12[9], o12[10], o12[11]);
+      td_split4(GH, GL, sw128b32_off(row, pp, cbO), u0);
+      td_split4(GH, GL, sw128b32_off(row, pp + 4, cbO), u1);
+      td_split4(GH, GL, sw128b32_off(row, pp + 8, cbO), u2);
+      if (n < a.N) {
+        float* d = tcAb + ((int64_t)row * a.N + n) * 12;
+        st4(d, u0); st4(d + 4, u1); st4(d + 8, u2);
+      }
+    }
+    {
+      // GZ[o][i] = sum_n A[n,i] g_s[o][n] through the CSC view; 4 channels x 4 positions per item
+      const int gi = tid - (TD_THREADS - (b / 4) * TD_NT * 3);
+      if (gi >= 0) {
+        const int ch = gi / (TD_NT * 3), pq = gi - ch * (TD_NT * 3), nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4, n = n0 + nl;
+        float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+        if (n < a.N) {
+          const int k1 = a.csc_ptr[n + 1];
+          for (int k = a.csc_ptr[n]; k < k1; ++k) {
+            const float w = pwb[a.csc_eid[k]];
+            const float* gr = Gs + ((int64_t)o0 * a.N + a.csc_row[k]) * 12 + t0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fma4(d[j], w, ld4(gr + (int64_t)j * a.N * 12));
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          td_split4(GH, GL, sw128b32_off(2 * b + o0 + j, nl * 12 + t0, cbO), d[j]);
+          if (n < a.N) st4(tcAb + ((int64_t)(2 * b + o0 + j) * a.N + n) * 12 + t0, d[j]);
+        }
+      }
+    }
+    fence_smem_to_async();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after_sync();
+      for (int ks = 0; ks < O / 8; ++ks)
+        td_mma3(Dh, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sW3H + ks * 1024u, sW3L + ks * 1024u, cbO, idescC, 1u);
+      umma_commit(smem_u32(&bar));
+    }
+    // ---- while the tensor core runs: dPt partials from the dY1 rows and the saved first-conv taps
+    if (tid < TD_NGR * 9) {
+      const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4;
+      double o16[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o16[i] = 0.0;
+      for (int r = grp; r < 2 * b * TD_NT; r += TD_NGR) {
+        const int tap = r / (b * TD_NT), rr = r - tap * b * TD_NT, k = rr / TD_NT, nl = rr - k * TD_NT, n = n0 + nl;
+        if (n >= a.N) continue;
+        const float* dy = DY + k * TD_PITCH + nl * 12;
+        const int sh = tap ? a.d1 : 0;
+        float g[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
+        const float4 h = ld4(A2b + ((int64_t)(tap * b + k) * a.N + n) * 12 + ib);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          o16[i * 4 + 0] += g[i] * h.x; o16[i * 4 + 1] += g[i] * h.y; o16[i * 4 + 2] += g[i] * h.z; o16[i * 4 + 3] += g[i] * h.w;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) PRE[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
+    }
+    mbar_wait(smem_u32(&bar), phase); phase ^= 1;
+    tc_fence_after_sync();
+    __syncthreads();
+    if (tid < 144) {
+      double s = 0.0;
+      for (int g2 = 0; g2 < TD_NGR; ++g2) s += (double)PRE[g2 * 144 + tid];
+      pt_acc += s;
+    }
+    // ---- 4. D_h -> staging rows STG[C][.] (over the A tile, which the tensor core has finished reading)
+    {
+      int g = 0;
+      for (int c0 = 0; c0 < C; c0 += 8, ++g) {
+        if ((g & 3) != quarter) continue;
+        float v[8];
+        tmem_ld8(Dh + lane_base + c0, v);
+        if (l < TD_P) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) STG[(c0 + j) * TD_PITCH + l] = v[j];
+        }
+      }
+    }
+    __syncthreads();
+    // ---- 5. LayerNorm backward on rows of 12 (msgat.py:122) + affine gradient partials
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = tid + q * TD_THREADS;
+      if (r < C * TD_NT) {
+        const int c = r / TD_NT, nl = r - c * TD_NT, n = n0 + nl;
+        if (n < a.N) {
+          const float* src = xb + c * a.x_sc + (int64_t)n * 12;
+          const float4 u = ld4(src), v = ld4(src + 4), w = ld4(src + 8);
+          float xh[12] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w, w.x, w.y, w.z, w.w};
+          float mu = 0.f;
+#pragma unroll
+          for (int t = 0; t < 12; ++t) mu += xh[t];
+          mu *= (1.0f / 12.0f);
+          float var = 0.f;
+#pragma unroll
+          for (int t = 0; t < 12; ++t) { xh[t] -= mu; var = fmaf(xh[t], xh[t], var); }
+          const float rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
+          float* qrow = STG + c * TD_PITCH + nl * 12;
+          float gg[12], m1 = 0.f, m2 = 0.f;
+#pragma unroll
+          for (int t = 0; t < 12; ++t) {
+            xh[t] *= rs;
+            const float dh = qrow[t];
+            lnw_acc[t] = fmaf(dh, xh[t], lnw_acc[t]);
+            lnb_acc[t] += dh;
+            gg[t] = dh * LW[t];
+            m1 += gg[t]; m2 = fmaf(gg[t], xh[t], m2);
+          }
+          m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+#pragma unroll
+          for (int t = 0; t < 12; ++t) qrow[t] = rs * (gg[t] - m1 - xh[t] * m2);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- 6. dx = LN^T(dh) + D_x, one thread per (position, column-group quarter), coalesced stores
+    {
+      const int nl = l / 12, n = n0 + nl, t = l - nl * 12;
+      const bool live = l < TD_P && n < a.N;
+      const int64_t cs = (int64_t)a.N * 12;
+      float* ob = a.dx + (int64_t)bi * C * cs + (int64_t)n * 12 + t;
+      const float* xp = xb + (int64_t)n * 12 + t;
+      int g = 0;
+      for (int c0 = 0; c0 < C; c0 += 8, ++g) {
+        if ((g & 3) != quarter) continue;
+        float r[8];
+        tmem_ld8(Dx + lane_base + c0, r);
+        if (live) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float v = r[j] + STG[(c0 + j) * TD_PITCH + l];
+            if (a.x_is_relu) v = xp[(c0 + j) * a.x_sc] > 0.f ? v : 0.f;
+            ob[(c0 + j) * cs] = v;
+          }
+        }
+      }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+  }
+  // ---- flush the per-block partials (layout of k_bwd_main: G row sums, then dY1 row sums)
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    float s = bsG[q];
+    s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4);
+    const int r = tid + q * TD_THREADS;
+    if (r < O * TD_NT && (r & 7) == 0) a.bias_part[(int64_t)blk * a.nbias + r / TD_NT] = s;
+  }
+  {
+    float s = bsY;   // rows k on the even threads tid = 2 (k * 8 + nl)
+    s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4); s += __shfl_xor_sync(0xffffffffu, s, 8);
+    if (tid < 2 * b * TD_NT && (tid & 15) == 0) a.bias_part[(int64_t)blk * a.nbias + O + (tid >> 4)] = s;
+  }
+  if (tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
+#pragma unroll
+  for (int t = 0; t < 12; ++t) {
+    const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
+    if (lane == 0) { RED[warp * 24 + t] = w; RED[warp * 24 + 12 + t] = bb; }
+  }
+  __syncthreads();
+  if (tid < 24) {
+    float s = 0.f;
+    for (int w = 0; w < TD_THREADS / 32; ++w) s += RED[w * 24 + tid];
+    a.ln_part[(int64_t)blk * 24 + tid] = s;
+  }
+  if (warp == 0) tmem_dealloc(tm, 256);
+}
+
+bool tc_dgrad_supported(const Plan& p) {
+  const char* off = getenv("MSGAT_TC_DISABLE");  // test switch: bit 2 = data-gradient kernel
+  if (off && (atoi(off) & 4)) return false;
+  // needs the first-conv taps (A2) kept by k_tc_apply3 and the weight-gradient kernel for dA / GZ
+  return tc_apply3_supported(p) && tc_wgrad_supported(p) && p.O == 3 * p.Oc;
+}
+
+int tc_dgrad_blocks_per_sample(const Plan& p) {
+  const int ntile = (p.N + TD_NT - 1) / TD_NT;
+  int J = 148 / p.B;
+  if (J > ntile) J = ntile;
+  return J < 1 ? 1 : J;
+}
+
+int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
+                    const float* saved, float* tcA, float* dx, float* delta, float* dSnz, float* bias_part, int nbias,
+                    float* ln_part, double* dPt_part, void* stream) {
+  TcDgradArgs a;
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
+  a.C = p.C; a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TD_NT - 1) / TD_NT; a.J = tc_dgrad_blocks_per_sample(p);
+  a.d1 = p.dil[0]; a.d2 = p.dil[1]; a.nnz = p.nnz; a.x_is_relu = (p.flags & MSGAT_F_X_IS_RELU) ? 1 : 0; a.nbias = nbias;
+  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.c1_w = prm->conv_w[0]; a.c2_w = prm->conv_w[1]; a.sa_W = prm->sa_W;
+  a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw; a.A2 = saved + p.o_A2;
+  a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+  a.dx = dx; a.tcA = tcA; a.delta = delta; a.dSnz = dSnz; a.bias_part = bias_part; a.ln_part = ln_part; a.dPt_part = dPt_part;
+  MSGAT_LAUNCH(k_tc_dgrad, dim3(a.J, p.B), dim3(TD_THREADS), tc_dgrad_smem(p.O, p.Oc), stream, a);
+  return 0;
+}

@@ -76,7 +76,7 @@ def test_tc_meam_layer2_matches_reference_golden():
     assert worst[0] < 10 * TC_TOL, worst
 
 
-def _run_tc_model(name, B, disable):
+def _run_tc_model(name, B, disable, precision=None):
     import os
     from msgat_b200 import _lib
     from oracle import msgat_oracle as O
@@ -84,7 +84,7 @@ def _run_tc_model(name, B, disable):
     os.environ["MSGAT_TC_DISABLE"] = str(disable)
     try:
         model, batch = _model_and_batch(name, B)
-        model = model.cuda().set_precision(_lib.PREC_TF32)
+        model = model.cuda().set_precision(_lib.PREC_TF32 if precision is None else precision)
         X = batch.X.cuda().requires_grad_(True)
         out = model(X, batch.H.cuda(), batch.D.cuda())
         O.huber(out, batch.Y.cuda(), 50.0).backward()
@@ -119,6 +119,22 @@ def test_tc_weight_gradients_match_fp32_kernels(name, B):
                    if a.grad is not None and float(b.grad.norm()) > 0), reverse=True)
     print("worst tcgen05-vs-fp32 weight gradients:", rows[:4])
     assert rows[0][0] < TC_TOL, rows[:4]
+
+
+@pytest.mark.parametrize("name,B", [("pemsd8", 3), ("pemsd7", 2), ("pemsd3", 2)])
+def test_tc_data_gradients_match_fp32_kernels(name, B):
+    """Default (fp32-grade) path: same 3xTF32 forward, every gradient with the tcgen05 data-gradient
+    kernel (k_tc_dgrad) against k_bwd_main on the CUDA cores.  Both are fp32-grade, so they agree
+    far below the parity bar; the outputs are identical (same forward kernels)."""
+    from msgat_b200 import _lib
+    m_tc, _, X_tc, o_tc = _run_tc_model(name, B, 0, _lib.PREC_FP32)
+    m_32, _, X_32, o_32 = _run_tc_model(name, B, 4, _lib.PREC_FP32)
+    assert torch.equal(o_tc, o_32)
+    rows = sorted(((_rel(a.grad, b.grad), n) for (n, a), (_, b) in zip(m_tc.named_parameters(), m_32.named_parameters())
+                   if a.grad is not None and float(b.grad.norm()) > 0), reverse=True)
+    print("dX", _rel(X_tc.grad, X_32.grad), "worst k_tc_dgrad-vs-k_bwd_main gradients:", rows[:5])
+    assert _rel(X_tc.grad, X_32.grad) < 2e-5
+    assert rows[0][0] < 2e-5, rows[:5]
 
 
 @pytest.mark.parametrize("name,B", [("pemsd8", 3)])
