@@ -69,13 +69,14 @@ TC_DEV void td_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float 
   *reinterpret_cast<float*>(lo + off) = td_rna(v - h);
 }
 // acc (+)= Ah Bh + Ah Bl + Al Bh for one k-step; MN-major operands, 128 B swizzle with 32 B atoms
-TC_DEV void td_mma3(uint32_t d, uint32_t ah, uint32_t al, uint32_t cba, uint32_t bh, uint32_t bl, uint32_t cbb, uint32_t idesc,
+// The descriptors of k-step 0 are built once; k-step ks (8 contraction rows = 1024 B) adds ks * 64 to
+// the start-address field (16-byte units).
+TC_DEV void td_mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64_t dbl, uint32_t ka, uint32_t kb, uint32_t idesc,
                     uint32_t acc) {
-  const uint64_t dah = umma_desc(ah, cba, 512u, 1), dal = umma_desc(al, cba, 512u, 1);
-  const uint64_t dbh = umma_desc(bh, cbb, 512u, 1), dbl = umma_desc(bl, cbb, 512u, 1);
-  umma_tf32(d, dah, dbh, idesc, acc);
-  umma_tf32(d, dah, dbl, idesc, 1u);
-  umma_tf32(d, dal, dbh, idesc, 1u);
+  const uint64_t oa = (uint64_t)(ka * 64u), ob = (uint64_t)(kb * 64u);
+  umma_tf32(d, dah + oa, dbh + ob, idesc, acc);
+  umma_tf32(d, dah + oa, dbl + ob, idesc, 1u);
+  umma_tf32(d, dal + oa, dbh + ob, idesc, 1u);
 }
 
 __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
@@ -141,8 +142,11 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   tc_fence_after_sync();
   const uint32_t tm = tmem_slot;
   const uint32_t Dx = tm, Dh = tm + 96, Dy = tm + 192;
-  const uint32_t sGH = smem_u32(GH), sGL = smem_u32(GL), sWXH = smem_u32(WXH), sWXL = smem_u32(WXL), sW3H = smem_u32(W3H),
-                 sW3L = smem_u32(W3L), sWMH = smem_u32(WMH), sWML = smem_u32(WML), sW2H = smem_u32(W2H), sW2L = smem_u32(W2L);
+  const uint64_t dGH = umma_desc(smem_u32(GH), cbO, 512u, 1), dGL = umma_desc(smem_u32(GL), cbO, 512u, 1);
+  const uint64_t dWXH = umma_desc(smem_u32(WXH), cbO, 512u, 1), dWXL = umma_desc(smem_u32(WXL), cbO, 512u, 1);
+  const uint64_t dW3H = umma_desc(smem_u32(W3H), cbO, 512u, 1), dW3L = umma_desc(smem_u32(W3L), cbO, 512u, 1);
+  const uint64_t dWMH = umma_desc(smem_u32(WMH), cbM, 512u, 1), dWML = umma_desc(smem_u32(WML), cbM, 512u, 1);
+  const uint64_t dW2H = umma_desc(smem_u32(W2H), cbM, 512u, 1), dW2L = umma_desc(smem_u32(W2L), cbM, 512u, 1);
   const uint32_t idescC = umma_idesc_tf32(128, (C + 15) & ~15, 1, 1), idescY = umma_idesc_tf32(128, 2 * b, 1, 1);
   uint32_t phase = 0;
   const int l = tid & 127, quarter = warp >> 2;   // l = TMEM lane = position; the 4 warpgroups split the column groups
@@ -155,6 +159,12 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   const float* A2b = a.A2 + (int64_t)bi * 2 * b * a.N * 12;
   float* tcAb = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
   const int blk = bi * a.J + blockIdx.x;
+
+  // GZ gather items on the top threads: 4 channels x 4 positions each
+  const int gz_i = tid - (TD_THREADS - (b / 4) * TD_NT * 3);
+  const bool gz_on = gz_i >= 0;
+  const int gz_ch = gz_i / (TD_NT * 3), gz_pq = gz_i - gz_ch * (TD_NT * 3), gz_nl = gz_pq / 3, gz_t0 = (gz_pq - gz_nl * 3) * 4, gz_o0 = gz_ch * 4;
+  uint32_t* MSK = reinterpret_cast<uint32_t*>(DY);   // [C][8] x > 0 bits of a row, over the dY1 rows once dPt has read them
 
   float bsG[2] = {0.f, 0.f}, bsY = 0.f, lnw_acc[12], lnb_acc[12];
   double pt_acc = 0.0;
@@ -181,15 +191,24 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
-      for (int ks = 0; ks < O / 8; ++ks)
-        td_mma3(Dx, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sWXH + ks * 1024u, sWXL + ks * 1024u, cbO, idescC, ks > 0);
-      for (int ks = 0; ks < b / 8; ++ks)
-        td_mma3(Dh, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sWMH + ks * 1024u, sWML + ks * 1024u, cbM, idescC, ks > 0);
-      for (int ks = 0; ks < b / 8; ++ks)
-        td_mma3(Dy, sGH + (b / 8 + ks) * 1024u, sGL + (b / 8 + ks) * 1024u, cbO, sW2H + ks * 1024u, sW2L + ks * 1024u, cbM, idescY, ks > 0);
+      for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dy, dGH, dGL, dW2H, dW2L, b / 8 + ks, ks, idescY, ks > 0);
+      for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dh, dGH, dGL, dWMH, dWML, ks, ks, idescC, ks > 0);
+      for (int ks = 0; ks < O / 8; ++ks) td_mma3(Dx, dGH, dGL, dWXH, dWXL, ks, ks, idescC, ks > 0);
       umma_commit(smem_u32(&bar));
     }
-    // ---- while the tensor core runs: dS at the adjacency non-zeros and its row sums (attention.py:35-36
+    // ---- while the tensor core runs: GZ[o][i] = sum_n A[n,i] g_s[o][n] through the CSC view (4 channels x
+    // 4 positions per item, kept in registers until the A tile is free), then dS at the adjacency non-zeros
+    float4 gz[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
+    if (gz_on && n0 + gz_nl < a.N) {
+      const int n = n0 + gz_nl, k1 = a.csc_ptr[n + 1];
+      for (int k = a.csc_ptr[n]; k < k1; ++k) {
+        const float w = pwb[a.csc_eid[k]];
+        const float* gr = Gs + ((int64_t)gz_o0 * a.N + a.csc_row[k]) * 12 + gz_t0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) fma4(gz[j], w, ld4(gr + (int64_t)j * a.N * 12));
+      }
+    }
+    // dS at the adjacency non-zeros and its row sums (attention.py:35-36
     // transposed): dSnz[e] = A[n,i_e] sum_{o,t} G_s[o,n,t] Z[o,i_e,t]; two warps share the edges of a node
     {
       const int nl = warp >> 1, par = warp & 1, n = n0 + nl;
@@ -262,60 +281,50 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
         st4(d, u0); st4(d + 4, u1); st4(d + 8, u2);
       }
     }
-    {
-      // GZ[o][i] = sum_n A[n,i] g_s[o][n] through the CSC view; 4 channels x 4 positions per item
-      const int gi = tid - (TD_THREADS - (b / 4) * TD_NT * 3);
-      if (gi >= 0) {
-        const int ch = gi / (TD_NT * 3), pq = gi - ch * (TD_NT * 3), nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4, n = n0 + nl;
-        float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
-        if (n < a.N) {
-          const int k1 = a.csc_ptr[n + 1];
-          for (int k = a.csc_ptr[n]; k < k1; ++k) {
-            const float w = pwb[a.csc_eid[k]];
-            const float* gr = Gs + ((int64_t)o0 * a.N + a.csc_row[k]) * 12 + t0;
+    if (gz_on) {
+      const int n = n0 + gz_nl;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) fma4(d[j], w, ld4(gr + (int64_t)j * a.N * 12));
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          td_split4(GH, GL, sw128b32_off(2 * b + o0 + j, nl * 12 + t0, cbO), d[j]);
-          if (n < a.N) st4(tcAb + ((int64_t)(2 * b + o0 + j) * a.N + n) * 12 + t0, d[j]);
-        }
+      for (int j = 0; j < 4; ++j) {
+        td_split4(GH, GL, sw128b32_off(2 * b + gz_o0 + j, gz_nl * 12 + gz_t0, cbO), gz[j]);
+        if (n < a.N) st4(tcAb + ((int64_t)(2 * b + gz_o0 + j) * a.N + n) * 12 + gz_t0, gz[j]);
       }
     }
     fence_smem_to_async();
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
-      for (int ks = 0; ks < O / 8; ++ks)
-        td_mma3(Dh, sGH + ks * 1024u, sGL + ks * 1024u, cbO, sW3H + ks * 1024u, sW3L + ks * 1024u, cbO, idescC, 1u);
+      for (int ks = 0; ks < O / 8; ++ks) td_mma3(Dh, dGH, dGL, dW3H, dW3L, ks, ks, idescC, 1u);
       umma_commit(smem_u32(&bar));
     }
     // ---- while the tensor core runs: dPt partials from the dY1 rows and the saved first-conv taps
     if (tid < TD_NGR * 9) {
-      const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4;
-      double o16[16];
+      // group g owns node g & 7 and the rows k = (g >> 3) + 4 m of both taps; 12 rows per group and
+      // tile are summed in fp32, the per-tile sums in fp64
+      const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4, nl = grp & 7, n = n0 + nl;
+      float o16[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) o16[i] = 0.0;
-      for (int r = grp; r < 2 * b * TD_NT; r += TD_NGR) {
-        const int tap = r / (b * TD_NT), rr = r - tap * b * TD_NT, k = rr / TD_NT, nl = rr - k * TD_NT, n = n0 + nl;
-        if (n >= a.N) continue;
-        const float* dy = DY + k * TD_PITCH + nl * 12;
-        const int sh = tap ? a.d1 : 0;
-        float g[4];
+      for (int i = 0; i < 16; ++i) o16[i] = 0.f;
+      if (n < a.N) {
+        for (int tap = 0; tap < 2; ++tap) {
+          const int sh = tap ? a.d1 : 0;
+          for (int k = grp >> 3; k < b; k += 4) {
+            const float* dy = DY + k * TD_PITCH + nl * 12;
+            const float4 h = ld4(A2b + ((int64_t)(tap * b + k) * a.N + n) * 12 + ib);
+            float g[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
-        const float4 h = ld4(A2b + ((int64_t)(tap * b + k) * a.N + n) * 12 + ib);
+            for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          o16[i * 4 + 0] += g[i] * h.x; o16[i * 4 + 1] += g[i] * h.y; o16[i * 4 + 2] += g[i] * h.z; o16[i * 4 + 3] += g[i] * h.w;
+            for (int i = 0; i < 4; ++i) {
+              o16[i * 4 + 0] = fmaf(g[i], h.x, o16[i * 4 + 0]); o16[i * 4 + 1] = fmaf(g[i], h.y, o16[i * 4 + 1]);
+              o16[i * 4 + 2] = fmaf(g[i], h.z, o16[i * 4 + 2]); o16[i * 4 + 3] = fmaf(g[i], h.w, o16[i * 4 + 3]);
+            }
+          }
         }
       }
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) PRE[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
+        for (int j = 0; j < 4; ++j) PRE[grp * 144 + (tb + i) * 12 + ib + j] = o16[i * 4 + j];
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
     tc_fence_after_sync();
@@ -349,6 +358,10 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           const float* src = xb + c * a.x_sc + (int64_t)n * 12;
           const float4 u = ld4(src), v = ld4(src + 4), w = ld4(src + 8);
           float xh[12] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w, w.x, w.y, w.z, w.w};
+          uint32_t mb = 0;
+#pragma unroll
+          for (int t = 0; t < 12; ++t) mb |= (xh[t] > 0.f ? 1u : 0u) << t;
+          MSK[c * TD_NT + nl] = a.x_is_relu ? mb : 0xfffu;
           float mu = 0.f;
 #pragma unroll
           for (int t = 0; t < 12; ++t) mu += xh[t];
@@ -381,7 +394,6 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       const bool live = l < TD_P && n < a.N;
       const int64_t cs = (int64_t)a.N * 12;
       float* ob = a.dx + (int64_t)bi * C * cs + (int64_t)n * 12 + t;
-      const float* xp = xb + (int64_t)n * 12 + t;
       int g = 0;
       for (int c0 = 0; c0 < C; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;
@@ -391,7 +403,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             float v = r[j] + STG[(c0 + j) * TD_PITCH + l];
-            if (a.x_is_relu) v = xp[(c0 + j) * a.x_sc] > 0.f ? v : 0.f;
+            v = (MSK[(c0 + j) * TD_NT + nl] >> t) & 1u ? v : 0.f;   // x is a ReLU output: its gradient stops at x <= 0
             ob[(c0 + j) * cs] = v;
           }
         }
