@@ -209,23 +209,36 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       }
     }
     // dS at the adjacency non-zeros and its row sums (attention.py:35-36
-    // transposed): dSnz[e] = A[n,i_e] sum_{o,t} G_s[o,n,t] Z[o,i_e,t]; two warps share the edges of a node
-    {
-      const int nl = warp >> 1, par = warp & 1, n = n0 + nl;
+    // transposed): dSnz[e] = A[n,i_e] sum_{o,t} G_s[o,n,t] Z[o,i_e,t]
+    if (warp < TD_NT) {   // one warp per node (the GZ gather above runs on the top warps at the same time)
+      const int n = n0 + warp;
       float dl = 0.f;
       if (n < a.N) {
-        const int e1 = a.row_ptr[n + 1];
-        for (int e = a.row_ptr[n] + par; e < e1; e += 2) {
-          const float* zr = Zb + (int64_t)a.col_idx[e] * 12;
-          float s = 0.f;
-          for (int pr = lane; pr < b * 3; pr += 32) {
-            const int cz = pr / 3, q4 = (pr - cz * 3) * 4;
-            s += dot4(ld4(Gs + ((int64_t)cz * a.N + n) * 12 + q4), ld4(zr + (int64_t)cz * a.N * 12 + q4));
+        const int e0 = a.row_ptr[n], e1 = a.row_ptr[n + 1];
+        // the node's own G_s rows do not depend on the edge: b x 12 values, three float4 per lane at most
+        float4 gs[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
+          gs[q] = pr < b * 3 ? ld4(Gs + ((int64_t)cz * a.N + n) * 12 + q4) : f4zero();
+        }
+        for (int eb = e0; eb < e1; eb += 32) {
+          const int my = eb + lane < e1 ? a.col_idx[eb + lane] : 0;
+          const float myw = eb + lane < e1 ? pwb[eb + lane] : 0.f;
+          const int cnt = e1 - eb < 32 ? e1 - eb : 32;
+          for (int j = 0; j < cnt; ++j) {
+            const float* zr = Zb + (int64_t)__shfl_sync(0xffffffffu, my, j) * 12;
+            float s = 0.f;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
+              if (pr < b * 3) s += dot4(gs[q], ld4(zr + (int64_t)cz * a.N * 12 + q4));
+            }
+            s = warp_sum(s);
+            const float dsn = __shfl_sync(0xffffffffu, myw, j) * s;
+            dl += dsn;
+            if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + eb + j] = dsn;
           }
-          s = warp_sum(s);
-          const float dsn = pwb[e] * s;
-          dl += dsn;
-          if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + e] = dsn;
         }
       }
       if (lane == 0) DL[warp] = dl;
@@ -246,7 +259,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       }
     }
     __syncthreads();
-    if (tid < TD_NT && n0 + tid < a.N) a.delta[(int64_t)bi * a.N + n0 + tid] = DL[2 * tid] + DL[2 * tid + 1];
+    if (tid < TD_NT && n0 + tid < a.N) a.delta[(int64_t)bi * a.N + n0 + tid] = DL[tid];
     // ---- 3. rows of 12: dY1, dA_now / dA_past (two threads per row), GZ gather -> the A tile again
     if (tid < 2 * b * TD_NT) {
       const int item = tid >> 1, half = tid & 1, k = item / TD_NT, nl = item - k * TD_NT, n = n0 + nl, pp = nl * 12;
@@ -306,17 +319,23 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int i = 0; i < 16; ++i) o16[i] = 0.f;
       if (n < a.N) {
         for (int tap = 0; tap < 2; ++tap) {
-          const int sh = tap ? a.d1 : 0;
-          for (int k = grp >> 3; k < b; k += 4) {
-            const float* dy = DY + k * TD_PITCH + nl * 12;
-            const float4 h = ld4(A2b + ((int64_t)(tap * b + k) * a.N + n) * 12 + ib);
-            float g[4];
+          const int sh = tap ? a.d1 : 0, kb = grp >> 3;
+          float4 h[6];   // all loads of a tap in flight before the first use (b <= 24: at most 6 rows)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
+          for (int m = 0; m < 6; ++m)
+            h[m] = kb + 4 * m < b ? ld4(A2b + ((int64_t)(tap * b + kb + 4 * m) * a.N + n) * 12 + ib) : f4zero();
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              o16[i * 4 + 0] = fmaf(g[i], h.x, o16[i * 4 + 0]); o16[i * 4 + 1] = fmaf(g[i], h.y, o16[i * 4 + 1]);
-              o16[i * 4 + 2] = fmaf(g[i], h.z, o16[i * 4 + 2]); o16[i * 4 + 3] = fmaf(g[i], h.w, o16[i * 4 + 3]);
+          for (int m = 0; m < 6; ++m) {
+            if (kb + 4 * m < b) {
+              const float* dy = DY + (kb + 4 * m) * TD_PITCH + nl * 12;
+              float g[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                o16[i * 4 + 0] = fmaf(g[i], h[m].x, o16[i * 4 + 0]); o16[i * 4 + 1] = fmaf(g[i], h[m].y, o16[i * 4 + 1]);
+                o16[i * 4 + 2] = fmaf(g[i], h[m].z, o16[i * 4 + 2]); o16[i * 4 + 3] = fmaf(g[i], h[m].w, o16[i * 4 + 3]);
+              }
             }
           }
         }
