@@ -819,6 +819,14 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   int NT = 16;
   while (NT > 4 && bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) NT >>= 1;
   if (bwd_smem_floats(p, NT, T) * 4 > MSGAT_SMEM_BUDGET + 16 * 1024) return -31;
+  // a narrow kernel (256 threads) is latency-bound at one CTA per SM: halve the tile when that
+  // lets a second CTA share the SM
+  {
+    const char* e = getenv("MSGAT_BWD_NT");
+    if (e && atoi(e) >= 4 && atoi(e) <= NT) NT = atoi(e);
+    else if (T <= 256 && NT > 4 && (bwd_smem_floats(p, NT, T) * 4 + 1024) * 2 > 227 * 1024 &&
+             (bwd_smem_floats(p, NT / 2, T) * 4 + 1024) * 2 <= 227 * 1024) NT >>= 1;
+  }
   L.NT = NT; p.NTb = NT; p.ntile_b = (p.N + NT - 1) / NT;
   {
     int64_t smem = bwd_smem_floats(p, NT, T) * 4 + 1024;
