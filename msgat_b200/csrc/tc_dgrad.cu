@@ -27,6 +27,7 @@
 #define TD_THREADS 512
 #define TD_PITCH 100
 #define TD_NGR 32      // 9-thread groups of the dPt contraction
+#define TD_ISSUER 320  // MMA-issuing thread: warp 10 has no work inside the two MMA windows, so nothing waits for the issue
 
 struct TcDgradArgs {
   const float* x; int64_t x_sb, x_sc;
@@ -189,7 +190,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     }
     fence_smem_to_async();
     __syncthreads();
-    if (tid == 0) {
+    if (tid == TD_ISSUER) {
       tc_fence_after_sync();
       for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dy, dGH, dGL, dW2H, dW2L, b / 8 + ks, ks, idescY, ks > 0);
       for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dh, dGH, dGL, dWMH, dWML, ks, ks, idescC, ks > 0);
@@ -226,18 +227,30 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           const int my = eb + lane < e1 ? a.col_idx[eb + lane] : 0;
           const float myw = eb + lane < e1 ? pwb[eb + lane] : 0.f;
           const int cnt = e1 - eb < 32 ? e1 - eb : 32;
-          for (int j = 0; j < cnt; ++j) {
-            const float* zr = Zb + (int64_t)__shfl_sync(0xffffffffu, my, j) * 12;
-            float s = 0.f;
+          for (int j = 0; j < cnt; j += 4) {   // four edges in flight: the Z rows are independent gathers
+            float s4[4];
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
-              if (pr < b * 3) s += dot4(gs[q], ld4(zr + (int64_t)cz * a.N * 12 + q4));
+            for (int u = 0; u < 4; ++u) {
+              const float* zr = Zb + (int64_t)__shfl_sync(0xffffffffu, my, (j + u) & 31) * 12;
+              float s = 0.f;
+              if (j + u < cnt) {
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                  const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
+                  if (pr < b * 3) s += dot4(gs[q], ld4(zr + (int64_t)cz * a.N * 12 + q4));
+                }
+              }
+              s4[u] = s;
             }
-            s = warp_sum(s);
-            const float dsn = __shfl_sync(0xffffffffu, myw, j) * s;
-            dl += dsn;
-            if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + eb + j] = dsn;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const float s = warp_sum(s4[u]);
+              const float dsn = __shfl_sync(0xffffffffu, myw, (j + u) & 31) * s;
+              if (j + u < cnt) {
+                dl += dsn;
+                if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + eb + j + u] = dsn;
+              }
+            }
           }
         }
       }
@@ -265,22 +278,39 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       const int item = tid >> 1, half = tid & 1, k = item / TD_NT, nl = item - k * TD_NT, n = n0 + nl, pp = nl * 12;
       const float* pn = PRE + k * TD_PITCH + pp;
       const float* pq = PRE + (b + k) * TD_PITCH + pp;
-      float v[12], o12[12];
+      float v[12], o12[12], w[12];
+      {
+        const float4 a0 = ld4(pn), a1 = ld4(pn + 4), a2 = ld4(pn + 8), b0 = ld4(pq), b1 = ld4(pq + 4), b2 = ld4(pq + 8);
+        v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w; v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
+        v[8] = a2.x; v[9] = a2.y; v[10] = a2.z; v[11] = a2.w;
+        w[0] = b0.x; w[1] = b0.y; w[2] = b0.z; w[3] = b0.w; w[4] = b1.x; w[5] = b1.y; w[6] = b1.z; w[7] = b1.w;
+        w[8] = b2.x; w[9] = b2.y; w[10] = b2.z; w[11] = b2.w;
+      }
+      // dY1[t] = now[t] + past[t + d2]; the shift is a compile-time-indexed select chain (registers only)
 #pragma unroll
-      for (int t = 0; t < 12; ++t) v[t] = pn[t] + (t + a.d2 < 12 ? pq[t + a.d2 < 12 ? t + a.d2 : 0] : 0.f);
+      for (int t = 0; t < 12; ++t) {
+        float sft = 0.f;
+#pragma unroll
+        for (int q = 1; q < 12; ++q) sft = (q == t + a.d2) ? w[q] : sft;
+        v[t] += sft;
+      }
       const float* P = half ? Ptd : Pt;
 #pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        float s = 0.f;
+      for (int j = 0; j < 12; ++j) o12[j] = 0.f;
 #pragma unroll
-        for (int t = 0; t < 12; ++t) s = fmaf(P[t * 12 + j], v[t], s);
-        o12[j] = s;
+      for (int t = 0; t < 12; ++t) {
+        const float4 p0 = ld4(P + t * 12), p1 = ld4(P + t * 12 + 4), p2 = ld4(P + t * 12 + 8);
+        o12[0] = fmaf(p0.x, v[t], o12[0]); o12[1] = fmaf(p0.y, v[t], o12[1]); o12[2] = fmaf(p0.z, v[t], o12[2]); o12[3] = fmaf(p0.w, v[t], o12[3]);
+        o12[4] = fmaf(p1.x, v[t], o12[4]); o12[5] = fmaf(p1.y, v[t], o12[5]); o12[6] = fmaf(p1.z, v[t], o12[6]); o12[7] = fmaf(p1.w, v[t], o12[7]);
+        o12[8] = fmaf(p2.x, v[t], o12[8]); o12[9] = fmaf(p2.y, v[t], o12[9]); o12[10] = fmaf(p2.z, v[t], o12[10]); o12[11] = fmaf(p2.w, v[t], o12[11]);
       }
       if (!half) {
         float* dy = DY + k * TD_PITCH + pp;
         float s = 0.f;
 #pragma unroll
-        for (int t = 0; t < 12; ++t) { dy[t] = v[t]; s += v[t]; }
+        for (int t = 0; t < 12; ++t) s += v[t];
+        st4(dy, make_float4(v[0], v[1], v[2], v[3])); st4(dy + 4, make_float4(v[4], v[5], v[6], v[7]));
+        st4(dy + 8, make_float4(v[8], v[9], v[10], v[11]));
         bsY += s;
       }
       const int row = half * b + k;
@@ -304,7 +334,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     }
     fence_smem_to_async();
     __syncthreads();
-    if (tid == 0) {
+    if (tid == TD_ISSUER) {
       tc_fence_after_sync();
       for (int ks = 0; ks < O / 8; ++ks) td_mma3(Dh, dGH, dGL, dW3H, dW3L, ks, ks, idescC, 1u);
       umma_commit(smem_u32(&bar));
@@ -319,7 +349,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int i = 0; i < 16; ++i) o16[i] = 0.f;
       if (n < a.N) {
         for (int tap = 0; tap < 2; ++tap) {
-          const int sh = tap ? a.d1 : 0, kb = grp >> 3;
+          const int sh = tap ? a.d1 : 0, kb = grp >> 3, sr = sh & 3, q0 = tb + (sh & ~3);
           float4 h[6];   // all loads of a tap in flight before the first use (b <= 24: at most 6 rows)
 #pragma unroll
           for (int m = 0; m < 6; ++m)
@@ -328,9 +358,13 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           for (int m = 0; m < 6; ++m) {
             if (kb + 4 * m < b) {
               const float* dy = DY + (kb + 4 * m) * TD_PITCH + nl * 12;
+              // g[i] = dY1[tb + i + sh] (0 past the end): two aligned float4 and a uniform select
+              const float4 ga = q0 < 12 ? ld4(dy + q0) : f4zero(), gb = (sr && q0 + 4 < 12) ? ld4(dy + q0 + 4) : f4zero();
               float g[4];
-#pragma unroll
-              for (int i = 0; i < 4; ++i) g[i] = tb + i + sh < 12 ? dy[tb + i + sh < 12 ? tb + i + sh : 0] : 0.f;
+              if (sr == 0) { g[0] = ga.x; g[1] = ga.y; g[2] = ga.z; g[3] = ga.w; }
+              else if (sr == 1) { g[0] = ga.y; g[1] = ga.z; g[2] = ga.w; g[3] = gb.x; }
+              else if (sr == 2) { g[0] = ga.z; g[1] = ga.w; g[2] = gb.x; g[3] = gb.y; }
+              else { g[0] = ga.w; g[1] = gb.x; g[2] = gb.y; g[3] = gb.z; }
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 o16[i * 4 + 0] = fmaf(g[i], h[m].x, o16[i * 4 + 0]); o16[i * 4 + 1] = fmaf(g[i], h[m].y, o16[i * 4 + 1]);
@@ -391,10 +425,12 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           const float rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
           float* qrow = STG + c * TD_PITCH + nl * 12;
           float gg[12], m1 = 0.f, m2 = 0.f;
+          const float4 d0 = ld4(qrow), d1 = ld4(qrow + 4), d2 = ld4(qrow + 8);
+          const float dhv[12] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x, d2.y, d2.z, d2.w};
 #pragma unroll
           for (int t = 0; t < 12; ++t) {
             xh[t] *= rs;
-            const float dh = qrow[t];
+            const float dh = dhv[t];
             lnw_acc[t] = fmaf(dh, xh[t], lnw_acc[t]);
             lnb_acc[t] += dh;
             gg[t] = dh * LW[t];
@@ -402,7 +438,9 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           }
           m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
 #pragma unroll
-          for (int t = 0; t < 12; ++t) qrow[t] = rs * (gg[t] - m1 - xh[t] * m2);
+          for (int t = 0; t < 12; ++t) gg[t] = rs * (gg[t] - m1 - xh[t] * m2);
+          st4(qrow, make_float4(gg[0], gg[1], gg[2], gg[3])); st4(qrow + 4, make_float4(gg[4], gg[5], gg[6], gg[7]));
+          st4(qrow + 8, make_float4(gg[8], gg[9], gg[10], gg[11]));
         }
       }
     }
