@@ -51,25 +51,43 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
     __syncthreads();
     for (int i = threadIdx.x; i < len * 3; i += blockDim.x) st4(Q + i * 4, ld4(qb + (int64_t)j0 * 12 + i * 4));
     __syncthreads();
-    for (int j = cl; j < len; j += SS_LANES) {
-      const float* qj = Q + j * 12;
-      float4 q0 = ld4(qj), q1 = ld4(qj + 4), q2 = ld4(qj + 8);
-      float s = U[0] * q0.x;
-      s = fmaf(U[1], q0.y, s); s = fmaf(U[2], q0.z, s); s = fmaf(U[3], q0.w, s);
-      s = fmaf(U[4], q1.x, s); s = fmaf(U[5], q1.y, s); s = fmaf(U[6], q1.z, s); s = fmaf(U[7], q1.w, s);
-      s = fmaf(U[8], q2.x, s); s = fmaf(U[9], q2.y, s); s = fmaf(U[10], q2.z, s); s = fmaf(U[11], q2.w, s);
-      if (s > m) {
-        const double c = (double)expf(m - s);
+    // Four columns per step: the scores and the products p * q of a group are summed in fp32 (p itself
+    // is an fp32 expf), the running sums stay in fp64 -- one conversion per group instead of one per pair.
+    for (int j = cl; j < len; j += 4 * SS_LANES) {
+      float4 q[4][3];
+      float sc4[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int ju = j + u * SS_LANES;
+        const float* qj = Q + (ju < len ? ju : j) * 12;
+        q[u][0] = ld4(qj); q[u][1] = ld4(qj + 4); q[u][2] = ld4(qj + 8);
+        float sv = U[0] * q[u][0].x;
+        sv = fmaf(U[1], q[u][0].y, sv); sv = fmaf(U[2], q[u][0].z, sv); sv = fmaf(U[3], q[u][0].w, sv);
+        sv = fmaf(U[4], q[u][1].x, sv); sv = fmaf(U[5], q[u][1].y, sv); sv = fmaf(U[6], q[u][1].z, sv); sv = fmaf(U[7], q[u][1].w, sv);
+        sv = fmaf(U[8], q[u][2].x, sv); sv = fmaf(U[9], q[u][2].y, sv); sv = fmaf(U[10], q[u][2].z, sv); sv = fmaf(U[11], q[u][2].w, sv);
+        sc4[u] = ju < len ? sv : -INFINITY;
+      }
+      const float mg = fmaxf(fmaxf(sc4[0], sc4[1]), fmaxf(sc4[2], sc4[3]));
+      if (mg > m) {
+        const double c = (double)expf(m - mg);
         l *= c;
         for (int t = 0; t < 12; ++t) E[t] *= c;
-        m = s;
+        m = mg;
       }
-      const double p = (double)expf(s - m);
-      l += p;
-      E[0] = fma(p, (double)q0.x, E[0]); E[1] = fma(p, (double)q0.y, E[1]); E[2] = fma(p, (double)q0.z, E[2]);
-      E[3] = fma(p, (double)q0.w, E[3]); E[4] = fma(p, (double)q1.x, E[4]); E[5] = fma(p, (double)q1.y, E[5]);
-      E[6] = fma(p, (double)q1.z, E[6]); E[7] = fma(p, (double)q1.w, E[7]); E[8] = fma(p, (double)q2.x, E[8]);
-      E[9] = fma(p, (double)q2.y, E[9]); E[10] = fma(p, (double)q2.z, E[10]); E[11] = fma(p, (double)q2.w, E[11]);
+      float lc = 0.f, Ec[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) Ec[t] = 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float pf = expf(sc4[u] - m);   // 0 for the padded columns
+        lc += pf;
+        Ec[0] = fmaf(pf, q[u][0].x, Ec[0]); Ec[1] = fmaf(pf, q[u][0].y, Ec[1]); Ec[2] = fmaf(pf, q[u][0].z, Ec[2]); Ec[3] = fmaf(pf, q[u][0].w, Ec[3]);
+        Ec[4] = fmaf(pf, q[u][1].x, Ec[4]); Ec[5] = fmaf(pf, q[u][1].y, Ec[5]); Ec[6] = fmaf(pf, q[u][1].z, Ec[6]); Ec[7] = fmaf(pf, q[u][1].w, Ec[7]);
+        Ec[8] = fmaf(pf, q[u][2].x, Ec[8]); Ec[9] = fmaf(pf, q[u][2].y, Ec[9]); Ec[10] = fmaf(pf, q[u][2].z, Ec[10]); Ec[11] = fmaf(pf, q[u][2].w, Ec[11]);
+      }
+      l += (double)lc;
+#pragma unroll
+      for (int t = 0; t < 12; ++t) E[t] += (double)Ec[t];
     }
   }
   // combine the 8 column lanes of each row (lanes of a row are adjacent in the warp)
@@ -135,7 +153,7 @@ struct SColArgs {
 
 MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][20]: U[12], m, pad, w = delta / l as one fp64 in slots 14-15; the 80-byte pitch keeps the 8 row lanes on distinct banks
+  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][20]: U[12], m, w = delta / l; the 80-byte pitch keeps the 8 row lanes on distinct banks
   const int b = blockIdx.y, rl = threadIdx.x / SS_LANES, cl = threadIdx.x % SS_LANES;
   const int i = blockIdx.x * SS_ROWS + rl;
   const bool live = i < a.N;
@@ -155,23 +173,32 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     for (int r = threadIdx.x; r < len; r += blockDim.x) {
       const int64_t g = (int64_t)b * a.N + n0 + r;
       UR[r * 20 + 12] = a.m[g];
-      *reinterpret_cast<double*>(UR + r * 20 + 14) = (double)a.delta[g] / a.l[g];
+      UR[r * 20 + 13] = (float)((double)a.delta[g] / a.l[g]);
     }
     __syncthreads();
-    for (int r = cl; r < len; r += SS_LANES) {
-      const float* u = UR + r * 20;
-      float4 u0 = ld4(u), u1 = ld4(u + 4), u2 = ld4(u + 8), u3 = ld4(u + 12);
-      float s = qi[0] * u0.x;
-      s = fmaf(qi[1], u0.y, s); s = fmaf(qi[2], u0.z, s); s = fmaf(qi[3], u0.w, s);
-      s = fmaf(qi[4], u1.x, s); s = fmaf(qi[5], u1.y, s); s = fmaf(qi[6], u1.z, s); s = fmaf(qi[7], u1.w, s);
-      s = fmaf(qi[8], u2.x, s); s = fmaf(qi[9], u2.y, s); s = fmaf(qi[10], u2.z, s); s = fmaf(qi[11], u2.w, s);
-      const double p = (double)expf(s - u3.x) * *reinterpret_cast<const double*>(u + 14);
-      acc[0] = fma(p, (double)u0.x, acc[0]); acc[1] = fma(p, (double)u0.y, acc[1]);
-      acc[2] = fma(p, (double)u0.z, acc[2]); acc[3] = fma(p, (double)u0.w, acc[3]);
-      acc[4] = fma(p, (double)u1.x, acc[4]); acc[5] = fma(p, (double)u1.y, acc[5]);
-      acc[6] = fma(p, (double)u1.z, acc[6]); acc[7] = fma(p, (double)u1.w, acc[7]);
-      acc[8] = fma(p, (double)u2.x, acc[8]); acc[9] = fma(p, (double)u2.y, acc[9]);
-      acc[10] = fma(p, (double)u2.z, acc[10]); acc[11] = fma(p, (double)u2.w, acc[11]);
+    // four rows per step, summed in fp32 inside the group and in fp64 across groups (see k_sstats)
+    for (int r = cl; r < len; r += 4 * SS_LANES) {
+      float ac[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) ac[t] = 0.f;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int rg = r + g * SS_LANES;
+        if (rg < len) {
+          const float* u = UR + rg * 20;
+          const float4 u0 = ld4(u), u1 = ld4(u + 4), u2 = ld4(u + 8), u3 = ld4(u + 12);
+          float sv = qi[0] * u0.x;
+          sv = fmaf(qi[1], u0.y, sv); sv = fmaf(qi[2], u0.z, sv); sv = fmaf(qi[3], u0.w, sv);
+          sv = fmaf(qi[4], u1.x, sv); sv = fmaf(qi[5], u1.y, sv); sv = fmaf(qi[6], u1.z, sv); sv = fmaf(qi[7], u1.w, sv);
+          sv = fmaf(qi[8], u2.x, sv); sv = fmaf(qi[9], u2.y, sv); sv = fmaf(qi[10], u2.z, sv); sv = fmaf(qi[11], u2.w, sv);
+          const float pf = expf(sv - u3.x) * u3.y;   // u3.y = (float)(delta / l)
+          ac[0] = fmaf(pf, u0.x, ac[0]); ac[1] = fmaf(pf, u0.y, ac[1]); ac[2] = fmaf(pf, u0.z, ac[2]); ac[3] = fmaf(pf, u0.w, ac[3]);
+          ac[4] = fmaf(pf, u1.x, ac[4]); ac[5] = fmaf(pf, u1.y, ac[5]); ac[6] = fmaf(pf, u1.z, ac[6]); ac[7] = fmaf(pf, u1.w, ac[7]);
+          ac[8] = fmaf(pf, u2.x, ac[8]); ac[9] = fmaf(pf, u2.y, ac[9]); ac[10] = fmaf(pf, u2.z, ac[10]); ac[11] = fmaf(pf, u2.w, ac[11]);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 12; ++t) acc[t] += (double)ac[t];
     }
   }
   for (int t = 0; t < 12; ++t) {
