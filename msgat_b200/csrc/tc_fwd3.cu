@@ -58,13 +58,13 @@ TC_DEV void tf3_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float
   *reinterpret_cast<float*>(lo + off) = tf3_rna(v - h);
 }
 // acc (+)= Ah Bh + Ah Bl + Al Bh for one k-step; descriptors: MN-major, 128 B swizzle with 32 B atoms
-TC_DEV void mma3(uint32_t d, uint32_t ah, uint32_t al, uint32_t cba, uint32_t bh, uint32_t bl, uint32_t cbb, uint32_t idesc,
-                 uint32_t acc) {
-  const uint64_t dah = umma_desc(ah, cba, 512u, 1), dal = umma_desc(al, cba, 512u, 1);
-  const uint64_t dbh = umma_desc(bh, cbb, 512u, 1), dbl = umma_desc(bl, cbb, 512u, 1);
-  umma_tf32(d, dah, dbh, idesc, acc);
-  umma_tf32(d, dah, dbl, idesc, 1u);
-  umma_tf32(d, dal, dbh, idesc, 1u);
+// The descriptors of k-step 0 are built once; k-step ks (8 contraction rows = 1024 B) adds ks * 64 to the
+// start-address field (16-byte units).
+TC_DEV void mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64_t dbl, uint32_t ks, uint32_t idesc, uint32_t acc) {
+  const uint64_t o = (uint64_t)(ks * 64u);
+  umma_tf32(d, dah + o, dbh + o, idesc, acc);
+  umma_tf32(d, dah + o, dbl + o, idesc, 1u);
+  umma_tf32(d, dal + o, dbh + o, idesc, 1u);
 }
 
 __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
@@ -127,8 +127,11 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
   tc_fence_after_sync();
   const uint32_t tm = tmem_slot;
   const uint32_t D1 = tm, D2 = tm + 96, D3 = tm + 192;
-  const uint32_t sAH = smem_u32(AH), sAL = smem_u32(AL), sWRH = smem_u32(WRH), sWRL = smem_u32(WRL), sWHH = smem_u32(WHH),
-                 sWHL = smem_u32(WHL), sW2H = smem_u32(W2H), sW2L = smem_u32(W2L), sYH = smem_u32(YH), sYL = smem_u32(YL);
+  const uint64_t dAH = umma_desc(smem_u32(AH), cbX, 512u, 1), dAL = umma_desc(smem_u32(AL), cbX, 512u, 1);
+  const uint64_t dWRH = umma_desc(smem_u32(WRH), cbX, 512u, 1), dWRL = umma_desc(smem_u32(WRL), cbX, 512u, 1);
+  const uint64_t dWHH = umma_desc(smem_u32(WHH), cbX, 512u, 1), dWHL = umma_desc(smem_u32(WHL), cbX, 512u, 1);
+  const uint64_t dW2H = umma_desc(smem_u32(W2H), cbY, 512u, 1), dW2L = umma_desc(smem_u32(W2L), cbY, 512u, 1);
+  const uint64_t dYH = umma_desc(smem_u32(YH), cbY, 512u, 1), dYL = umma_desc(smem_u32(YL), cbY, 512u, 1);
   const uint32_t idesc80 = umma_idesc_tf32(128, 80, 1, 1), idesc32 = umma_idesc_tf32(128, 32, 1, 1);
   uint32_t phase = 0;
   const int l = tid & 127, quarter = warp >> 2;    // l = TMEM lane = position; the 4 warpgroups split the column groups
@@ -157,8 +160,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
-      for (int ks = 0; ks < C / 8; ++ks)
-        mma3(D1, sAH + ks * 1024u, sAL + ks * 1024u, cbX, sWRH + ks * 1024u, sWRL + ks * 1024u, cbX, idesc80, ks > 0);
+      for (int ks = 0; ks < C / 8; ++ks) mma3(D1, dAH, dAL, dWRH, dWRL, ks, idesc80, ks > 0);
       umma_commit(smem_u32(&bar));
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
@@ -188,8 +190,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
-      for (int ks = 0; ks < C / 8; ++ks)
-        mma3(D2, sAH + ks * 1024u, sAL + ks * 1024u, cbX, sWHH + ks * 1024u, sWHL + ks * 1024u, cbX, idesc80, ks > 0);
+      for (int ks = 0; ks < C / 8; ++ks) mma3(D2, dAH, dAL, dWHH, dWHL, ks, idesc80, ks > 0);
       umma_commit(smem_u32(&bar));
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
@@ -256,8 +257,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
     // ---- 5. D3 = [y1 ; shift(y1)]^T [Wnow2 ; Wpast2]^T
     if (tid == 0) {
       tc_fence_after_sync();
-      for (int ks = 0; ks < 2 * b / 8; ++ks)
-        mma3(D3, sYH + ks * 1024u, sYL + ks * 1024u, cbY, sW2H + ks * 1024u, sW2L + ks * 1024u, cbY, idesc32, ks > 0);
+      for (int ks = 0; ks < 2 * b / 8; ++ks) mma3(D3, dYH, dYL, dW2H, dW2L, ks, idesc32, ks > 0);
       umma_commit(smem_u32(&bar));
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
