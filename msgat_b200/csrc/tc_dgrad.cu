@@ -174,6 +174,18 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
 
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
     const int n0 = tile * TD_NT;
+    // L2 prefetch of what this tile reads late and latency-bound: the saved first-conv taps (dPt, inside
+    // the second MMA window) and the x rows of the LayerNorm backward.  One 128-byte line per thread.
+    {
+      const int nrow = 2 * b + C, seg = tid >> 2, part = tid & 3;   // a row segment = 8 nodes x 48 B = 384 B
+      for (int sgi = seg; sgi < nrow; sgi += TD_THREADS / 4) {
+        const float* base = sgi < 2 * b ? A2b + (int64_t)sgi * a.N * 12 : xb + (int64_t)(sgi - 2 * b) * a.x_sc;
+        int64_t off = (int64_t)n0 * 12 + part * 32;                 // floats
+        const int64_t last = (int64_t)a.N * 12 - 1;
+        if (off > last) off = last;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));
+      }
+    }
     // ---- 1. G rows -> the A tile (hi / lo); row sums for the bias gradients
 #pragma unroll
     for (int q = 0; q < 2; ++q) {

@@ -137,6 +137,21 @@ def test_tc_data_gradients_match_fp32_kernels(name, B):
     assert rows[0][0] < 2e-5, rows[:5]
 
 
+@pytest.mark.parametrize("name,B", [("pemsd8", 3), ("pemsd7", 2)])
+def test_default_path_gradients_are_bit_reproducible(name, B):
+    """Two identical training steps on the default path (tcgen05 forward, data-gradient and weight-gradient
+    kernels, fixed-order partial reductions) give bit-identical outputs and gradients: no atomics, no races
+    between the producer threads, the MMA-issuing thread and the epilogues."""
+    from msgat_b200 import _lib
+    m1, _, X1, o1 = _run_tc_model(name, B, 0, _lib.PREC_FP32)
+    m2, _, X2, o2 = _run_tc_model(name, B, 0, _lib.PREC_FP32)
+    assert torch.equal(o1, o2)
+    assert torch.equal(X1.grad, X2.grad)
+    for (n, a), (_, b) in zip(m1.named_parameters(), m2.named_parameters()):
+        if a.grad is not None:
+            assert torch.equal(a.grad, b.grad), n
+
+
 @pytest.mark.parametrize("name,B", [("pemsd8", 3)])
 def test_tc_gradients_against_oracle_are_mask_flip_limited(name, B):
     """Against the fp64 oracle the TF32 path's gradients differ mostly because a few ReLU
