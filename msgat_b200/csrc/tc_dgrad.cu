@@ -512,8 +512,8 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
 bool tc_dgrad_supported(const Plan& p) {
   const char* off = getenv("MSGAT_TC_DISABLE");  // test switch: bit 2 = data-gradient kernel
   if (off && (atoi(off) & 4)) return false;
-  // needs the first-conv taps (A2) kept by k_tc_apply3 and the weight-gradient kernel for dA / GZ
-  return tc_apply3_supported(p) && tc_wgrad_supported(p) && p.O == 3 * p.Oc;
+  // needs the first-conv taps (A2) kept by the tcgen05 forward kernels and the weight-gradient kernel for dA / GZ
+  return (tc_apply3_supported(p) || tc_apply_supported(p)) && tc_wgrad_supported(p) && p.O == 3 * p.Oc;
 }
 
 int tc_dgrad_blocks_per_sample(const Plan& p) {

@@ -32,6 +32,7 @@ struct TcApplyArgs {
   const int32_t *row_ptr, *col_idx;
   float* out;
   float* Y1;  // [B,b,N,12] first-conv output, kept for the weight gradients
+  float* A2;  // [B,2b,N,12] first-conv taps before the temporal mix, kept for dPt (k_tc_dgrad)
 };
 
 // bytes of one operand tile with R rows and W positions
@@ -171,6 +172,14 @@ __global__ void __launch_bounds__(TCF_THREADS, 1) k_tc_apply(TcApplyArgs a) {
 #pragma unroll
       for (int i = 0; i < 12; ++i) { vn[i] = an[i]; vp[i] = ap[i]; }
       const float bias = c1B[o];
+      if (n0 + nl < a.N) {
+        float* an2 = a.A2 + (((int64_t)bi * 2 * b + o) * a.N + n0 + nl) * 12;
+        float* ap2 = a.A2 + (((int64_t)bi * 2 * b + b + o) * a.N + n0 + nl) * 12;
+        st4(an2, make_float4(vn[0], vn[1], vn[2], vn[3])); st4(an2 + 4, make_float4(vn[4], vn[5], vn[6], vn[7]));
+        st4(an2 + 8, make_float4(vn[8], vn[9], vn[10], vn[11]));
+        st4(ap2, make_float4(vp[0], vp[1], vp[2], vp[3])); st4(ap2 + 4, make_float4(vp[4], vp[5], vp[6], vp[7]));
+        st4(ap2 + 8, make_float4(vp[8], vp[9], vp[10], vp[11]));
+      }
 #pragma unroll
       for (int t = 0; t < 12; ++t) {
         float s = bias;
@@ -270,7 +279,7 @@ int launch_tc_apply(const Plan& p, const msgat_meam_params* prm, const msgat_adj
   a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.res_b = prm->res_b; a.ca_b = prm->ca_b;
   a.c1_w = prm->conv_w[0]; a.c1_b = prm->conv_b[0]; a.c2_w = prm->conv_w[1]; a.c2_b = prm->conv_b[1];
   a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
-  a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out; a.Y1 = saved + p.o_Y1;
+  a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out; a.Y1 = saved + p.o_Y1; a.A2 = saved + p.o_A2;
   int J = 148 / p.B;  // one CTA per SM (512 TMEM columns each), all tiles of a CTA in one sample
   if (J > a.ntile) J = a.ntile;
   if (J < 1) J = 1;
