@@ -140,8 +140,20 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
   const float* pwb = a.pw + (int64_t)bi * a.nnz;
   const float* Zb = a.Z + (int64_t)bi * b * a.N * 12;
 
+  // the one column group (if any) of this thread's quarter that holds spatial channels
+  int sp_c0 = -1;
+  { int g = 0; for (int c0 = 0; c0 < O; c0 += 8, ++g) if ((g & 3) == quarter && c0 >= 2 * b) sp_c0 = c0; }
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
     const int n0 = tile * TF3_NT;
+    // L2 prefetch of the next tile's x rows (8 nodes x 48 B = 384 B per channel), one 128-byte line per thread
+    if (tile + a.J < a.ntile) {
+      for (int i = tid; i < C * 4; i += TF3_THREADS) {
+        int64_t off = (int64_t)(n0 + a.J * TF3_NT) * 12 + (i & 3) * 32;
+        const int64_t last = (int64_t)a.N * 12 - 1;
+        if (off > last) off = last;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(xb + (i >> 2) * a.x_sc + off));
+      }
+    }
     // ---- 1. x rows -> registers and the A tiles (hi / lo)
     float4 xr[2][3];
 #pragma unroll
@@ -162,6 +174,24 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
       tc_fence_after_sync();
       for (int ks = 0; ks < C / 8; ++ks) mma3(D1, dAH, dAL, dWRH, dWRL, ks, idesc80, ks > 0);
       umma_commit(smem_u32(&bar));
+    }
+    // ---- while the tensor core runs: sparse spatial aggregation of this thread's 8 channels
+    // (attention.py:36 at the adjacency non-zeros); the values wait in registers for the epilogue
+    float sp[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sp[j] = 0.f;
+    if (sp_c0 >= 0) {
+      const int nl = l / 12, n = n0 + nl, t = l - nl * 12;
+      if (l < TF3_P && n < a.N) {
+        const int64_t cs = (int64_t)a.N * 12;
+        const int e1 = a.row_ptr[n + 1];
+        for (int e = a.row_ptr[n]; e < e1; ++e) {
+          const float w = pwb[e];
+          const float* z = Zb + ((int64_t)(sp_c0 - 2 * b) * a.N + a.col_idx[e]) * 12 + t;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sp[j] = fmaf(w, z[j * cs], sp[j]);
+        }
+      }
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
     tc_fence_after_sync();
@@ -268,8 +298,6 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
       const bool live = l < TF3_P && n < a.N;
       float* ob = a.out + (int64_t)bi * O * a.N * 12 + (int64_t)n * 12 + t;
       const int64_t cs = (int64_t)a.N * 12;
-      int e0 = 0, e1 = 0;
-      if (live) { e0 = a.row_ptr[n]; e1 = a.row_ptr[n + 1]; }
       int g = 0;
       for (int c0 = 0; c0 < O; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;   // warp-uniform
@@ -285,13 +313,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
           for (int j = 0; j < 8; ++j) v[j] += c2B[c0 - b + j];
         } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = 0.f;
-          for (int e = e0; e < e1; ++e) {  // attention.py:36 at the adjacency non-zeros
-            const float w = pwb[e];
-            const float* z = Zb + ((int64_t)(c0 - 2 * b) * a.N + a.col_idx[e]) * 12 + t;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaf(w, z[j * cs], v[j]);
-          }
+          for (int j = 0; j < 8; ++j) v[j] = sp[j];   // gathered inside the first MMA window (c0 == sp_c0)
         }
         if (live) {
 #pragma unroll
