@@ -2,6 +2,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "plan.h"
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
@@ -13,6 +14,15 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
                        void* stream);
 int64_t meam_backward_scratch(Plan& p);
 void msgat_set_error(const char* fmt, ...);
+// CTAs per sample of a one-CTA-per-SM tcgen05 kernel whose CTAs stay inside a sample (per-sample weights):
+// `waves` rounds of 148 CTAs; more waves waste fewer SMs (148 is not a multiple of B) but repeat the set-up.
+static inline int tc_ctas_per_sample(int B, int ntile, int waves, const char* env) {
+  const char* e = getenv(env);
+  if (e && atoi(e) > 0) waves = atoi(e);
+  int J = (148 * waves) / B;
+  if (J > ntile) J = ntile;
+  return J < 1 ? 1 : J;
+}
 // tensor-core (tcgen05 kind::tf32) kernels, tc_*.cu: MSGAT_PREC_TF32 on the layer-2 MEAM shape
 bool tc_apply_supported(const Plan& p);
 bool tc_apply3_supported(const Plan& p);

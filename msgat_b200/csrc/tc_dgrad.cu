@@ -518,9 +518,7 @@ bool tc_dgrad_supported(const Plan& p) {
 
 int tc_dgrad_blocks_per_sample(const Plan& p) {
   const int ntile = (p.N + TD_NT - 1) / TD_NT;
-  int J = 148 / p.B;
-  if (J > ntile) J = ntile;
-  return J < 1 ? 1 : J;
+  return tc_ctas_per_sample(p.B, ntile, 2, "MSGAT_TD_WAVES");
 }
 
 int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,

@@ -280,9 +280,7 @@ int launch_tc_apply(const Plan& p, const msgat_meam_params* prm, const msgat_adj
   a.c1_w = prm->conv_w[0]; a.c1_b = prm->conv_b[0]; a.c2_w = prm->conv_w[1]; a.c2_b = prm->conv_b[1];
   a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
   a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out; a.Y1 = saved + p.o_Y1; a.A2 = saved + p.o_A2;
-  int J = 148 / p.B;  // one CTA per SM (512 TMEM columns each), all tiles of a CTA in one sample
-  if (J > a.ntile) J = a.ntile;
-  if (J < 1) J = 1;
+  const int J = tc_ctas_per_sample(p.B, a.ntile, 2, "MSGAT_TF_WAVES");  // one CTA per SM (512 TMEM columns each), all tiles of a CTA in one sample
   a.J = J;
   const size_t smem = tc_apply_smem(p.C, p.Oc);
   MSGAT_LAUNCH(k_tc_apply, dim3(J, p.B), dim3(TCF_THREADS), smem, stream, a);

@@ -327,9 +327,7 @@ bool tc_wgrad_supported(const Plan& p) {
 
 int tc_wgrad_blocks_per_sample(const Plan& p) {
   const int ntile = (p.N + TCW_NT - 1) / TCW_NT;
-  int J = 148 / p.B;
-  if (J > ntile) J = ntile;
-  return J < 1 ? 1 : J;
+  return tc_ctas_per_sample(p.B, ntile, 2, "MSGAT_TW_WAVES");
 }
 
 int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
