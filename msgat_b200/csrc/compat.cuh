@@ -70,22 +70,24 @@ MSGAT_DEV void fma4(float4& a, float w, const float4& x) {
 MSGAT_DEV float dot4(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
 // value of a 12-step row at t-d for t = t0..t0+3, given the quad at t0 and the quad before it
 // (zeros when t0 == 0): the causal "past" tap of Conv2d(k=[1,2], dilation d) + Chomp(d).
+// Two aligned float4 loads and a select on the sub-quad shift replace four predicated scalar loads:
+// rows are 16-byte aligned, t0 is a multiple of 4, d is uniform over the block.
+MSGAT_DEV float4 quad_shifted(const float4& A, const float4& B, int r) {
+  if (r == 0) return A;
+  if (r == 1) return make_float4(A.y, A.z, A.w, B.x);
+  if (r == 2) return make_float4(A.z, A.w, B.x, B.y);
+  return make_float4(A.w, B.x, B.y, B.z);
+}
 MSGAT_DEV float4 quad_past(const float* row, int t0, int d) {
-  float4 r;
-  int t = t0 - d;
-  r.x = (t >= 0) ? row[t] : 0.f;
-  r.y = (t + 1 >= 0) ? row[t + 1] : 0.f;
-  r.z = (t + 2 >= 0) ? row[t + 2] : 0.f;
-  r.w = (t + 3 >= 0) ? row[t + 3] : 0.f;
-  return r;
+  const int t = t0 - d, q0 = t & ~3, r = t & 3;   // floor to a quad boundary (also for negative t)
+  const float4 A = (q0 >= 0) ? ld4(row + q0) : f4zero();
+  const float4 B = (r != 0 && q0 + 4 >= 0) ? ld4(row + q0 + 4) : f4zero();   // q0 + 4 <= t0 < 12
+  return quad_shifted(A, B, r);
 }
 // value at t+d (transpose of the past tap), zero beyond the 12-step window
 MSGAT_DEV float4 quad_future(const float* row, int t0, int d) {
-  float4 r;
-  int t = t0 + d;
-  r.x = (t < MSGAT_T12) ? row[t] : 0.f;
-  r.y = (t + 1 < MSGAT_T12) ? row[t + 1] : 0.f;
-  r.z = (t + 2 < MSGAT_T12) ? row[t + 2] : 0.f;
-  r.w = (t + 3 < MSGAT_T12) ? row[t + 3] : 0.f;
-  return r;
+  const int t = t0 + d, q0 = t & ~3, r = t & 3;
+  const float4 A = (q0 < MSGAT_T12) ? ld4(row + q0) : f4zero();
+  const float4 B = (r != 0 && q0 + 4 < MSGAT_T12) ? ld4(row + q0 + 4) : f4zero();
+  return quad_shifted(A, B, r);
 }

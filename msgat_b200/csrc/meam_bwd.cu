@@ -46,6 +46,7 @@ struct BwdArgs {
   int nbias, arena_floats, S;
   float* tcA;  // [B,3b,N,12] dA_now | dA_past | GZ for the tensor-core weight-gradient kernel (null: not used)
   int skip_wgrad;  // weight gradients come from the tensor-core kernel (tc_wgrad.cu) instead
+  int resident;    // the backward-chain weights are staged once per CTA, not once per tile and phase
 };
 
 // acc[r] (+)= A[oa..oa+3][p] . B[kb..kb+3][p] over the tile's positions, for the blocks of job jb
@@ -124,6 +125,17 @@ static int bwd_arena_floats(const Plan& p, int nthreads) {
   v = (nthreads / 32) * 24; a = v > a ? v : a;
   return rup4(a);
 }
+// Backward-chain weights small enough to stay in shared memory for the whole kernel (layer-1 MEAMs):
+// Mc, both taps of every conv, Ws, Wres, in the [rows][rup4(K)] layout of stage_w.  0 = restage per tile.
+static int bwd_resident_floats(const Plan& p) {
+  const int RC = rup4(p.C);
+  int f = 0;
+  if (p.Oc) f += p.Oc * RC;
+  for (int i = 0; i < p.n_conv; ++i) f += 2 * p.Ot * rup4(i == 0 ? p.C : p.Ot);
+  if (p.Os && (p.flags & MSGAT_F_SMIX)) f += p.Os * RC;
+  if (p.flags & MSGAT_F_RES) f += p.O * RC;
+  return f <= 4096 ? f : 0;
+}
 static int64_t bwd_smem_floats(const Plan& p, int NT, int nthreads) {
   const int PS = NT * 12 + 4;
   int64_t f = 0;
@@ -134,6 +146,7 @@ static int64_t bwd_smem_floats(const Plan& p, int NT, int nthreads) {
   if (p.Os && (p.flags & MSGAT_F_SMIX) && !p.s_pre) f += (int64_t)p.C * PS;                // DOS
   f += rup4(p.C * NT * 2) + 144 + 24;
   f += bwd_arena_floats(p, nthreads);
+  f += bwd_resident_floats(p);
   return f;
 }
 
@@ -161,6 +174,8 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   float* Pt = sp; sp += 144;
   float* LW = sp; sp += 24;
   float* AR = sp;  // arena
+  float* RW = AR + a.arena_floats;  // resident weights (a.resident)
+  float *rMc = nullptr, *rWn[MSGAT_MAX_CONV], *rWp[MSGAT_MAX_CONV], *rWs = nullptr, *rWres = nullptr;
   const int Ooff = a.Oc + a.Ot;
   const int chC = (C + 3) >> 2;
   const int blk = b * a.J + blockIdx.x;
@@ -169,6 +184,18 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   const float* Zb = a.Z + (int64_t)b * a.Cz * a.N * 12;
 
   if (a.Ot) for (int i = tid; i < 144; i += T) Pt[i] = a.Pt[(int64_t)b * 144 + i];
+  if (a.resident) {   // stage every backward-chain weight once instead of once per tile and phase
+    float* q = RW;
+    if (a.Oc) { rMc = q; q += a.Oc * RC; stage_w(rMc, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, RC, 1, 0); }
+    for (int i = 0; i < a.n_conv; ++i) {
+      const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
+      rWn[i] = q; q += a.Ot * RK; rWp[i] = q; q += a.Ot * RK;
+      stage_w(rWn[i], a.conv_w[i], a.Ot, K, RK, 2, 1);
+      stage_w(rWp[i], a.conv_w[i], a.Ot, K, RK, 2, 0);
+    }
+    if (a.Os && (a.flags & MSGAT_F_SMIX)) { rWs = q; q += a.Os * RC; stage_w(rWs, a.sa_W, a.Os, C, RC, 1, 0); }
+    if (a.flags & MSGAT_F_RES) { rWres = q; stage_w(rWres, a.res_w, a.O, C, RC, 1, 0); }
+  }
   if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
 
   float acc[RBT][16];
@@ -199,12 +226,12 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       bacc += s;
     }
     // ---- S2: channel branch: dh = Mc^T g_c ; dMc = g_c h^T
-    if (a.Oc) stage_w(AR, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, RC, 1, 0);
+    if (a.Oc && !a.resident) stage_w(AR, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, RC, 1, 0);
     __syncthreads();
     for (int it = tid; it < chC * PQ; it += T) {
       const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4;
       float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
-      if (a.Oc) mix_item(d, G, PS, a.Oc, AR, RC, c0, nl, t0);
+      if (a.Oc) mix_item(d, G, PS, a.Oc, a.resident ? rMc : AR, RC, c0, nl, t0);
       for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
     }
     if (a.Oc && !a.skip_wgrad) wgrad_accum<RBT>(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1, a.S);
@@ -275,9 +302,11 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             bacc += s;
           }
         }
-        float *Wn = AR, *Wp = AR + a.Ot * RK;
-        stage_w(Wn, a.conv_w[i], a.Ot, K, RK, 2, 1);
-        stage_w(Wp, a.conv_w[i], a.Ot, K, RK, 2, 0);
+        float *Wn = a.resident ? rWn[i] : AR, *Wp = a.resident ? rWp[i] : AR + a.Ot * RK;
+        if (!a.resident) {
+          stage_w(Wn, a.conv_w[i], a.Ot, K, RK, 2, 1);
+          stage_w(Wp, a.conv_w[i], a.Ot, K, RK, 2, 0);
+        }
         __syncthreads();
         float* dst = i == 0 ? OT : DY[i & 1];
         for (int it = tid; it < (RK >> 2) * PQ; it += T) {
@@ -323,7 +352,8 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
     if (a.Os) {
       const float* Gs = G + Ooff * PS;
       const int RCs = RC;
-      if (smix) stage_w(AR, a.sa_W, a.Os, C, RCs, 1, 0);
+      const float* Wsm = a.resident ? rWs : AR;
+      if (smix && !a.resident) stage_w(AR, a.sa_W, a.Os, C, RCs, 1, 0);
       // GZ[o][i] = sum_n A[n,i] g_s[o][n]  (transpose aggregation through the CSC view)
       const int chS = (a.Os + 3) >> 2;
       for (int it = tid; it < chS * PQ; it += T) {
@@ -348,7 +378,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
         float4 d[4];
         for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
         if (smix) {
-          mix_item(d, GZ, PS, a.Os, AR, RCs, c0, nl, t0);
+          mix_item(d, GZ, PS, a.Os, Wsm, RCs, c0, nl, t0);
         } else {
           for (int j = 0; j < 4; ++j)
             if (c0 + j < C) { float4 z = ld4(GZ + (c0 + j) * PS + nl * 12 + t0); d[j].x += z.x; d[j].y += z.y; d[j].z += z.z; d[j].w += z.w; }
@@ -356,7 +386,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
         for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
         if (DOS) {  // d(aggregated h) = W^T g_s, the left operand of dA when h (not W h) was aggregated
           float4 e[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
-          mix_item(e, Gs, PS, a.Os, AR, RCs, c0, nl, t0);
+          mix_item(e, Gs, PS, a.Os, Wsm, RCs, c0, nl, t0);
           for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DOS + (c0 + j) * PS + nl * 12 + t0, e[j]);
         }
       }
@@ -408,13 +438,13 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       }
     }
     // ---- S6: dx = LN^T(dh) + Wres^T g
-    if (has_res) stage_w(AR, a.res_w, a.O, C, RC, 1, 0);
+    if (has_res && !a.resident) stage_w(AR, a.res_w, a.O, C, RC, 1, 0);
     __syncthreads();
     for (int it = tid; it < chC * PQ; it += T) {
       const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4, n = n0 + nl;
       float4 d[4];
       for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
-      if (has_res) mix_item(d, G, PS, a.O, AR, RC, c0, nl, t0);
+      if (has_res) mix_item(d, G, PS, a.O, a.resident ? rWres : AR, RC, c0, nl, t0);
       if (n < a.N) {
         for (int j = 0; j < 4; ++j) {
           if (c0 + j >= C) continue;
@@ -934,6 +964,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
     a.S = L.S;
     a.skip_wgrad = tc_w ? 1 : 0;
+    a.resident = (tc_w && bwd_resident_floats(p) > 0) ? 1 : 0;
     a.tcA = tc_w ? scratch + L.o_tcA : nullptr;
 #define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
     if (L.RBT == 2) {
