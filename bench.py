@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="samples per step of the CPU baseline (0: the full per-GPU batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="replay the step as one CUDA graph (msgat_b200.train.GraphedStep); auto: on, eager if capture fails")
     return ap.parse_args()
 
 
@@ -201,7 +203,7 @@ def main():
     if args.precision == "tf32":
         model.set_precision(_lib.PREC_TF32)
     fg = FlatGradients(model)
-    opt = torch.optim.Adam(fg.params, lr=1e-3, weight_decay=5e-4, fused=True)  # engine.py:106
+    opt = torch.optim.Adam(fg.params, lr=1e-3, weight_decay=5e-4, fused=True, capturable=args.graph != "off")  # engine.py:106
     host = synthetic.make_batch(Bper, shape["M"], shape["C"], shape["N"], seed=1234 + rank, pin=True)
     devb = [t.to(dev) for t in (host.X, host.H, host.D, host.Y)]
     h2d = sum(t.numel() * t.element_size() for t in (host.X, host.H, host.D, host.Y))
@@ -217,8 +219,13 @@ def main():
         return loss
 
     def step_e2e():
-        X, H, D, Y = (t.to(dev, non_blocking=True) for t in (host.X, host.H, host.D, host.Y))
-        loss = step(X, H, D, Y)
+        if graphed is not None:   # pinned host memory -> the graph's input buffers, then one replay
+            for dst, src in zip(graphed.inputs, (host.X, host.H, host.D, host.Y)):
+                dst.copy_(src, non_blocking=True)
+            loss = graphed(*graphed.inputs)
+        else:
+            X, H, D, Y = (t.to(dev, non_blocking=True) for t in (host.X, host.H, host.D, host.Y))
+            loss = step(X, H, D, Y)
         loss_host.copy_(loss.detach(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(loss_host)
@@ -245,10 +252,29 @@ def main():
 
     for _ in range(max(args.warmup, 3)):
         step(*devb)
+    # launches of this library per step, counted on an eager step (a graph replay launches the same kernels)
+    torch.cuda.synchronize()
     l0 = _lib.launch_count()
+    step(*devb)
+    launches = _lib.launch_count() - l0
+    graphed = None
+    if args.graph != "off":
+        from msgat_b200.train import GraphedStep
+        try:
+            graphed = GraphedStep(model, lambda o, y: huber(o, y, DELTA), opt, fg, devb, warmup=1)
+            for _ in range(2):
+                graphed(*graphed.inputs)
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001 - a failed capture must not take the bench down
+            if args.graph == "on":
+                raise
+            print(f"[bench] CUDA graph capture failed, running eager: {e!r}", file=sys.stderr)
+            graphed = None
+            torch.cuda.synchronize()
+    config["cuda_graph"] = graphed is not None
+    run = (lambda: graphed(*graphed.inputs)) if graphed is not None else (lambda: step(*devb))
     with ClockSampler(local) as clk:
-        ms = timed(lambda: step(*devb), args.steps)
-    launches = (_lib.launch_count() - l0) // max(args.steps, 1)
+        ms = timed(run, args.steps)
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
