@@ -316,9 +316,19 @@ def main():
                 "frac": None if ach is None else ach / peak, "traffic": traffic, "peak_source": src,
                 "algorithmic_bytes_per_launch": ab, "avg_launch_ms": avg_ms, "share_of_device_time": top[1][1] / total,
                 "my_kernels_ms_per_step": total / args.profile_steps}
-    if rank != 0:
+    def finish():
+        sys.stdout.flush()
+        sys.stderr.flush()
         if world > 1:
+            torch.cuda.synchronize()
+            if graphed is not None:
+                # tearing NCCL down while a captured graph still holds its collectives can hang: every
+                # collective of the run has completed on every rank here, so leave without the teardown
+                os._exit(0)
             dist.destroy_process_group()
+
+    if rank != 0:
+        finish()
         return
     cpu = None
     if not args.no_cpu_baseline and world == 1:
@@ -331,8 +341,7 @@ def main():
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "kernels": kernels}
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
 
 
 if __name__ == "__main__":
