@@ -287,6 +287,7 @@ def main():
     kernels = {}
     # every rank runs the profiled steps (they contain the gradient all-reduce); rank 0 records
     torch.cuda.synchronize()
+    model.concurrent_components = False   # one stream: a kernel's events then time that kernel alone
     if rank == 0:
         _lib.profile(True)
     for _ in range(args.profile_steps):

@@ -9,6 +9,8 @@ call into the sm_100a kernels (``msgat_b200.ops``).
 """
 from typing import List
 
+import os
+
 import torch
 from torch import nn
 
@@ -169,9 +171,17 @@ class TPC(nn.Module):
 
     def forward(self, signals: torch.Tensor, adjacency: torch.Tensor, gate: torch.Tensor = None,
                 acc: torch.Tensor = None) -> torch.Tensor:
+        return self.head(self.features(signals, adjacency), gate=gate, acc=acc)
+
+    def features(self, signals: torch.Tensor, adjacency: torch.Tensor) -> torch.Tensor:
+        """The MEAM stack (msgat.py:155-157)."""
         for i, meam in enumerate(self.tgacns):
             # the only consumer of this MEAM's output (next MEAM or the head) returns a masked gradient
             signals = meam._run(signals, adjacency, dout_masked=True, x_is_relu=i > 0)
+        return signals
+
+    def head(self, signals: torch.Tensor, gate: torch.Tensor = None, acc: torch.Tensor = None) -> torch.Tensor:
+        """LayerNorm_T + fc (+ gate, + running sum over components) (msgat.py:158-160, 204)."""
         return ops.head_op(signals, self.ln.weight, self.ln.bias, self.fc.weight, self.fc.bias, gate=gate, acc=acc,
                            x_is_relu=len(self.tgacns) > 0)
 
@@ -200,6 +210,8 @@ class MSGAT(nn.Module):
                 dilations=c["dilations"]) for c in components
         ])
         self.reset_parameters()
+        self.concurrent_components = os.environ.get("MSGAT_STREAMS", "1") != "0"
+        self._streams = {}
 
     def set_precision(self, precision: int):
         for tpc in self.tpcs:
@@ -214,9 +226,32 @@ class MSGAT(nn.Module):
         else:
             gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(len(self.tpcs))]
         out = None
+        if X.is_cuda and self.concurrent_components and len(self.tpcs) > 1:
+            # The M components are independent up to the gated sum (msgat.py:204): each MEAM stack runs on
+            # its own stream, so the small per-sample kernels of one component (32 CTAs) and the tail waves
+            # of the large ones overlap with the other components' work, forward and backward (autograd
+            # runs a node's backward on the stream of its forward).  The heads join on the caller's stream.
+            main = torch.cuda.current_stream(X.device)
+            streams = self._component_streams(X.device)
+            feats = []
+            for m, tpc in enumerate(self.tpcs):
+                streams[m].wait_stream(main)
+                with torch.cuda.stream(streams[m]):
+                    feats.append(tpc.features(X[:, m], self.adj))
+            for m, tpc in enumerate(self.tpcs):
+                main.wait_stream(streams[m])
+                feats[m].record_stream(main)
+                out = tpc.head(feats[m], gate=gates[m], acc=out)
+            return out
         for m, tpc in enumerate(self.tpcs):
             out = tpc(X[:, m], self.adj, gate=gates[m], acc=out)
         return out
+
+    def _component_streams(self, device):
+        key = str(device)
+        if self._streams.get(key) is None:
+            self._streams[key] = [torch.cuda.Stream(device=device) for _ in self.tpcs]
+        return self._streams[key]
 
     def reset_parameters(self):
         """xavier-normal for matrices, U(+-1/sqrt(size0)) for vectors incl. the LayerNorm
