@@ -251,6 +251,10 @@ class MSGAT(nn.Module):
         key = str(device)
         if self._streams.get(key) is None:
             self._streams[key] = [torch.cuda.Stream(device=device) for _ in self.tpcs]
+            # parameters accumulate their gradients from the component streams on purpose
+            quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+            if quiet is not None:
+                quiet(False)
         return self._streams[key]
 
     def reset_parameters(self):

@@ -174,3 +174,36 @@ def test_engine_protocol_autocast_and_state_dict():
     assert torch.equal(ref, out.detach()), "autocast changed the arithmetic of the fp32 path"
     sd = {k: v.clone() for k, v in model.state_dict().items()}
     model.load_state_dict(sd)
+
+
+@pytest.mark.gpu
+def test_n4096_full_size_properties():
+    """BASELINE.json's largest configuration (N=4096, C=3) at full graph size: the oracle's dense
+    [B,N,N] attention is too slow to check here, so the test uses properties that do not depend on the
+    size: finite outputs and gradients, bit-reproducibility, and independence of a sample from the rest
+    of its batch (every operator of the path is per-sample)."""
+    from msgat_b200 import models, synthetic
+    from oracle.msgat_oracle import huber
+    shape = synthetic.PEMS_SHAPES["n4096"]
+    torch.manual_seed(3)
+    adj = synthetic.make_adjacency("n4096")
+    model = models.msgat72(n_components=2, in_channels=shape["C"], in_timesteps=12, out_timesteps=12, use_te=True,
+                           adj=adj.clone()).cuda()
+    b = synthetic.make_batch(2, 2, shape["C"], shape["N"], seed=11)
+    X, H, D, Y = (t.cuda() for t in (b.X, b.H, b.D, b.Y))
+
+    def run(Xs, Hs, Ds, Ys):
+        model.zero_grad(set_to_none=True)
+        Xs = Xs.clone().requires_grad_(True)
+        out = model(Xs, Hs, Ds)
+        huber(out, Ys, 50.0).backward()
+        torch.cuda.synchronize()
+        return out.detach(), Xs.grad, [p.grad.clone() for p in model.parameters() if p.grad is not None]
+
+    o1, gx1, gp1 = run(X, H, D, Y)
+    o2, gx2, gp2 = run(X, H, D, Y)
+    assert torch.isfinite(o1).all() and torch.isfinite(gx1).all() and all(torch.isfinite(g).all() for g in gp1)
+    assert torch.equal(o1, o2) and torch.equal(gx1, gx2) and all(torch.equal(a, c) for a, c in zip(gp1, gp2))
+    o_single, _, _ = run(X[1:], H[1:], D[1:], Y[1:])
+    assert torch.equal(o_single[0], o1[1]), "a sample's output depends on the rest of its batch"
+    assert float(gx1.abs().max()) > 0
