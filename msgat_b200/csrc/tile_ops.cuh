@@ -76,6 +76,7 @@ MSGAT_DEV void stage_vec(float* dst, const float* MSGAT_RESTRICT src, int n, int
 MSGAT_DEV void mix_item(float4 acc[4], const float* src, int PS, int K, const float* Wt, int WS, int o0, int nl, int t0) {
   const float* s = src + nl * 12 + t0;
   const float* w = Wt + o0;
+#pragma unroll 4
   for (int k = 0; k < K; ++k) {
     float4 x = ld4(s + k * PS);
     float4 ww = ld4(w + k * WS);
@@ -85,6 +86,7 @@ MSGAT_DEV void mix_item(float4 acc[4], const float* src, int PS, int K, const fl
 // causal two-tap conv: acc[j] += sum_k Wnow[k][o0+j] x[k][t] + Wpast[k][o0+j] x[k][t-d]
 MSGAT_DEV void mix_item_taps(float4 acc[4], const float* src, int PS, int K, const float* Wnow, const float* Wpast,
                              int WS, int o0, int nl, int t0, int d) {
+#pragma unroll 4
   for (int k = 0; k < K; ++k) {
     const float* row = src + k * PS + nl * 12;
     float4 x = ld4(row + t0);
@@ -99,6 +101,7 @@ MSGAT_DEV void mix_item_taps(float4 acc[4], const float* src, int PS, int K, con
 // (weights staged untransposed, rows = o)
 MSGAT_DEV void mix_item_taps_T(float4 acc[4], const float* src, int PS, int K, const float* Wnow, const float* Wpast,
                                int WS, int o0, int nl, int t0, int d) {
+#pragma unroll 4
   for (int k = 0; k < K; ++k) {
     const float* row = src + k * PS + nl * 12;
     float4 x = ld4(row + t0);
