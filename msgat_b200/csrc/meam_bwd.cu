@@ -60,6 +60,7 @@ MSGAT_DEV void wgrad_accum(float (&acc)[RBT][16], const WJob& jb, const float* A
     const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
     const float* ar[4];
     const float* br[4];
+    MSGAT_UNROLL
     for (int i = 0; i < 4; ++i) {
       ar[i] = A + (oa + i < jb.Oa ? oa + i : jb.Oa - 1) * PS;
       br[i] = Bm + (kb + i < jb.Kb ? kb + i : jb.Kb - 1) * PS;
@@ -70,7 +71,9 @@ MSGAT_DEV void wgrad_accum(float (&acc)[RBT][16], const WJob& jb, const float* A
     for (int pq = slice; pq < PQ; pq += S) {
       const int nl = pq / 3, t0 = (pq - nl * 3) * 4, off = nl * 12;
       float4 a[4], b[4];
+      MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) a[i] = ld4(ar[i] + off + t0);
+      MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) b[i] = (tapd < 0) ? ld4(br[i] + off + t0) : quad_past(br[i] + off, t0, tapd);
       MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) {
@@ -94,7 +97,9 @@ MSGAT_DEV void wgrad_flush(const float (&acc)[RBT][16], const WJob* jobs, int bl
       const int slice = vloc / jb.nblk, local = vloc - slice * jb.nblk;
       const int oa = (local / jb.nkb) * 4, kb = (local % jb.nkb) * 4;
       float* dst = jb.out + ((int64_t)blk * S + slice) * jb.blk_stride;
+      MSGAT_UNROLL
       for (int i = 0; i < 4; ++i)
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
           if (oa + i < jb.Oa && kb + j < jb.Kb) dst[(oa + i) * jb.Kb + kb + j] = acc[r][i * 4 + j];
     }
@@ -162,11 +167,13 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   float* OT = sp; sp += C * PS;
   float* DH = sp; sp += C * PS;
   float* G = sp; sp += a.O * PS;
-  float* Y[MSGAT_MAX_CONV] = {nullptr, nullptr, nullptr, nullptr};
-  float* DY[2] = {nullptr, nullptr};
+  // conv intermediates Y[i] = Yb + i * Ot * PS and the two ping-pong gradient buffers DY[j] = DYb + j * Ot * PS:
+  // offsets from one shared-memory base (pointer arrays would live in local memory and turn every access
+  // through them into a generic load / store)
+  float *Yb = nullptr, *DYb = nullptr;
   if (a.n_conv >= 2) {
-    for (int i = 0; i + 1 < a.n_conv; ++i) { Y[i] = sp; sp += a.Ot * PS; }
-    DY[0] = sp; sp += a.Ot * PS; DY[1] = sp; sp += a.Ot * PS;
+    Yb = sp; sp += (a.n_conv - 1) * a.Ot * PS;
+    DYb = sp; sp += 2 * a.Ot * PS;
   }
   float* GZ = nullptr; if (a.Os) { GZ = sp; sp += a.Os * PS; }
   float* DOS = nullptr; if (a.Os && smix && !a.s_pre) { DOS = sp; sp += C * PS; }
@@ -175,7 +182,8 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   float* LW = sp; sp += 24;
   float* AR = sp;  // arena
   float* RW = AR + a.arena_floats;  // resident weights (a.resident)
-  float *rMc = nullptr, *rWn[MSGAT_MAX_CONV], *rWp[MSGAT_MAX_CONV], *rWs = nullptr, *rWres = nullptr;
+  float *rMc = nullptr, *rWc = nullptr, *rWs = nullptr, *rWres = nullptr;   // rWc: conv taps, [now | past] per conv
+  const int RKt = (a.Ot + 3) & ~3;
   const int Ooff = a.Oc + a.Ot;
   const int chC = (C + 3) >> 2;
   const int blk = b * a.J + blockIdx.x;
@@ -189,9 +197,10 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
     if (a.Oc) { rMc = q; q += a.Oc * RC; stage_w(rMc, a.Mc + (int64_t)b * a.Oc * C, a.Oc, C, RC, 1, 0); }
     for (int i = 0; i < a.n_conv; ++i) {
       const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
-      rWn[i] = q; q += a.Ot * RK; rWp[i] = q; q += a.Ot * RK;
-      stage_w(rWn[i], a.conv_w[i], a.Ot, K, RK, 2, 1);
-      stage_w(rWp[i], a.conv_w[i], a.Ot, K, RK, 2, 0);
+      if (i == 0) rWc = q;
+      stage_w(q, a.conv_w[i], a.Ot, K, RK, 2, 1);
+      stage_w(q + a.Ot * RK, a.conv_w[i], a.Ot, K, RK, 2, 0);
+      q += 2 * a.Ot * RK;
     }
     if (a.Os && (a.flags & MSGAT_F_SMIX)) { rWs = q; q += a.Os * RC; stage_w(rWs, a.sa_W, a.Os, C, RC, 1, 0); }
     if (a.flags & MSGAT_F_RES) { rWres = q; stage_w(rWres, a.res_w, a.O, C, RC, 1, 0); }
@@ -202,6 +211,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   for (int r = 0; r < RBT; ++r) for (int i = 0; i < 16; ++i) acc[r][i] = 0.f;
   float bacc = 0.f, lnw_acc[12], lnb_acc[12];
   double pt_acc = 0.0;
+  MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
 
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
@@ -232,6 +242,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4;
       float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
       if (a.Oc) mix_item(d, G, PS, a.Oc, a.resident ? rMc : AR, RC, c0, nl, t0);
+      MSGAT_UNROLL
       for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
     }
     if (a.Oc && !a.skip_wgrad) wgrad_accum<RBT>(acc, a.jobs[JOB_MC], G, H, PS, PQ, -1, a.S);
@@ -252,18 +263,20 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
         for (int it = tid; it < (WOt >> 2) * PQ; it += T) {
           const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4;
           float4 d[4];
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) { float bj = cvB[o0 + j]; d[j] = make_float4(bj, bj, bj, bj); }
           mix_item_taps(d, cin, PS, K, cvA, cvP, WOt, o0, nl, t0, a.dil[i]);
-          for (int j = 0; j < 4; ++j) if (o0 + j < a.Ot) st4(Y[i] + (o0 + j) * PS + nl * 12 + t0, d[j]);
+          MSGAT_UNROLL
+          for (int j = 0; j < 4; ++j) if (o0 + j < a.Ot) st4(Yb + i * a.Ot * PS + (o0 + j) * PS + nl * 12 + t0, d[j]);
         }
         __syncthreads();
-        cin = Y[i];
+        cin = Yb + i * a.Ot * PS;
       }
       // walk the chain backwards
       const float* dy = G + a.Oc * PS;
       for (int i = a.n_conv - 1; i >= 0; --i) {
         const int K = i == 0 ? C : a.Ot, RK = (K + 3) & ~3;
-        const float* in = i == 0 ? OT : Y[i - 1];
+        const float* in = i == 0 ? OT : Yb + (i - 1) * a.Ot * PS;
         if (a.tcA && i == 0) {
           // dy = dY1 here.  The first conv sits behind the temporal mix, which commutes with it:
           // y1 = Pt a_now + Pt(t-d1) a_past with a = W1 h, so the weight gradients contract
@@ -274,11 +287,15 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             if (n >= a.N) continue;
             const float* q = dy + k * PS + nl * 12;
             float v[12], an[12], ap[12];
+            MSGAT_UNROLL
             for (int t = 0; t < 12; ++t) v[t] = q[t];
+            MSGAT_UNROLL
             for (int j = 0; j < 12; ++j) {
               float s1 = 0.f, s2 = 0.f;
+              MSGAT_UNROLL
               for (int t = 0; t < 12; ++t) s1 = fmaf(Pt[t * 12 + j], v[t], s1);
-              for (int t = d1; t < 12; ++t) s2 = fmaf(Pt[(t - d1) * 12 + j], v[t], s2);
+              MSGAT_UNROLL
+              for (int t = 0; t < 12; ++t) s2 = t >= d1 ? fmaf(Pt[(t - d1 < 0 ? 0 : t - d1) * 12 + j], v[t], s2) : s2;
               an[j] = s1; ap[j] = s2;
             }
             float* o1 = a.tcA + (((int64_t)b * 3 * a.Ot + k) * a.N + n) * 12;
@@ -302,17 +319,20 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             bacc += s;
           }
         }
-        float *Wn = a.resident ? rWn[i] : AR, *Wp = a.resident ? rWp[i] : AR + a.Ot * RK;
+        // resident taps: conv 0 has RK = rup4(C) columns, the later ones rup4(Ot)
+        float* Wn = a.resident ? rWc + (i == 0 ? 0 : 2 * a.Ot * RC + (i - 1) * 2 * a.Ot * RKt) : AR;
+        float* Wp = Wn + a.Ot * RK;
         if (!a.resident) {
           stage_w(Wn, a.conv_w[i], a.Ot, K, RK, 2, 1);
           stage_w(Wp, a.conv_w[i], a.Ot, K, RK, 2, 0);
         }
         __syncthreads();
-        float* dst = i == 0 ? OT : DY[i & 1];
+        float* dst = i == 0 ? OT : DYb + (i & 1) * a.Ot * PS;
         for (int it = tid; it < (RK >> 2) * PQ; it += T) {
           const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, k0 = ch * 4;
           float4 d[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
           mix_item_taps_T(d, dy, PS, a.Ot, Wn, Wp, RK, k0, nl, t0, a.dil[i]);
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) if (k0 + j < K) st4(dst + (k0 + j) * PS + nl * 12 + t0, d[j]);
         }
         __syncthreads();
@@ -325,6 +345,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
         if (tid < ngr * 9) {
           const int blk9 = tid % 9, grp = tid / 9, tb = (blk9 / 3) * 4, ib = (blk9 % 3) * 4;
           double o16[16];
+          MSGAT_UNROLL
           for (int i = 0; i < 16; ++i) o16[i] = 0.0;
           for (int r = grp; r < C * NT; r += ngr) {
             const int c = r / NT, nl = r - c * NT;
@@ -334,7 +355,9 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
             o16[8] += g.z * h.x; o16[9] += g.z * h.y; o16[10] += g.z * h.z; o16[11] += g.z * h.w;
             o16[12] += g.w * h.x; o16[13] += g.w * h.y; o16[14] += g.w * h.z; o16[15] += g.w * h.w;
           }
+          MSGAT_UNROLL
           for (int i = 0; i < 4; ++i)
+            MSGAT_UNROLL
             for (int j = 0; j < 4; ++j) AR[grp * 144 + (tb + i) * 12 + ib + j] = (float)o16[i * 4 + j];
         }
         // dh[c,n,i] += sum_t Pt[t][i] dOt[c,n,t]
@@ -364,11 +387,14 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
           for (int k = a.csc_ptr[n]; k < k1; ++k) {
             const float w = pwb[a.csc_eid[k]];
             const float* gr = Gb + ((int64_t)(Ooff + o0) * a.N + a.csc_row[k]) * 12 + t0;
+            MSGAT_UNROLL
             for (int j = 0; j < 4; ++j) if (o0 + j < a.Os) fma4(d[j], w, ld4(gr + (int64_t)j * a.N * 12));
           }
         }
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) if (o0 + j < a.Os) st4(GZ + (o0 + j) * PS + nl * 12 + t0, d[j]);
         if (a.tcA && n < a.N)
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j)
             if (o0 + j < a.Os) st4(a.tcA + (((int64_t)b * 3 * a.Os + 2 * a.Os + o0 + j) * a.N + n) * 12 + t0, d[j]);
       }
@@ -376,17 +402,21 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
       for (int it = tid; it < chC * PQ; it += T) {
         const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4;
         float4 d[4];
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
         if (smix) {
           mix_item(d, GZ, PS, a.Os, Wsm, RCs, c0, nl, t0);
         } else {
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j)
             if (c0 + j < C) { float4 z = ld4(GZ + (c0 + j) * PS + nl * 12 + t0); d[j].x += z.x; d[j].y += z.y; d[j].z += z.z; d[j].w += z.w; }
         }
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DH + (c0 + j) * PS + nl * 12 + t0, d[j]);
         if (DOS) {  // d(aggregated h) = W^T g_s, the left operand of dA when h (not W h) was aggregated
           float4 e[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
           mix_item(e, Gs, PS, a.Os, Wsm, RCs, c0, nl, t0);
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) if (c0 + j < C) st4(DOS + (c0 + j) * PS + nl * 12 + t0, e[j]);
         }
       }
@@ -425,8 +455,10 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
         const float mu = ST[2 * r], rs = ST[2 * r + 1];
         float xh[12], dh[12];
         float* q = DH + c * PS + nl * 12;
+        MSGAT_UNROLL
         for (int t = 0; t < 12; ++t) { xh[t] = (src[t] - mu) * rs; dh[t] = q[t]; }
         float m1 = 0.f, m2 = 0.f;
+        MSGAT_UNROLL
         for (int t = 0; t < 12; ++t) {
           lnw_acc[t] += dh[t] * xh[t];
           lnb_acc[t] += dh[t];
@@ -434,6 +466,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
           m1 += gg; m2 += gg * xh[t];
         }
         m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+        MSGAT_UNROLL
         for (int t = 0; t < 12; ++t) q[t] = rs * (dh[t] * LW[t] - m1 - xh[t] * m2);
       }
     }
@@ -443,9 +476,11 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
     for (int it = tid; it < chC * PQ; it += T) {
       const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, c0 = ch * 4, n = n0 + nl;
       float4 d[4];
+      MSGAT_UNROLL
       for (int j = 0; j < 4; ++j) d[j] = (c0 + j < C) ? ld4(DH + (c0 + j) * PS + nl * 12 + t0) : f4zero();
       if (has_res) mix_item(d, G, PS, a.O, a.resident ? rWres : AR, RC, c0, nl, t0);
       if (n < a.N) {
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) {
           if (c0 + j >= C) continue;
           float4 v = d[j];
@@ -465,6 +500,7 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
   if (a.Ot && tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
   {
     const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
+    MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) {
       const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
       if (lane == 0) { AR[warp * 24 + t] = w; AR[warp * 24 + 12 + t] = bb; }
@@ -502,31 +538,39 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
   __syncthreads();
   float q[12], dq[12];
   double dU[12];  // sum_e dSnz q_i and delta E nearly cancel
+  MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.0; dq[t] = 0.f; }
   if (n < a.N) {
     const int64_t g = (int64_t)b * a.N + n;
     const double dl = (double)a.delta[g];
+    MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * a.E[g * 12 + t]; dq[t] = a.dq_dense[g * 12 + t]; }
     for (int e = a.row_ptr[n]; e < a.row_ptr[n + 1]; ++e) {
       const double w = (double)ds[e];
       const float* qi = qb + (int64_t)a.col_idx[e] * 12;
+      MSGAT_UNROLL
       for (int t = 0; t < 12; ++t) dU[t] = fma(w, (double)qi[t], dU[t]);
     }
     for (int k = a.csc_ptr[n]; k < a.csc_ptr[n + 1]; ++k) {
       const float w = ds[a.csc_eid[k]];
       const float* qr = qb + (int64_t)a.csc_row[k] * 12;
+      MSGAT_UNROLL
       for (int t = 0; t < 12; ++t) {
         float u = 0.f;
+        MSGAT_UNROLL
         for (int t1 = 0; t1 < 12; ++t1) u = fmaf(qr[t1], WG[t1 * 12 + t], u);
         dq[t] = fmaf(w, u, dq[t]);
       }
     }
+    MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) {
       double s = 0.0;
+      MSGAT_UNROLL
       for (int t2 = 0; t2 < 12; ++t2) s = fma(dU[t2], (double)WG[t * 12 + t2], s);
       a.dqs[g * 12 + t] = (float)((double)dq[t] + s);
     }
   }
+  MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) { QD[threadIdx.x * 24 + t] = q[t]; QD[threadIdx.x * 24 + 12 + t] = (float)dU[t]; }
   __syncthreads();
   for (int i = threadIdx.x; i < 144; i += blockDim.x) {
@@ -591,6 +635,7 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     for (int i = tid; i < C * 12; i += T) {
       const int c = i / 12, t = i - c * 12;
       double s1 = 0.0, s2 = 0.0;
+      MSGAT_UNROLL
       for (int u = 0; u < 12; ++u) {
         s1 += (double)(__ldg(a.Wc + t * 12 + u)) * (double)(qc[c * 12 + u]);   // (qc Wc^T)[c][t]
         s2 += (double)(qc[c * 12 + u]) * (double)(__ldg(a.Wc + u * 12 + t));   // (qc Wc)[c][t]
@@ -630,7 +675,9 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_bwd_small(BSmallArgs a) {
     __syncthreads();
     if (tid < 12) {
       double s = 0.0;
+      MSGAT_UNROLL
       for (int k = 0; k < 12; ++k) s += (double)(Pt[tid * 12 + k]) * (double)(dSt[tid * 12 + k]);
+      MSGAT_UNROLL
       for (int k = 0; k < 12; ++k) dSt[tid * 12 + k] = (float)((double)Pt[tid * 12 + k] * ((double)dSt[tid * 12 + k] - s));
     }
     __syncthreads();
@@ -651,6 +698,7 @@ MSGAT_KERNEL k_dwt(const float* dK, const float* qt, int B, int N, float* dWt1, 
   const int n = i / 20, r = i - n * 20;
   float s = 0.f;
   for (int b = 0; b < B; ++b)
+    MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) s = fmaf(dK[(int64_t)b * 240 + t * 20 + r], qt[((int64_t)b * N + n) * 12 + t], s);
   if (r < 10) { if (dWt1) dWt1[(int64_t)r * N + n] = s; }
   else { if (dWt2) dWt2[(int64_t)(r - 10) * N + n] = s; }
@@ -689,6 +737,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
   double at_acc = 0.0, as_acc = 0.0;
   float lnw_acc[12], lnb_acc[12];
+  MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
   for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
     const int n0 = tile * NT;
@@ -718,18 +767,23 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         xv[8] = w.x; xv[9] = w.y; xv[10] = w.z; xv[11] = w.w;
         float mu = 0.f, rs = 1.f;
         if (do_ln) {
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) mu += xv[t];
           mu *= (1.0f / 12.0f);
           float var = 0.f;
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { const float d = xv[t] - mu; var = fmaf(d, d, var); }
           rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { xh[t] = (xv[t] - mu) * rs; h[t] = xh[t] * LW[t] + LW[12 + t]; }
         } else {
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { xh[t] = 0.f; h[t] = xv[t]; }
         }
         const float an = a.Oc ? __ldg(a.ca_alpha + n) : 0.f;
         const float att = a.Ot ? __ldg(a.ta_alpha + c) : 0.f;
         const float as = a.Os ? __ldg(a.sa_alpha + c) : 0.f;
+        MSGAT_UNROLL
         for (int t = 0; t < 12; ++t) {
           const float dqc = a.Oc ? DQC[c * 12 + t] : 0.f, dqt = DQT[nl * 12 + t], dqs = DQS[nl * 12 + t];
           dh[t] = an * dqc + att * dqt + as * dqs;
@@ -738,6 +792,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         float out[12];
         if (do_ln) {
           float m1 = 0.f, m2 = 0.f;
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) {
             lnw_acc[t] += dh[t] * xh[t];
             lnb_acc[t] += dh[t];
@@ -745,11 +800,14 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
             m1 += gg; m2 += gg * xh[t];
           }
           m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) out[t] = rs * (dh[t] * LW[t] - m1 - xh[t] * m2);
         } else {
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) out[t] = dh[t];
         }
         if (a.flags & MSGAT_F_X_IS_RELU)
+          MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) out[t] = xv[t] > 0.f ? out[t] : 0.f;
         float* d = a.dx + (((int64_t)b * C + c) * a.N + n) * 12;
         float4 d0 = ld4(d), d1 = ld4(d + 4), d2 = ld4(d + 8);
@@ -778,6 +836,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = at_acc; a.pa_s[(int64_t)blk * C + tid] = as_acc; }
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
+  MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) {
     const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
     if (lane == 0) { RED[warp * 24 + t] = w; RED[warp * 24 + 12 + t] = bb; }

@@ -62,10 +62,12 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_prep(PrepArgs a) {
       if (a.s_pre) {
         mix_item(acc, H, PS, a.C, WsT, WS, o0, nl, t0);
       } else {
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
           if (o0 + j < a.Cz) acc[j] = ld4(H + (o0 + j) * PS + nl * 12 + t0);
       }
       if (n < a.N)
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
           if (o0 + j < a.Cz) st4(a.Z + (((int64_t)b * a.Cz + o0 + j) * a.N + n) * 12 + t0, acc[j]);
     }
@@ -288,11 +290,14 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
       for (int it = threadIdx.x; it < chT * PQ; it += blockDim.x) {
         const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4;
         float4 acc[4];
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
         mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
           if (o0 + j < a.Ot) st4(dst + (o0 + j) * PS + nl * 12 + t0, acc[j]);
         if (a.Y1 && i == 0 && n0 + nl < a.N)
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j)
             if (o0 + j < a.Ot) st4(a.Y1 + (((int64_t)b * a.Ot + o0 + j) * a.N + n0 + nl) * 12 + t0, acc[j]);
       }
@@ -306,14 +311,17 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
       int obase, width, o0;
       if (chg < chC) {  // channel branch: Mc[b] h + bias  (attention.py:94 + msgat.py:94)
         o0 = chg * 4; obase = 0; width = a.Oc;
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) { float bj = caB[o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
         mix_item(acc, H, PS, C, McT, WOc, o0, nl, t0);
       } else if (chg < chC + chT) {  // temporal branch: last conv of the chain (or OT itself)
         o0 = (chg - chC) * 4; obase = a.Oc; width = a.Ot;
         if (a.n_conv == 0) {
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) if (o0 + j < width) acc[j] = ld4(OT + (o0 + j) * PS + nl * 12 + t0);
         } else {
           const int i = a.n_conv - 1, K = i == 0 ? C : a.Ot;
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
           mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
         }
@@ -325,6 +333,7 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
             for (int e = a.row_ptr[n]; e < e1; ++e) {
               const float w = pwb[e];
               const float* zr = Zb + (int64_t)a.col_idx[e] * 12 + t0;
+              MSGAT_UNROLL
               for (int j = 0; j < 4; ++j)
                 if (o0 + j < width) fma4(acc[j], w, ld4(zr + (int64_t)(o0 + j) * a.N * 12));
             }
@@ -332,11 +341,13 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
         } else if (smix) {
           mix_item(acc, OS, PS, C, WsT, WOs, o0, nl, t0);
         } else {
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) if (o0 + j < width) acc[j] = ld4(OS + (o0 + j) * PS + nl * 12 + t0);
         }
       }
       if (has_res) {
         float4 r[4];
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) { float bj = (o0 + j < width) ? resB[obase + o0 + j] : 0.f; r[j] = make_float4(bj, bj, bj, bj); }
         // residual rows obase+o0.. may be unaligned to 4 in resT when widths are not
         // multiples of 4 (bare attentions never have a residual), so index per row
@@ -344,11 +355,14 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
         for (int k = 0; k < C; ++k) {
           float4 xv = ld4(s + k * PS);
           const float* w = resT + k * WO + obase + o0;
+          MSGAT_UNROLL
           for (int j = 0; j < 4; ++j) if (o0 + j < width) fma4(r[j], w[j], xv);
         }
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) { acc[j].x += r[j].x; acc[j].y += r[j].y; acc[j].z += r[j].z; acc[j].w += r[j].w; }
       }
       if (n < a.N) {
+        MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) {
           if (o0 + j >= width) continue;
           float4 v = acc[j];
