@@ -139,6 +139,7 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
       const int c = i / 12, t2 = i - c * 12;
       double s = 0.0;
+      MSGAT_UNROLL
       for (int t = 0; t < 12; ++t) s += qc[c * 12 + t] * (double)__ldg(a.Wc + t * 12 + t2);
       tmp[i] = s;
     }
@@ -146,6 +147,7 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
     for (int i = threadIdx.x; i < C * C; i += blockDim.x) {
       const int c = i / C, j = i - c * C;
       double s = 0.0;
+      MSGAT_UNROLL
       for (int t = 0; t < 12; ++t) s += tmp[c * 12 + t] * qc[j * 12 + t];
       S[i] = s;
     }
@@ -185,10 +187,13 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_small(SmallArgs a) {
     if (threadIdx.x < 12) {
       const int t = threadIdx.x;
       double m = -INFINITY;
+      MSGAT_UNROLL
       for (int j = 0; j < 12; ++j) m = fmax(m, St[t * 12 + j]);
       double e[12], l = 0.0;
+      MSGAT_UNROLL
       for (int j = 0; j < 12; ++j) { e[j] = exp(St[t * 12 + j] - m); l += e[j]; }
       const double inv = 1.0 / l;
+      MSGAT_UNROLL
       for (int j = 0; j < 12; ++j) a.Pt[(int64_t)b * 144 + t * 12 + j] = (float)(e[j] * inv);
     }
   }
@@ -228,11 +233,11 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
   if (has_res) { resT = sp; sp += C * WO; resB = sp; sp += WO; }
   float *McT = nullptr, *caB = nullptr;
   if (a.Oc) { McT = sp; sp += C * WOc; caB = sp; sp += WOc; }
-  float *cvA[MSGAT_MAX_CONV], *cvP[MSGAT_MAX_CONV], *cvB[MSGAT_MAX_CONV];
-  for (int i = 0; i < a.n_conv; ++i) {
-    const int K = i == 0 ? C : a.Ot;
-    cvA[i] = sp; sp += K * WOt; cvP[i] = sp; sp += K * WOt; cvB[i] = sp; sp += WOt;
-  }
+  // conv i: [now taps K x WOt | past taps K x WOt | bias WOt] at cv0 + cv_off(i); offsets from one base
+  // instead of pointer arrays, which would live in local memory and make every access through them generic
+  float* cv0 = sp;
+  for (int i = 0; i < a.n_conv; ++i) sp += 2 * (i == 0 ? C : a.Ot) * WOt + WOt;
+  auto cv_off = [&](int i) { return i == 0 ? 0 : (2 * C * WOt + WOt) + (i - 1) * (2 * a.Ot * WOt + WOt); };
   float* WsT = nullptr; if (a.Os && smix && !a.s_pre) { WsT = sp; sp += C * WOs; }
   float* Pt = sp; sp += 144;
   float* LW = sp; sp += 24;
@@ -244,9 +249,10 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
   }
   for (int i = 0; i < a.n_conv; ++i) {
     const int K = i == 0 ? C : a.Ot;
-    stage_wT(cvA[i], a.conv_w[i], a.Ot, K, WOt, 2, 1);  // tap 1 multiplies x[t]
-    stage_wT(cvP[i], a.conv_w[i], a.Ot, K, WOt, 2, 0);  // tap 0 multiplies x[t-d]
-    stage_vec(cvB[i], a.conv_b[i], a.Ot, WOt);
+    float* cvA = cv0 + cv_off(i);
+    stage_wT(cvA, a.conv_w[i], a.Ot, K, WOt, 2, 1);              // tap 1 multiplies x[t]
+    stage_wT(cvA + K * WOt, a.conv_w[i], a.Ot, K, WOt, 2, 0);    // tap 0 multiplies x[t-d]
+    stage_vec(cvA + 2 * K * WOt, a.conv_b[i], a.Ot, WOt);
   }
   if (WsT) stage_wT(WsT, a.sa_W, a.Os, C, WOs, 1, 0);
   if (a.Ot) for (int i = threadIdx.x; i < 144; i += blockDim.x) Pt[i] = a.Pt[(int64_t)b * 144 + i];
@@ -287,12 +293,13 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
     for (int i = 0; i + 1 < a.n_conv; ++i) {
       float* dst = (i & 1) ? YB : YA;
       const int K = i == 0 ? C : a.Ot;
+      const float* cvA = cv0 + cv_off(i);
       for (int it = threadIdx.x; it < chT * PQ; it += blockDim.x) {
         const int ch = it / PQ, pq = it - ch * PQ, nl = pq / 3, t0 = (pq - nl * 3) * 4, o0 = ch * 4;
         float4 acc[4];
         MSGAT_UNROLL
-        for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
-        mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
+        for (int j = 0; j < 4; ++j) { float bj = cvA[2 * K * WOt + o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
+        mix_item_taps(acc, cin, PS, K, cvA, cvA + K * WOt, WOt, o0, nl, t0, a.dil[i]);
         MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
           if (o0 + j < a.Ot) st4(dst + (o0 + j) * PS + nl * 12 + t0, acc[j]);
@@ -321,9 +328,10 @@ MSGAT_KERNEL MSGAT_LB(512, 1) k_apply(ApplyArgs a) {
           for (int j = 0; j < 4; ++j) if (o0 + j < width) acc[j] = ld4(OT + (o0 + j) * PS + nl * 12 + t0);
         } else {
           const int i = a.n_conv - 1, K = i == 0 ? C : a.Ot;
+          const float* cvA = cv0 + cv_off(i);
           MSGAT_UNROLL
-          for (int j = 0; j < 4; ++j) { float bj = cvB[i][o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
-          mix_item_taps(acc, cin, PS, K, cvA[i], cvP[i], WOt, o0, nl, t0, a.dil[i]);
+          for (int j = 0; j < 4; ++j) { float bj = cvA[2 * K * WOt + o0 + j]; acc[j] = make_float4(bj, bj, bj, bj); }
+          mix_item_taps(acc, cin, PS, K, cvA, cvA + K * WOt, WOt, o0, nl, t0, a.dil[i]);
         }
       } else {  // spatial branch (attention.py:36 + msgat.py:27)
         o0 = (chg - chC - chT) * 4; obase = a.Oc + a.Ot; width = a.Os;
