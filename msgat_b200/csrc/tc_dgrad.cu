@@ -298,14 +298,16 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
         w[0] = b0.x; w[1] = b0.y; w[2] = b0.z; w[3] = b0.w; w[4] = b1.x; w[5] = b1.y; w[6] = b1.z; w[7] = b1.w;
         w[8] = b2.x; w[9] = b2.y; w[10] = b2.z; w[11] = b2.w;
       }
-      // dY1[t] = now[t] + past[t + d2]; the shift is a compile-time-indexed select chain (registers only)
-#pragma unroll
-      for (int t = 0; t < 12; ++t) {
-        float sft = 0.f;
-#pragma unroll
-        for (int q = 1; q < 12; ++q) sft = (q == t + a.d2) ? w[q] : sft;
-        v[t] += sft;
+      // dY1[t] = now[t] + past[t + d2]
+      // (a switch over the uniform dilation keeps every index static: a select chain over a register
+      // array is turned into a local-memory array by the compiler)
+#define TD_SHIFT(D) case D: _Pragma("unroll") for (int t = 0; t + D < 12; ++t) v[t] += w[t + D]; break;
+      switch (a.d2) {
+        TD_SHIFT(1) TD_SHIFT(2) TD_SHIFT(3) TD_SHIFT(4) TD_SHIFT(5) TD_SHIFT(6) TD_SHIFT(7) TD_SHIFT(8) TD_SHIFT(9) TD_SHIFT(10)
+        TD_SHIFT(11)
+        default: break;
       }
+#undef TD_SHIFT
       const float* P = half ? Ptd : Pt;
 #pragma unroll
       for (int j = 0; j < 12; ++j) o12[j] = 0.f;

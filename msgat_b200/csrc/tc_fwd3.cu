@@ -271,15 +271,21 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
         st4(yd, make_float4(y[0], y[1], y[2], y[3])); st4(yd + 4, make_float4(y[4], y[5], y[6], y[7]));
         st4(yd + 8, make_float4(y[8], y[9], y[10], y[11]));
       }
+      // shifted copy ys[t] = y[t - d2]: a switch over the uniform dilation keeps every index static
+      float ys[12];
+#pragma unroll
+      for (int t = 0; t < 12; ++t) ys[t] = 0.f;
+#define TF3_SHIFT(D) case D: _Pragma("unroll") for (int t = D; t < 12; ++t) ys[t] = y[t - D]; break;
+      switch (a.d2) {
+        TF3_SHIFT(1) TF3_SHIFT(2) TF3_SHIFT(3) TF3_SHIFT(4) TF3_SHIFT(5) TF3_SHIFT(6) TF3_SHIFT(7) TF3_SHIFT(8) TF3_SHIFT(9)
+        TF3_SHIFT(10) TF3_SHIFT(11)
+        default: break;
+      }
+#undef TF3_SHIFT
 #pragma unroll
       for (int t0 = 0; t0 < 12; t0 += 4) {
         tf3_split4(YH, YL, sw128b32_off(o, pp + t0, cbY), make_float4(y[t0], y[t0 + 1], y[t0 + 2], y[t0 + 3]));
-        float4 s;
-        s.x = t0 >= a.d2 ? y[t0 - a.d2 < 0 ? 0 : t0 - a.d2] : 0.f;
-        s.y = t0 + 1 >= a.d2 ? y[t0 + 1 - a.d2 < 0 ? 0 : t0 + 1 - a.d2] : 0.f;
-        s.z = t0 + 2 >= a.d2 ? y[t0 + 2 - a.d2 < 0 ? 0 : t0 + 2 - a.d2] : 0.f;
-        s.w = t0 + 3 >= a.d2 ? y[t0 + 3 - a.d2 < 0 ? 0 : t0 + 3 - a.d2] : 0.f;
-        tf3_split4(YH, YL, sw128b32_off(b + o, pp + t0, cbY), s);
+        tf3_split4(YH, YL, sw128b32_off(b + o, pp + t0, cbY), make_float4(ys[t0], ys[t0 + 1], ys[t0 + 2], ys[t0 + 3]));
       }
     }
     fence_smem_to_async();
