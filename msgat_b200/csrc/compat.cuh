@@ -16,6 +16,7 @@
 #define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...) \
   emu::launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
 #define MSGAT_UNROLL
+#define MSGAT_PIN(x)
 static inline void msgat_prof_tag(const char*, int, int) {}
 #else
 #include <cuda_runtime.h>
@@ -40,6 +41,9 @@ void msgat_prof_tag(const char* fmt, int a, int b);
     if (_slot >= 0) msgat_prof_end(_slot, (cudaStream_t)(stream));                                \
   } while (0)
 #define MSGAT_UNROLL _Pragma("unroll")
+// keep a kernel-parameter value (e.g. dil[i], an indexed constant-bank load) in a register instead of
+// letting the compiler reload it inside the inner loops
+#define MSGAT_PIN(x) asm volatile("" : "+r"(x))
 #endif
 
 #define MSGAT_T12 12

@@ -86,6 +86,7 @@ MSGAT_DEV void mix_item(float4 acc[4], const float* src, int PS, int K, const fl
 // causal two-tap conv: acc[j] += sum_k Wnow[k][o0+j] x[k][t] + Wpast[k][o0+j] x[k][t-d]
 MSGAT_DEV void mix_item_taps(float4 acc[4], const float* src, int PS, int K, const float* Wnow, const float* Wpast,
                              int WS, int o0, int nl, int t0, int d) {
+  MSGAT_PIN(d);
 #pragma unroll 4
   for (int k = 0; k < K; ++k) {
     const float* row = src + k * PS + nl * 12;
@@ -101,6 +102,7 @@ MSGAT_DEV void mix_item_taps(float4 acc[4], const float* src, int PS, int K, con
 // (weights staged untransposed, rows = o)
 MSGAT_DEV void mix_item_taps_T(float4 acc[4], const float* src, int PS, int K, const float* Wnow, const float* Wpast,
                                int WS, int o0, int nl, int t0, int d) {
+  MSGAT_PIN(d);
 #pragma unroll 4
   for (int k = 0; k < K; ++k) {
     const float* row = src + k * PS + nl * 12;
