@@ -151,8 +151,8 @@ def algorithmic_bytes(kernel: str, B: int, N: int):
         "k_tc_wgrad": (C + O + b + 3 * b) * A,         # x, dout, Y1, dA_now/dA_past/GZ
         "k_bwd_fix": 3 * C * A,
         "k_relu_mask": 3 * O * A,
-        "k_head_fwd": C * A,
-        "k_head_bwd": 2 * C * A,
+        "k_head_fwd": C * A, "k_head_fwd12": C * A,
+        "k_head_bwd": 2 * C * A, "k_head_bwd12": 2 * C * A,
         "k_sstats": 15 * B * N * 4 + B * N * 12 * 4,
         "k_scol": (12 + 3 + 12) * B * N * 4,
     }

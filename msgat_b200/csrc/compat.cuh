@@ -65,6 +65,24 @@ MSGAT_DEV float warp_max(float v) {
   return v;
 }
 
+// 16-byte asynchronous global -> shared copy (LDGSTS): the data never passes through registers, so a thread
+// can keep the next rows of its stream in flight at no register cost.  live = false writes zeros.
+#ifdef MSGAT_EMU
+MSGAT_DEV void cp_async16(float* dst, const float* src, bool live) {
+  for (int i = 0; i < 4; ++i) dst[i] = live ? src[i] : 0.f;
+}
+MSGAT_DEV void cp_async_commit() {}
+template <int N> MSGAT_DEV void cp_async_wait() {}
+#else
+MSGAT_DEV void cp_async16(float* dst, const float* src, bool live) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+  const int n = live ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+MSGAT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> MSGAT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+#endif
+
 MSGAT_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 MSGAT_DEV void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 MSGAT_DEV float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }

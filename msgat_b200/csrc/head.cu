@@ -171,6 +171,312 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_head_bwd(HeadArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Tout == 12 (every shipped model: main.py:34): the streaming pair of kernels.  A block owns 64
+// consecutive nodes of one sample; warp w owns the channels w, w+8, ...; lane l owns the nodes
+// l and l+32, whose 12-step rows it reads straight from HBM (a warp reads two runs of 1536
+// contiguous bytes per channel) and keeps in registers -- no activation tile in shared memory,
+// no block barrier inside the channel loop.  The fc weights of a channel are warp-uniform
+// shared-memory reads, each reused for both nodes.
+#define HS_NODES 64
+#define HS_WARPS 8
+
+#define HS_WP 148  // floats between the channels of the staged fc weight (16-byte aligned rows)
+// fc.weight [12 o][12 t][1][C] (channel fastest) -> Wh[c][o][t].  A warp moves 8 channels x 4 consecutive (o,t)
+// per step: four 32-byte sectors on the global side, 32 distinct banks on the shared side (pitch 148 = 20 mod 32);
+// the loads of a batch of channel groups are issued before their stores, so a thread waits for one round trip
+// per batch instead of one per element.
+MSGAT_DEV void stage_fc12(float* Wh, const float* MSGAT_RESTRICT fc_w, int C) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cl = lane >> 2, tl = lane & 3, nwarp = blockDim.x >> 5;
+  for (int og = warp; og < 36; og += nwarp) {
+    const int ot = og * 4 + tl;
+    for (int c0 = 0; c0 < C; c0 += 72) {
+      float v[9];
+      MSGAT_UNROLL
+      for (int k = 0; k < 9; ++k) {
+        const int c = c0 + k * 8 + cl;
+        v[k] = c < C ? __ldg(fc_w + (int64_t)ot * C + c) : 0.f;
+      }
+      MSGAT_UNROLL
+      for (int k = 0; k < 9; ++k) {
+        const int c = c0 + k * 8 + cl;
+        if (c < C) Wh[c * HS_WP + ot] = v[k];
+      }
+    }
+  }
+}
+
+struct Row12 { float4 a, b, c; };
+MSGAT_DEV Row12 row_load(const float* p, bool live) {
+  Row12 r;
+  if (live) { r.a = ld4(p); r.b = ld4(p + 4); r.c = ld4(p + 8); }
+  else { r.a = f4zero(); r.b = f4zero(); r.c = f4zero(); }
+  return r;
+}
+// the thread's two rows (nodes lane and lane + 32 of the block) of one channel, global -> the warp's stage
+MSGAT_DEV void rows_fetch(float* stage, const float* xc, int64_t nA, bool liveA, bool liveB, int lane) {
+  const float* pa = liveA ? xc + nA * 12 : xc;          // dead rows are zero-filled; the address stays valid
+  const float* pb = liveB ? xc + (nA + 32) * 12 : xc;
+  float* sa = stage + lane * 12;
+  float* sb = sa + 32 * 12;
+  cp_async16(sa, pa, liveA); cp_async16(sa + 4, pa + 4, liveA); cp_async16(sa + 8, pa + 8, liveA);
+  cp_async16(sb, pb, liveB); cp_async16(sb + 4, pb + 4, liveB); cp_async16(sb + 8, pb + 8, liveB);
+}
+MSGAT_DEV Row12 row_smem(const float* p) { Row12 r; r.a = ld4(p); r.b = ld4(p + 4); r.c = ld4(p + 8); return r; }
+// (x - mean) * rstd of nn.LayerNorm([12]) (msgat.py:152): biased variance, eps 1e-5, same order as tile_load_ln
+MSGAT_DEV void row_normalise(const Row12& x, float (&xh)[12], float& rs_out) {
+  float4 a = x.a, b = x.b, d = x.c;
+  const float mu = (a.x + a.y + a.z + a.w + b.x + b.y + b.z + b.w + d.x + d.y + d.z + d.w) * (1.0f / 12.0f);
+  a.x -= mu; a.y -= mu; a.z -= mu; a.w -= mu; b.x -= mu; b.y -= mu; b.z -= mu; b.w -= mu;
+  d.x -= mu; d.y -= mu; d.z -= mu; d.w -= mu;
+  const float var = (dot4(a, a) + dot4(b, b) + dot4(d, d)) * (1.0f / 12.0f);
+  const float rs = rsqrtf(var + LN_EPS);
+  xh[0] = a.x * rs; xh[1] = a.y * rs; xh[2] = a.z * rs; xh[3] = a.w * rs;
+  xh[4] = b.x * rs; xh[5] = b.y * rs; xh[6] = b.z * rs; xh[7] = b.w * rs;
+  xh[8] = d.x * rs; xh[9] = d.y * rs; xh[10] = d.z * rs; xh[11] = d.w * rs;
+  rs_out = rs;
+}
+
+MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
+  float* RED = Wh + C * HS_WP;                       // [HS_WARPS][HS_NODES][12] (after the channel loop)
+  float* LW = RED + 2 * HS_WARPS * HS_NODES * 12;   // [24]
+  float* XS = RED;                                  // [HS_WARPS][2 stages][HS_NODES][12] rows in flight (RED reuses it after the loop)
+  const int n0 = blockIdx.x * HS_NODES, nA = n0 + lane, nB = nA + 32;
+  const bool liveA = nA < a.N, liveB = nB < a.N;
+  const float* xb = a.x + (int64_t)b * C * a.N * 12;
+  float* ring = XS + warp * 2 * HS_NODES * 12;
+  // two channels ahead of the one being consumed: issued before the weights are staged
+  if (warp < C) rows_fetch(ring, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
+  if (warp + HS_WARPS < C) rows_fetch(ring + HS_NODES * 12, xb + (int64_t)(warp + HS_WARPS) * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
+  stage_fc12(Wh, a.fc_w, C);
+  if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  __syncthreads();
+  float lw[12], lb[12];
+  MSGAT_UNROLL
+  for (int t = 0; t < 12; ++t) { lw[t] = LW[t]; lb[t] = LW[12 + t]; }
+  float accA[12], accB[12];
+  MSGAT_UNROLL
+  for (int o = 0; o < 12; ++o) { accA[o] = 0.f; accB[o] = 0.f; }
+  int st = 0;
+  for (int c = warp; c < C; c += HS_WARPS) {
+    cp_async_wait<1>();   // this channel's rows have landed (each thread reads back only what it fetched itself)
+    float* stage = ring + st * HS_NODES * 12;
+    const Row12 xa = row_smem(stage + lane * 12), xc = row_smem(stage + (lane + 32) * 12);
+    float hA[12], hB[12], rs;
+    row_normalise(xa, hA, rs);
+    row_normalise(xc, hB, rs);
+    const int c2 = c + 2 * HS_WARPS;
+    if (c2 < C) rows_fetch(stage, xb + (int64_t)c2 * a.N * 12, nA, liveA, liveB, lane);
+    cp_async_commit();
+    st ^= 1;
+    MSGAT_UNROLL
+    for (int t = 0; t < 12; ++t) { hA[t] = hA[t] * lw[t] + lb[t]; hB[t] = hB[t] * lw[t] + lb[t]; }
+    const float* w = Wh + c * HS_WP;
+    MSGAT_UNROLL
+    for (int o = 0; o < 12; ++o) {
+      const float4 w0 = ld4(w + o * 12), w1 = ld4(w + o * 12 + 4), w2 = ld4(w + o * 12 + 8);
+      float sA = accA[o], sB = accB[o];
+      sA = fmaf(hA[0], w0.x, sA); sA = fmaf(hA[1], w0.y, sA); sA = fmaf(hA[2], w0.z, sA); sA = fmaf(hA[3], w0.w, sA);
+      sA = fmaf(hA[4], w1.x, sA); sA = fmaf(hA[5], w1.y, sA); sA = fmaf(hA[6], w1.z, sA); sA = fmaf(hA[7], w1.w, sA);
+      sA = fmaf(hA[8], w2.x, sA); sA = fmaf(hA[9], w2.y, sA); sA = fmaf(hA[10], w2.z, sA); sA = fmaf(hA[11], w2.w, sA);
+      sB = fmaf(hB[0], w0.x, sB); sB = fmaf(hB[1], w0.y, sB); sB = fmaf(hB[2], w0.z, sB); sB = fmaf(hB[3], w0.w, sB);
+      sB = fmaf(hB[4], w1.x, sB); sB = fmaf(hB[5], w1.y, sB); sB = fmaf(hB[6], w1.z, sB); sB = fmaf(hB[7], w1.w, sB);
+      sB = fmaf(hB[8], w2.x, sB); sB = fmaf(hB[9], w2.y, sB); sB = fmaf(hB[10], w2.z, sB); sB = fmaf(hB[11], w2.w, sB);
+      accA[o] = sA; accB[o] = sB;
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();   // every warp is done with its ring before RED overwrites it
+  // fixed-order sum of the eight channel groups
+  float* ra = RED + (warp * HS_NODES + lane) * 12;
+  float* rb = ra + 32 * 12;
+  st4(ra, make_float4(accA[0], accA[1], accA[2], accA[3])); st4(ra + 4, make_float4(accA[4], accA[5], accA[6], accA[7]));
+  st4(ra + 8, make_float4(accA[8], accA[9], accA[10], accA[11]));
+  st4(rb, make_float4(accB[0], accB[1], accB[2], accB[3])); st4(rb + 4, make_float4(accB[4], accB[5], accB[6], accB[7]));
+  st4(rb + 8, make_float4(accB[8], accB[9], accB[10], accB[11]));
+  __syncthreads();
+  for (int it = tid; it < HS_NODES * 12; it += 256) {
+    const int nl = it / 12, o = it - nl * 12, n = n0 + nl;
+    if (n >= a.N) continue;
+    float s = __ldg(a.fc_b + o);
+    MSGAT_UNROLL
+    for (int w = 0; w < HS_WARPS; ++w) s += RED[w * HS_NODES * 12 + it];
+    const int64_t g = ((int64_t)b * a.N + n) * 12 + o;
+    a.head_out[g] = s;
+    const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
+    a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
+  }
+}
+
+// LayerNorm([12]) backward of one row: dh -> dx (masked by x > 0 when x is a ReLU output), affine gradient
+// partials.  The normalised row comes back from the warp buffer the thread wrote it to.
+MSGAT_DEV void head_ln_bwd_row(const float (&dh)[12], const Row12& xr, const float* hrow, float rs, const float* LW,
+                               float (&lnw_acc)[12], float (&lnb_acc)[12], int x_is_relu, float* dst) {
+  const float4 h0 = ld4(hrow), h1 = ld4(hrow + 4), h2 = ld4(hrow + 8);
+  const float xh[12] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w, h2.x, h2.y, h2.z, h2.w};
+  const float xv[12] = {xr.a.x, xr.a.y, xr.a.z, xr.a.w, xr.b.x, xr.b.y, xr.b.z, xr.b.w, xr.c.x, xr.c.y, xr.c.z, xr.c.w};
+  float m1 = 0.f, m2 = 0.f;
+  MSGAT_UNROLL
+  for (int t = 0; t < 12; ++t) {
+    lnw_acc[t] += dh[t] * xh[t]; lnb_acc[t] += dh[t];
+    const float gg = dh[t] * LW[t];
+    m1 += gg; m2 += gg * xh[t];
+  }
+  m1 *= (1.0f / 12.0f); m2 *= (1.0f / 12.0f);
+  float o12[12];
+  MSGAT_UNROLL
+  for (int t = 0; t < 12; ++t) {
+    float v = rs * (dh[t] * LW[t] - m1 - xh[t] * m2);
+    if (x_is_relu && !(xv[t] > 0.f)) v = 0.f;
+    o12[t] = v;
+  }
+  if (dst) {
+    st4(dst, make_float4(o12[0], o12[1], o12[2], o12[3]));
+    st4(dst + 4, make_float4(o12[4], o12[5], o12[6], o12[7]));
+    st4(dst + 8, make_float4(o12[8], o12[9], o12[10], o12[11]));
+  }
+}
+
+// Backward of the same block shape.  dh = W^T dy per row and the LayerNorm backward stay in the
+// registers of the row's thread; the fc weight gradient of a channel, dW[c][o][t] =
+// ln_w[t] * sum_n dy[n][o] xh[c][n][t] + ln_b[t] * sum_n dy[n][o], is contracted over the block's 64
+// nodes by the warp that owns the channel: the normalised rows go through a per-warp buffer,
+// 27 lanes own (node third, o quad, t quad) and combine the thirds with two shuffles.
+MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
+  float* HB = Wh + C * HS_WP;                        // [HS_WARPS][HS_NODES][12]  normalised rows of the warp's channel
+  float* DY = HB + HS_WARPS * HS_NODES * 12;        // [HS_NODES][12]   dy = dout * gate
+  float* DYT = DY + HS_NODES * 12;                  // [12][HS_NODES]
+  float* LW = DYT + HS_NODES * 12;                  // [24]
+  float* BS = LW + 24;                              // [12] column sums of DY (fc bias gradient of the block)
+  float* RED = BS + 12;                             // [HS_WARPS][24]
+  float* XS = RED + HS_WARPS * 24;                  // [HS_WARPS][HS_NODES][12]  next channel's rows in flight
+  const int n0 = blockIdx.x * HS_NODES, nA = n0 + lane, nB = nA + 32;
+  const bool liveA = nA < a.N, liveB = nB < a.N;
+  const float* xb = a.x + (int64_t)b * C * a.N * 12;
+  // the first channel's rows are in flight while the block stages the weights and dy
+  float* stage = XS + warp * HS_NODES * 12;
+  if (warp < C) rows_fetch(stage, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
+  stage_fc12(Wh, a.fc_w, C);
+  if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  for (int it = tid; it < HS_NODES * 12; it += 256) {
+    const int nl = it / 12, o = it - nl * 12, n = n0 + nl;
+    float dy = 0.f;
+    if (n < a.N) {
+      const int64_t g = ((int64_t)b * a.N + n) * 12 + o;
+      const float d = a.dout[g];
+      const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
+      dy = d * gt;
+      if (a.d_gate) a.d_gate[g] = d * a.head_out[g];
+    }
+    DY[it] = dy;
+    DYT[o * HS_NODES + nl] = dy;
+  }
+  __syncthreads();
+  if (tid < 12) {
+    float s = 0.f;
+    for (int nl = 0; nl < HS_NODES; ++nl) s += DY[nl * 12 + tid];
+    BS[tid] = s;
+  }
+  __syncthreads();
+  float* part = a.part + (int64_t)(b * gridDim.x + blockIdx.x) * a.pstride;
+  float* hb = HB + warp * HS_NODES * 12;
+  float lnw_acc[12], lnb_acc[12];
+  MSGAT_UNROLL
+  for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
+  const int third = lane / 9, item = lane - third * 9, oq = item / 3, tq = item - oq * 3;
+  for (int c = warp; c < C; c += HS_WARPS) {
+    cp_async_wait<0>();   // each thread reads back only the rows it fetched itself
+    const Row12 xa = row_smem(stage + lane * 12), xc = row_smem(stage + (lane + 32) * 12);
+    float hA[12], hB[12], rsA, rsB;
+    row_normalise(xa, hA, rsA);
+    row_normalise(xc, hB, rsB);
+    if (c + HS_WARPS < C) rows_fetch(stage, xb + (int64_t)(c + HS_WARPS) * a.N * 12, nA, liveA, liveB, lane);
+    cp_async_commit();
+    {
+      float* ra = hb + lane * 12;
+      float* rb = ra + 32 * 12;
+      st4(ra, make_float4(hA[0], hA[1], hA[2], hA[3])); st4(ra + 4, make_float4(hA[4], hA[5], hA[6], hA[7]));
+      st4(ra + 8, make_float4(hA[8], hA[9], hA[10], hA[11]));
+      st4(rb, make_float4(hB[0], hB[1], hB[2], hB[3])); st4(rb + 4, make_float4(hB[4], hB[5], hB[6], hB[7]));
+      st4(rb + 8, make_float4(hB[8], hB[9], hB[10], hB[11]));
+    }
+    // dh[t] = sum_o fc_w[o][t][c] dy[n][o]
+    float dA[12], dB[12];
+    MSGAT_UNROLL
+    for (int t = 0; t < 12; ++t) { dA[t] = 0.f; dB[t] = 0.f; }
+    const float* w = Wh + c * HS_WP;
+    MSGAT_UNROLL
+    for (int o = 0; o < 12; ++o) {
+      const float4 w0 = ld4(w + o * 12), w1 = ld4(w + o * 12 + 4), w2 = ld4(w + o * 12 + 8);
+      const float ya = DYT[o * HS_NODES + lane], yb = DYT[o * HS_NODES + 32 + lane];
+      dA[0] = fmaf(ya, w0.x, dA[0]); dA[1] = fmaf(ya, w0.y, dA[1]); dA[2] = fmaf(ya, w0.z, dA[2]); dA[3] = fmaf(ya, w0.w, dA[3]);
+      dA[4] = fmaf(ya, w1.x, dA[4]); dA[5] = fmaf(ya, w1.y, dA[5]); dA[6] = fmaf(ya, w1.z, dA[6]); dA[7] = fmaf(ya, w1.w, dA[7]);
+      dA[8] = fmaf(ya, w2.x, dA[8]); dA[9] = fmaf(ya, w2.y, dA[9]); dA[10] = fmaf(ya, w2.z, dA[10]); dA[11] = fmaf(ya, w2.w, dA[11]);
+      dB[0] = fmaf(yb, w0.x, dB[0]); dB[1] = fmaf(yb, w0.y, dB[1]); dB[2] = fmaf(yb, w0.z, dB[2]); dB[3] = fmaf(yb, w0.w, dB[3]);
+      dB[4] = fmaf(yb, w1.x, dB[4]); dB[5] = fmaf(yb, w1.y, dB[5]); dB[6] = fmaf(yb, w1.z, dB[6]); dB[7] = fmaf(yb, w1.w, dB[7]);
+      dB[8] = fmaf(yb, w2.x, dB[8]); dB[9] = fmaf(yb, w2.y, dB[9]); dB[10] = fmaf(yb, w2.z, dB[10]); dB[11] = fmaf(yb, w2.w, dB[11]);
+    }
+    // LayerNorm backward, masked by the ReLU that produced x, one row per (thread, node)
+    head_ln_bwd_row(dA, xa, hb + lane * 12, rsA, LW, lnw_acc, lnb_acc, a.x_is_relu,
+                    liveA ? a.dx + (((int64_t)b * C + c) * a.N + nA) * 12 : nullptr);
+    head_ln_bwd_row(dB, xc, hb + (lane + 32) * 12, rsB, LW, lnw_acc, lnb_acc, a.x_is_relu,
+                    liveB ? a.dx + (((int64_t)b * C + c) * a.N + nB) * 12 : nullptr);
+    __syncwarp();
+    // fc weight gradient of channel c over the block's nodes
+    float4 g0 = f4zero(), g1 = f4zero(), g2 = f4zero(), g3 = f4zero();
+    if (lane < 27) {
+      for (int nl = third; nl < HS_NODES; nl += 3) {
+        const float4 d4 = ld4(DY + nl * 12 + oq * 4), h4 = ld4(hb + nl * 12 + tq * 4);
+        fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
+      }
+    }
+    float gv[16] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w, g2.x, g2.y, g2.z, g2.w, g3.x, g3.y, g3.z, g3.w};
+    MSGAT_UNROLL
+    for (int i = 0; i < 16; ++i) {
+      const float v1 = __shfl_sync(0xffffffffu, gv[i], (lane + 9) & 31), v2 = __shfl_sync(0xffffffffu, gv[i], (lane + 18) & 31);
+      gv[i] = (gv[i] + v1) + v2;
+    }
+    if (lane < 9) {
+      MSGAT_UNROLL
+      for (int i = 0; i < 4; ++i) {
+        const int o = oq * 4 + i;
+        const float bs = BS[o];
+        MSGAT_UNROLL
+        for (int j = 0; j < 4; ++j) {
+          const int t = tq * 4 + j;
+          part[((int64_t)o * 12 + t) * C + c] = fmaf(LW[t], gv[i * 4 + j], LW[12 + t] * bs);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (tid < 12) part[144 * C + tid] = BS[tid];
+  MSGAT_UNROLL
+  for (int t = 0; t < 12; ++t) {
+    const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
+    if (lane == 0) { RED[warp * 24 + t] = w; RED[warp * 24 + 12 + t] = bb; }
+  }
+  __syncthreads();
+  if (tid < 24) {
+    float s = 0.f;
+    for (int w = 0; w < HS_WARPS; ++w) s += RED[w * 24 + tid];
+    part[144 * C + 12 + tid] = s;
+  }
+}
+
+static bool head_streaming(const msgat_head_desc* d) {
+  return d->Tout == 12 && ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4 <= 110 * 1024;
+}
+
 static int head_J(const msgat_head_desc* d, int ntile) {
   int J = (2 * 148) / d->B;
   return J > ntile ? ntile : (J < 1 ? 1 : J);
@@ -195,8 +501,13 @@ int msgat_head_forward(const msgat_head_desc* d, const float* x, const float* ln
   a.x = x; a.C = d->C; a.N = d->N; a.Tout = d->Tout; a.ntile = (d->N + HNT - 1) / HNT; a.J = head_J(d, a.ntile);
   a.accumulate = d->accumulate; a.ln_w = ln_w; a.ln_b = ln_b; a.fc_w = fc_w; a.fc_b = fc_b; a.gate = gate;
   a.gate_sb = d->gate_sb; a.head_out = head_out; a.out = out;
-  size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
-  MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+  if (head_streaming(d)) {
+    size_t smem = ((size_t)d->C * HS_WP + 2 * HS_WARPS * HS_NODES * 12 + 24) * 4;
+    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B), dim3(256), smem, stream, a);
+  } else {
+    size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
+    MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { msgat_set_error("head_forward: %s", cudaGetErrorString(e)); return -100; }
   return 0;
@@ -204,7 +515,8 @@ int msgat_head_forward(const msgat_head_desc* d, const float* x, const float* ln
 
 int64_t msgat_head_scratch_floats(const msgat_head_desc* d) {
   const int ntile = (d->N + HNT - 1) / HNT;
-  return (int64_t)head_J(d, ntile) * d->B * (d->Tout * 12 * d->C + d->Tout + 24);
+  const int64_t blocks = head_streaming(d) ? (d->N + HS_NODES - 1) / HS_NODES : head_J(d, ntile);
+  return blocks * d->B * (d->Tout * 12 * d->C + d->Tout + 24);
 }
 
 int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* ln_w, const float* ln_b, const float* fc_w,
@@ -218,11 +530,18 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   a.head_out = const_cast<float*>(head_out); a.dout = dout; a.dx = dx; a.d_gate = d_gate; a.part = scratch;
   const int nW = d->Tout * 12 * d->C;
   a.pstride = nW + d->Tout + 24;
-  size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
-  MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+  int nblk = a.J;
+  if (head_streaming(d)) {
+    nblk = (d->N + HS_NODES - 1) / HS_NODES;
+    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
+    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B), dim3(256), smem, stream, a);
+  } else {
+    size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
+    MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+  }
   ReduceArgs r;
   int nj = 0, tot = 0;
-  const int nparts = a.J * d->B;
+  const int nparts = nblk * d->B;
   auto add = [&](float* dst, const float* src, int n) {
     if (!dst) return;
     r.j[nj] = RJob{dst, src, n, nparts, 1, 0, (int64_t)a.pstride, 0};
