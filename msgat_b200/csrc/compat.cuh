@@ -83,6 +83,19 @@ MSGAT_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "me
 template <int N> MSGAT_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 #endif
 
+// exp(x) for x <= 0 in the dense softmax passes: one multiply + MUFU.EX2 (ex2.approx, 2^-22 relative) instead of the
+// ~10-instruction expf.  The product x * log2(e) is rounded once, so the relative error grows as |x| * 6e-8: the
+// columns that matter to a softmax row have |x| of a few units, the ones with large |x| contribute ~0.
+#ifdef MSGAT_EMU
+MSGAT_DEV float exp_neg(float x) { return exp2f(x * 1.4426950408889634f); }
+#else
+MSGAT_DEV float exp_neg(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
+#endif
+
 MSGAT_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 MSGAT_DEV void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 MSGAT_DEV float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }

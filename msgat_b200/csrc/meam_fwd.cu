@@ -23,7 +23,7 @@ struct PrepArgs {
 };
 
 template <int NT>
-MSGAT_KERNEL MSGAT_LB(256, 1) k_prep(PrepArgs a) {
+MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
   constexpr int P = NT * 12, PS = P + 4, PQ = NT * 3;
   MSGAT_DYN_SMEM(smem_raw);
   float* H = reinterpret_cast<float*>(smem_raw);  // [C][PS]

@@ -10,8 +10,8 @@
 #include "kernels.h"
 #include "compat.cuh"
 
-#define SS_ROWS 32
-#define SS_LANES 8
+#define SS_ROWS 64
+#define SS_QUART 4
 #define SS_CHUNK 256
 
 struct SStatsArgs {
@@ -22,11 +22,16 @@ struct SStatsArgs {
   double *l, *E;  // kept in fp64: the backward subtracts delta * E and delta / l * P from sums they nearly cancel
 };
 
+// Thread map: a block owns SS_ROWS = 64 rows; a warp is 32 rows x ONE column quarter, so the q row of a
+// column is the same shared-memory address for every lane (a broadcast: one wavefront per 128-bit read
+// instead of one per 8 lanes) and the 24 FMAs + exp of a pair run against registers only.  The four
+// column quarters of a row are merged through shared memory in a fixed order.
 MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   float* Q = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][12]
   float* WG = Q + SS_CHUNK * 12;                  // [144]
-  const int b = blockIdx.y, rl = threadIdx.x / SS_LANES, cl = threadIdx.x % SS_LANES;
+  double* MG = reinterpret_cast<double*>(WG + 144);  // [SS_QUART][SS_ROWS][14]: m, l, E[12]
+  const int b = blockIdx.y, rl = threadIdx.x % SS_ROWS, cq = threadIdx.x / SS_ROWS;
   const int n = blockIdx.x * SS_ROWS + rl;
   const bool live = n < a.N;
   const float* qb = a.qs + (int64_t)b * a.N * 12;
@@ -51,14 +56,14 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
     __syncthreads();
     for (int i = threadIdx.x; i < len * 3; i += blockDim.x) st4(Q + i * 4, ld4(qb + (int64_t)j0 * 12 + i * 4));
     __syncthreads();
-    // Four columns per step: the scores and the products p * q of a group are summed in fp32 (p itself
-    // is an fp32 expf), the running sums stay in fp64 -- one conversion per group instead of one per pair.
-    for (int j = cl; j < len; j += 4 * SS_LANES) {
+    // Four consecutive columns per step: the scores and the products p * q of a group are summed in fp32 (p
+    // itself is an fp32 expf), the running sums stay in fp64 -- one conversion per group instead of one per pair.
+    for (int j = cq * 4; j < len; j += 4 * SS_QUART) {
       float4 q[4][3];
       float sc4[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int ju = j + u * SS_LANES;
+        const int ju = j + u;
         const float* qj = Q + (ju < len ? ju : j) * 12;
         q[u][0] = ld4(qj); q[u][1] = ld4(qj + 4); q[u][2] = ld4(qj + 8);
         float sv = U[0] * q[u][0].x;
@@ -79,7 +84,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
       for (int t = 0; t < 12; ++t) Ec[t] = 0.f;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const float pf = expf(sc4[u] - m);   // 0 for the padded columns
+        const float pf = exp_neg(sc4[u] - m);   // 0 for the padded columns
         lc += pf;
         Ec[0] = fmaf(pf, q[u][0].x, Ec[0]); Ec[1] = fmaf(pf, q[u][0].y, Ec[1]); Ec[2] = fmaf(pf, q[u][0].z, Ec[2]); Ec[3] = fmaf(pf, q[u][0].w, Ec[3]);
         Ec[4] = fmaf(pf, q[u][1].x, Ec[4]); Ec[5] = fmaf(pf, q[u][1].y, Ec[5]); Ec[6] = fmaf(pf, q[u][1].z, Ec[6]); Ec[7] = fmaf(pf, q[u][1].w, Ec[7]);
@@ -90,35 +95,37 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
       for (int t = 0; t < 12; ++t) E[t] += (double)Ec[t];
     }
   }
-  // combine the 8 column lanes of each row (lanes of a row are adjacent in the warp)
-  float M = m;
-  M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, 1));
-  M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, 2));
-  M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, 4));
-  const double sc = (m == -INFINITY) ? 0.0 : (double)expf(m - M);
-  l *= sc;
-  l += __shfl_xor_sync(0xffffffffu, l, 1);
-  l += __shfl_xor_sync(0xffffffffu, l, 2);
-  l += __shfl_xor_sync(0xffffffffu, l, 4);
-  for (int t = 0; t < 12; ++t) {
-    double e = E[t] * sc;
-    e += __shfl_xor_sync(0xffffffffu, e, 1);
-    e += __shfl_xor_sync(0xffffffffu, e, 2);
-    e += __shfl_xor_sync(0xffffffffu, e, 4);
-    E[t] = e;
+  // merge the column quarters of each row, quarter 0 first
+  {
+    double* mine = MG + ((int64_t)cq * SS_ROWS + rl) * 14;
+    mine[0] = (double)m; mine[1] = l;
+    for (int t = 0; t < 12; ++t) mine[2 + t] = E[t];
   }
-  if (!live) return;
+  __syncthreads();
+  if (cq != 0 || !live) return;
+  float M = m;
+  for (int k = 1; k < SS_QUART; ++k) M = fmaxf(M, (float)MG[((int64_t)k * SS_ROWS + rl) * 14]);
+  {
+    const double sc = (m == -INFINITY) ? 0.0 : (double)expf(m - M);
+    l *= sc;
+    for (int t = 0; t < 12; ++t) E[t] *= sc;
+  }
+  for (int k = 1; k < SS_QUART; ++k) {
+    const double* o = MG + ((int64_t)k * SS_ROWS + rl) * 14;
+    const float mk = (float)o[0];
+    const double sc = (mk == -INFINITY) ? 0.0 : (double)expf(mk - M);
+    l += o[1] * sc;
+    for (int t = 0; t < 12; ++t) E[t] += o[2 + t] * sc;
+  }
   const double invd = 1.0 / l;
   const float inv = (float)invd;
-  if (cl == 0) {
-    a.m[(int64_t)b * a.N + n] = M;
-    a.l[(int64_t)b * a.N + n] = l;
-    for (int t = 0; t < 12; ++t) a.E[((int64_t)b * a.N + n) * 12 + t] = E[t] * invd;
-    for (int t = 0; t < 12; ++t) a.U[((int64_t)b * a.N + n) * 12 + t] = U[t];  // reused by k_scol
-  }
+  a.m[(int64_t)b * a.N + n] = M;
+  a.l[(int64_t)b * a.N + n] = l;
+  for (int t = 0; t < 12; ++t) a.E[((int64_t)b * a.N + n) * 12 + t] = E[t] * invd;
+  for (int t = 0; t < 12; ++t) a.U[((int64_t)b * a.N + n) * 12 + t] = U[t];  // reused by k_scol
   // masked attention at the adjacency non-zeros of this row (attention.py:36: att * adjacency)
   const int e1 = a.row_ptr[n + 1];
-  for (int e = a.row_ptr[n] + cl; e < e1; e += SS_LANES) {
+  for (int e = a.row_ptr[n]; e < e1; ++e) {
     const float* qi = qb + (int64_t)a.col_idx[e] * 12;
     float s = 0.f;
     for (int t = 0; t < 12; ++t) s = fmaf(U[t], qi[t], s);
@@ -134,7 +141,7 @@ int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* 
   a.m = saved + p.o_m; a.l = reinterpret_cast<double*>(saved + p.o_l); a.E = reinterpret_cast<double*>(saved + p.o_E);
   a.U = saved + p.o_U; a.pw = saved + p.o_pw;
   dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B);
-  size_t smem = (SS_CHUNK * 12 + 144) * sizeof(float);
+  size_t smem = (SS_CHUNK * 12 + 144) * sizeof(float) + (size_t)SS_QUART * SS_ROWS * 14 * sizeof(double);
   MSGAT_LAUNCH(k_sstats, grid, dim3(256), smem, stream, a);
   return 0;
 }
@@ -153,8 +160,9 @@ struct SColArgs {
 
 MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][20]: U[12], m, w = delta / l; the 80-byte pitch keeps the 8 row lanes on distinct banks
-  const int b = blockIdx.y, rl = threadIdx.x / SS_LANES, cl = threadIdx.x % SS_LANES;
+  float* UR = reinterpret_cast<float*>(smem_raw);  // [SS_CHUNK][16]: U[12], m, w = delta / l; read as warp-wide broadcasts
+  double* MG = reinterpret_cast<double*>(UR + SS_CHUNK * 16);  // [SS_QUART][SS_ROWS][12]
+  const int b = blockIdx.y, rl = threadIdx.x % SS_ROWS, cq = threadIdx.x / SS_ROWS;   // same thread map as k_sstats
   const int i = blockIdx.x * SS_ROWS + rl;
   const bool live = i < a.N;
   const float* qb = a.qs + (int64_t)b * a.N * 12;
@@ -168,30 +176,30 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     // stage the U rows of this chunk (written by k_sstats) with their (m, delta / l)
     for (int k = threadIdx.x; k < len * 3; k += blockDim.x) {
       const int r = k / 3, c4 = (k - r * 3) * 4;
-      st4(UR + r * 20 + c4, ld4(Ub + (int64_t)(n0 + r) * 12 + c4));
+      st4(UR + r * 16 + c4, ld4(Ub + (int64_t)(n0 + r) * 12 + c4));
     }
     for (int r = threadIdx.x; r < len; r += blockDim.x) {
       const int64_t g = (int64_t)b * a.N + n0 + r;
-      UR[r * 20 + 12] = a.m[g];
-      UR[r * 20 + 13] = (float)((double)a.delta[g] / a.l[g]);
+      UR[r * 16 + 12] = a.m[g];
+      UR[r * 16 + 13] = (float)((double)a.delta[g] / a.l[g]);
     }
     __syncthreads();
-    // four rows per step, summed in fp32 inside the group and in fp64 across groups (see k_sstats)
-    for (int r = cl; r < len; r += 4 * SS_LANES) {
+    // four consecutive rows per step, summed in fp32 inside the group and in fp64 across groups (see k_sstats)
+    for (int r = cq * 4; r < len; r += 4 * SS_QUART) {
       float ac[12];
 #pragma unroll
       for (int t = 0; t < 12; ++t) ac[t] = 0.f;
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        const int rg = r + g * SS_LANES;
+        const int rg = r + g;
         if (rg < len) {
-          const float* u = UR + rg * 20;
+          const float* u = UR + rg * 16;
           const float4 u0 = ld4(u), u1 = ld4(u + 4), u2 = ld4(u + 8), u3 = ld4(u + 12);
           float sv = qi[0] * u0.x;
           sv = fmaf(qi[1], u0.y, sv); sv = fmaf(qi[2], u0.z, sv); sv = fmaf(qi[3], u0.w, sv);
           sv = fmaf(qi[4], u1.x, sv); sv = fmaf(qi[5], u1.y, sv); sv = fmaf(qi[6], u1.z, sv); sv = fmaf(qi[7], u1.w, sv);
           sv = fmaf(qi[8], u2.x, sv); sv = fmaf(qi[9], u2.y, sv); sv = fmaf(qi[10], u2.z, sv); sv = fmaf(qi[11], u2.w, sv);
-          const float pf = expf(sv - u3.x) * u3.y;   // u3.y = (float)(delta / l)
+          const float pf = exp_neg(sv - u3.x) * u3.y;   // u3.y = (float)(delta / l)
           ac[0] = fmaf(pf, u0.x, ac[0]); ac[1] = fmaf(pf, u0.y, ac[1]); ac[2] = fmaf(pf, u0.z, ac[2]); ac[3] = fmaf(pf, u0.w, ac[3]);
           ac[4] = fmaf(pf, u1.x, ac[4]); ac[5] = fmaf(pf, u1.y, ac[5]); ac[6] = fmaf(pf, u1.z, ac[6]); ac[7] = fmaf(pf, u1.w, ac[7]);
           ac[8] = fmaf(pf, u2.x, ac[8]); ac[9] = fmaf(pf, u2.y, ac[9]); ac[10] = fmaf(pf, u2.z, ac[10]); ac[11] = fmaf(pf, u2.w, ac[11]);
@@ -201,22 +209,24 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
       for (int t = 0; t < 12; ++t) acc[t] += (double)ac[t];
     }
   }
-  for (int t = 0; t < 12; ++t) {
-    double e = acc[t];
-    e += __shfl_xor_sync(0xffffffffu, e, 1);
-    e += __shfl_xor_sync(0xffffffffu, e, 2);
-    e += __shfl_xor_sync(0xffffffffu, e, 4);
-    acc[t] = e;
+  {
+    double* mine = MG + ((int64_t)cq * SS_ROWS + rl) * 12;
+    for (int t = 0; t < 12; ++t) mine[t] = acc[t];
   }
-  if (live && cl == 0)
-    for (int t = 0; t < 12; ++t) a.dq[((int64_t)b * a.N + i) * 12 + t] = (float)(-acc[t]);
+  __syncthreads();
+  if (cq != 0 || !live) return;
+  for (int k = 1; k < SS_QUART; ++k) {
+    const double* o = MG + ((int64_t)k * SS_ROWS + rl) * 12;
+    for (int t = 0; t < 12; ++t) acc[t] += o[t];
+  }
+  for (int t = 0; t < 12; ++t) a.dq[((int64_t)b * a.N + i) * 12 + t] = (float)(-acc[t]);
 }
 
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream) {
   SColArgs a;
   a.N = p.N; a.qs = saved + p.o_qs; a.U = saved + p.o_U; a.m = saved + p.o_m; a.l = reinterpret_cast<const double*>(saved + p.o_l); a.delta = delta; a.dq = dq;
   dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B);
-  size_t smem = (SS_CHUNK * 20) * sizeof(float);
+  size_t smem = (SS_CHUNK * 16) * sizeof(float) + (size_t)SS_QUART * SS_ROWS * 12 * sizeof(double);
   MSGAT_LAUNCH(k_scol, grid, dim3(256), smem, stream, a);
   return 0;
 }
