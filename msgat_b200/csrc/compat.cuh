@@ -96,6 +96,17 @@ MSGAT_DEV float exp_neg(float x) {
 }
 #endif
 
+// two fp32 FMAs in one instruction (FFMA2, sm_100): halves the issue slots of the FMA-dense inner loops
+#ifdef MSGAT_EMU
+MSGAT_DEV float2 ffma2(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+MSGAT_DEV float2 fmul2(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+#else
+MSGAT_DEV float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+MSGAT_DEV float2 fmul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+#endif
+MSGAT_DEV float2 lo2(const float4& v) { return make_float2(v.x, v.y); }
+MSGAT_DEV float2 hi2(const float4& v) { return make_float2(v.z, v.w); }
+
 MSGAT_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 MSGAT_DEV void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 MSGAT_DEV float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }

@@ -48,6 +48,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
       U[t2] = s;
     }
   }
+  float2 U2[6];
+  for (int k = 0; k < 6; ++k) U2[k] = make_float2(U[2 * k], U[2 * k + 1]);
   float m = -INFINITY;
   double l = 0.0, E[12];
   for (int t = 0; t < 12; ++t) E[t] = 0.0;
@@ -66,10 +68,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
         const int ju = j + u;
         const float* qj = Q + (ju < len ? ju : j) * 12;
         q[u][0] = ld4(qj); q[u][1] = ld4(qj + 4); q[u][2] = ld4(qj + 8);
-        float sv = U[0] * q[u][0].x;
-        sv = fmaf(U[1], q[u][0].y, sv); sv = fmaf(U[2], q[u][0].z, sv); sv = fmaf(U[3], q[u][0].w, sv);
-        sv = fmaf(U[4], q[u][1].x, sv); sv = fmaf(U[5], q[u][1].y, sv); sv = fmaf(U[6], q[u][1].z, sv); sv = fmaf(U[7], q[u][1].w, sv);
-        sv = fmaf(U[8], q[u][2].x, sv); sv = fmaf(U[9], q[u][2].y, sv); sv = fmaf(U[10], q[u][2].z, sv); sv = fmaf(U[11], q[u][2].w, sv);
+        float2 s2 = fmul2(U2[0], lo2(q[u][0]));
+        s2 = ffma2(U2[1], hi2(q[u][0]), s2); s2 = ffma2(U2[2], lo2(q[u][1]), s2); s2 = ffma2(U2[3], hi2(q[u][1]), s2);
+        s2 = ffma2(U2[4], lo2(q[u][2]), s2); s2 = ffma2(U2[5], hi2(q[u][2]), s2);
+        const float sv = s2.x + s2.y;
         sc4[u] = ju < len ? sv : -INFINITY;
       }
       const float mg = fmaxf(fmaxf(sc4[0], sc4[1]), fmaxf(sc4[2], sc4[3]));
@@ -79,20 +81,22 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
         for (int t = 0; t < 12; ++t) E[t] *= c;
         m = mg;
       }
-      float lc = 0.f, Ec[12];
+      float lc = 0.f;
+      float2 Ec2[6];
 #pragma unroll
-      for (int t = 0; t < 12; ++t) Ec[t] = 0.f;
+      for (int k = 0; k < 6; ++k) Ec2[k] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float pf = exp_neg(sc4[u] - m);   // 0 for the padded columns
+        const float2 p2 = make_float2(pf, pf);
         lc += pf;
-        Ec[0] = fmaf(pf, q[u][0].x, Ec[0]); Ec[1] = fmaf(pf, q[u][0].y, Ec[1]); Ec[2] = fmaf(pf, q[u][0].z, Ec[2]); Ec[3] = fmaf(pf, q[u][0].w, Ec[3]);
-        Ec[4] = fmaf(pf, q[u][1].x, Ec[4]); Ec[5] = fmaf(pf, q[u][1].y, Ec[5]); Ec[6] = fmaf(pf, q[u][1].z, Ec[6]); Ec[7] = fmaf(pf, q[u][1].w, Ec[7]);
-        Ec[8] = fmaf(pf, q[u][2].x, Ec[8]); Ec[9] = fmaf(pf, q[u][2].y, Ec[9]); Ec[10] = fmaf(pf, q[u][2].z, Ec[10]); Ec[11] = fmaf(pf, q[u][2].w, Ec[11]);
+        Ec2[0] = ffma2(p2, lo2(q[u][0]), Ec2[0]); Ec2[1] = ffma2(p2, hi2(q[u][0]), Ec2[1]);
+        Ec2[2] = ffma2(p2, lo2(q[u][1]), Ec2[2]); Ec2[3] = ffma2(p2, hi2(q[u][1]), Ec2[3]);
+        Ec2[4] = ffma2(p2, lo2(q[u][2]), Ec2[4]); Ec2[5] = ffma2(p2, hi2(q[u][2]), Ec2[5]);
       }
       l += (double)lc;
 #pragma unroll
-      for (int t = 0; t < 12; ++t) E[t] += (double)Ec[t];
+      for (int k = 0; k < 6; ++k) { E[2 * k] += (double)Ec2[k].x; E[2 * k + 1] += (double)Ec2[k].y; }
     }
   }
   // merge the column quarters of each row, quarter 0 first
@@ -170,6 +174,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
   float qi[12];
   double acc[12];  // the dense sum cancels against the sparse part of dq: keep it in fp64
   for (int t = 0; t < 12; ++t) { qi[t] = live ? qb[(int64_t)i * 12 + t] : 0.f; acc[t] = 0.0; }
+  float2 qi2[6];
+  for (int k = 0; k < 6; ++k) qi2[k] = make_float2(qi[2 * k], qi[2 * k + 1]);
   for (int n0 = 0; n0 < a.N; n0 += SS_CHUNK) {
     const int len = (a.N - n0 < SS_CHUNK) ? a.N - n0 : SS_CHUNK;
     __syncthreads();
@@ -186,27 +192,27 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     __syncthreads();
     // four consecutive rows per step, summed in fp32 inside the group and in fp64 across groups (see k_sstats)
     for (int r = cq * 4; r < len; r += 4 * SS_QUART) {
-      float ac[12];
+      float2 ac2[6];
 #pragma unroll
-      for (int t = 0; t < 12; ++t) ac[t] = 0.f;
+      for (int k = 0; k < 6; ++k) ac2[k] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         const int rg = r + g;
         if (rg < len) {
           const float* u = UR + rg * 16;
           const float4 u0 = ld4(u), u1 = ld4(u + 4), u2 = ld4(u + 8), u3 = ld4(u + 12);
-          float sv = qi[0] * u0.x;
-          sv = fmaf(qi[1], u0.y, sv); sv = fmaf(qi[2], u0.z, sv); sv = fmaf(qi[3], u0.w, sv);
-          sv = fmaf(qi[4], u1.x, sv); sv = fmaf(qi[5], u1.y, sv); sv = fmaf(qi[6], u1.z, sv); sv = fmaf(qi[7], u1.w, sv);
-          sv = fmaf(qi[8], u2.x, sv); sv = fmaf(qi[9], u2.y, sv); sv = fmaf(qi[10], u2.z, sv); sv = fmaf(qi[11], u2.w, sv);
-          const float pf = exp_neg(sv - u3.x) * u3.y;   // u3.y = (float)(delta / l)
-          ac[0] = fmaf(pf, u0.x, ac[0]); ac[1] = fmaf(pf, u0.y, ac[1]); ac[2] = fmaf(pf, u0.z, ac[2]); ac[3] = fmaf(pf, u0.w, ac[3]);
-          ac[4] = fmaf(pf, u1.x, ac[4]); ac[5] = fmaf(pf, u1.y, ac[5]); ac[6] = fmaf(pf, u1.z, ac[6]); ac[7] = fmaf(pf, u1.w, ac[7]);
-          ac[8] = fmaf(pf, u2.x, ac[8]); ac[9] = fmaf(pf, u2.y, ac[9]); ac[10] = fmaf(pf, u2.z, ac[10]); ac[11] = fmaf(pf, u2.w, ac[11]);
+          float2 s2 = fmul2(qi2[0], lo2(u0));
+          s2 = ffma2(qi2[1], hi2(u0), s2); s2 = ffma2(qi2[2], lo2(u1), s2); s2 = ffma2(qi2[3], hi2(u1), s2);
+          s2 = ffma2(qi2[4], lo2(u2), s2); s2 = ffma2(qi2[5], hi2(u2), s2);
+          const float pf = exp_neg((s2.x + s2.y) - u3.x) * u3.y;   // u3.y = (float)(delta / l)
+          const float2 p2 = make_float2(pf, pf);
+          ac2[0] = ffma2(p2, lo2(u0), ac2[0]); ac2[1] = ffma2(p2, hi2(u0), ac2[1]);
+          ac2[2] = ffma2(p2, lo2(u1), ac2[2]); ac2[3] = ffma2(p2, hi2(u1), ac2[3]);
+          ac2[4] = ffma2(p2, lo2(u2), ac2[4]); ac2[5] = ffma2(p2, hi2(u2), ac2[5]);
         }
       }
 #pragma unroll
-      for (int t = 0; t < 12; ++t) acc[t] += (double)ac[t];
+      for (int k = 0; k < 6; ++k) { acc[2 * k] += (double)ac2[k].x; acc[2 * k + 1] += (double)ac2[k].y; }
     }
   }
   {
