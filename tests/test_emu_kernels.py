@@ -29,3 +29,13 @@ def test_emulated_kernels_match_reference_golden(case):
     out, grads, gin = run_case(G)
     fails, _ = check_case(G, out, grads, gin)
     assert not fails, "\n".join(fails)
+
+
+def test_emulated_head_kernels_ragged_shapes():
+    """Streaming (Tout = 12) and generic head kernels on ragged node / channel counts (tests/head_cases.py)."""
+    import torch
+    from head_cases import HEAD_CASES, run_head_case
+    for case in HEAD_CASES:
+        errs = run_head_case(case, torch.device("cpu"))
+        bad = {k: v for k, v in errs.items() if not v < 1e-5}
+        assert not bad, f"{case}: {bad}"
