@@ -10,6 +10,7 @@
 //   k_apply   reads x again: LN, residual 1x1, Mc h, temporal attention + dilated causal
 //             conv chain, sparse spatial aggregation, concat, ReLU, one write of the output.
 // The N x N attention matrix never exists in HBM.
+#include <stdlib.h>
 #include "kernels.h"
 #include "tile_ops.cuh"
 
@@ -434,7 +435,14 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.Y1 = (p.n_conv == 2) ? saved + p.o_Y1 : nullptr;
     const int chunks = ((p.Oc + 3) >> 2) + ((p.Ot + 3) >> 2) + ((p.Os + 3) >> 2);
     size_t smem = (size_t)apply_smem_floats(p, p.NTa) * 4;
-    const int nthr = pick_threads(chunks * p.NTa * 3, 512);
+    // Narrow operators (layer-1 MEAMs: a tile needs < 48 KB) run as 128-thread blocks, four or more per SM: the
+    // kernel is a sequence of barrier-separated phases and independent blocks hide each other's barriers and
+    // loads (measured at C = 1: 123 us with 448 threads x 1 block per SM, 98 us with 128 x 4).  Wide ones
+    // are limited to one block per SM by their tile and keep up to 512 threads.  MSGAT_APPLY_CAP overrides.
+    static int cap_env = -1;
+    if (cap_env < 0) { const char* e = getenv("MSGAT_APPLY_CAP"); cap_env = e ? atoi(e) : 0; }
+    const int cap = cap_env >= 64 ? cap_env : (smem <= 48 * 1024 ? 128 : 512);
+    const int nthr = pick_threads(chunks * p.NTa * 3, cap);
     int occ = (int)(227 * 1024 / (smem + 1024));
     if (occ > 2048 / nthr) occ = 2048 / nthr;
     if (occ > 65536 / (nthr * 128)) occ = 65536 / (nthr * 128);
