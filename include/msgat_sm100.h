@@ -41,8 +41,9 @@ extern "C" {
                                  returned already multiplied by (x > 0) so that the previous
                                  MEAM can set MSGAT_F_DOUT_MASKED */
 
-#define MSGAT_PREC_FP32 0 /* CUDA-core fp32 everywhere (1e-5 path) */
-#define MSGAT_PREC_TF32 1 /* tcgen05 kind::tf32 for the N x N spatial contractions (2e-3 path) */
+#define MSGAT_PREC_FP32 0 /* fp32-grade results (1e-5 bar): CUDA-core fp32 and, for the layer-2 channel mixes,
+                             tcgen05 kind::tf32 with error-compensated operands (hi/lo split, "3xTF32") */
+#define MSGAT_PREC_TF32 1 /* single-pass tcgen05 kind::tf32 channel mixes in the forward (2e-3 bar) */
 
 /* One MEAM-shaped operator.  With all three widths set, LN|RES|RELU|CMIX|SMIX it is
  * MEAM.forward (msgat.py:121-131); with a single width and no flags it is the bare
@@ -142,6 +143,24 @@ int msgat_head_backward(const msgat_head_desc *d, const float *x, const float *l
                         const float *fc_w, const float *gate, const float *head_out, const float *dout,
                         float *dx, float *d_ln_w, float *d_ln_b, float *d_fc_w, float *d_fc_b,
                         float *d_gate, float *scratch, void *stream);
+
+/* Step plumbing on the device.
+ * msgat_loss_forward: Huber loss of engine.py:56 (loss.py:51-52): loss[0] = mean over n elements of
+ *   0.5 r^2 if |r| <= delta else delta |r| - 0.5 delta^2, r = pred - target; dpred (may be null) = d loss / d pred;
+ *   metrics (may be null) is the running state of metrics.py:20-35, double[4] += {sum |r|,
+ *   100 * sum_{target > mask_value} |r / target|, sum r^2, n}: MAE = m[0]/m[3], MAPE = m[1]/m[3],
+ *   RMSE = sqrt(m[2]/m[3]).  No host synchronisation (the reference reads four scalars back per step).
+ *   scratch: msgat_loss_scratch_bytes() bytes, zeroed once by the caller before its first use.
+ * msgat_loss_backward: out = dpred * gout[0] (gout: the device scalar autograd hands to the mean).
+ * msgat_adam_step: torch.optim.Adam(lr, betas, eps, weight_decay) of engine.py:106 over one flat fp32 buffer;
+ *   g is read as g * grad_scale (1 / world size of the gradient all-reduce); step[0] is the device-side count of
+ *   steps taken so far and is advanced by the kernel; scratch: 16 bytes, zeroed once. */
+int64_t msgat_loss_scratch_bytes(void);
+int msgat_loss_forward(const float *pred, const float *target, int64_t n, float delta, float mask_value, float *loss,
+                       float *dpred, double *metrics, void *scratch, void *stream);
+int msgat_loss_backward(const float *dpred, const float *gout, int64_t n, float *out, void *stream);
+int msgat_adam_step(float *p, const float *g, float *m, float *v, int64_t n, float lr, float beta1, float beta2,
+                    float eps, float weight_decay, float grad_scale, int32_t *step, void *scratch, void *stream);
 
 /* Self-test of the tcgen05 (kind::tf32) building block of the tensor-core path; see
  * csrc/tc_probe.cu.  mode 0: D[256,N] = A[K,256]^T B[K,N]; mode 1: D[128,N] = A[Ra,P] B[Rb,P]^T. */

@@ -56,7 +56,8 @@ class HeadDesc(C.Structure):
 EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_launch_count", "msgat_profile",
            "msgat_profile_report", "msgat_adj_count", "msgat_adj_fill",
            "msgat_meam_sizes", "msgat_meam_forward", "msgat_meam_backward", "msgat_head_forward",
-           "msgat_head_scratch_floats", "msgat_head_backward", "msgat_tc_probe"]
+           "msgat_head_scratch_floats", "msgat_head_backward", "msgat_tc_probe",
+           "msgat_loss_scratch_bytes", "msgat_loss_forward", "msgat_loss_backward", "msgat_adam_step"]
 
 _LIB = None
 _DEBUG_BACKEND = False  # set only by tests/emu (kernel-logic debugging on the GPU-less build box)
@@ -68,6 +69,11 @@ def _declare(lib):
     lib.msgat_device_check.restype = C.c_int
     lib.msgat_head_scratch_floats.restype = C.c_int64
     lib.msgat_launch_count.restype = C.c_longlong
+    lib.msgat_loss_scratch_bytes.restype = C.c_int64
+    lib.msgat_loss_forward.argtypes = [_fp, _fp, C.c_int64, C.c_float, C.c_float, _fp, _fp, _fp, _fp, _fp]
+    lib.msgat_loss_backward.argtypes = [_fp, _fp, C.c_int64, _fp, _fp]
+    lib.msgat_adam_step.argtypes = [_fp, _fp, _fp, _fp, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float,
+                                    C.c_float, C.c_float, _fp, _fp, _fp]
     for name in EXPORTS:
         getattr(lib, name)  # AttributeError if the .so is stale
     return lib

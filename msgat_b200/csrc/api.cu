@@ -43,6 +43,21 @@ int msgat_prof_begin(const char* name, cudaStream_t s) {
   g_recs.push_back(r);
   return (int)g_recs.size() - 1;
 }
+int msgat_current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+int msgat_sm_count() {
+  static std::atomic<int> cache[64];
+  const int dev = msgat_current_device() & 63;
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n <= 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
 void msgat_prof_end(int slot, cudaStream_t s) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   cudaEventRecord(g_recs[slot].e1, s);

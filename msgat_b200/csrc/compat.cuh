@@ -18,8 +18,11 @@
 #define MSGAT_UNROLL
 #define MSGAT_PIN(x)
 static inline void msgat_prof_tag(const char*, int, int) {}
+static inline int msgat_current_device() { return 0; }
+static inline int msgat_sm_count() { return 148; }
 #else
 #include <cuda_runtime.h>
+#include <atomic>
 #define MSGAT_KERNEL static __global__ void
 #define MSGAT_DEV __device__ __forceinline__
 #define MSGAT_LB(n, m) __launch_bounds__(n, m)
@@ -29,12 +32,17 @@ static inline void msgat_prof_tag(const char*, int, int) {}
 int msgat_prof_begin(const char* name, cudaStream_t s);  // counts the launch; >= 0 when event timing is on
 void msgat_prof_end(int slot, cudaStream_t s);
 void msgat_prof_tag(const char* fmt, int a, int b);
+int msgat_current_device();   // ordinal of the calling thread's current device
+int msgat_sm_count();         // multiprocessors of the current device (148 on a B200), cached per device
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute of the function: one bit per device
+// ordinal and call site (a process may drive several GPUs, e.g. under nn.DataParallel, main.py:53-54).
 #define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...)                                        \
   do {                                                                                            \
-    static bool _attr = false;                                                                    \
-    if (!_attr) {                                                                                 \
+    static std::atomic<unsigned long long> _attr{0ull};                                           \
+    const unsigned long long _bit = 1ull << (msgat_current_device() & 63);                        \
+    if (!(_attr.load(std::memory_order_relaxed) & _bit)) {                                        \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, MSGAT_MAX_SMEM);    \
-      _attr = true;                                                                               \
+      _attr.fetch_or(_bit, std::memory_order_relaxed);                                            \
     }                                                                                             \
     int _slot = msgat_prof_begin(#kern, (cudaStream_t)(stream));                                  \
     kern<<<(grid), (block), (smem), (cudaStream_t)(stream)>>>(__VA_ARGS__);                       \

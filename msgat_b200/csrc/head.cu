@@ -478,7 +478,7 @@ static bool head_streaming(const msgat_head_desc* d) {
 }
 
 static int head_J(const msgat_head_desc* d, int ntile) {
-  int J = (2 * 148) / d->B;
+  int J = (2 * msgat_sm_count()) / d->B;
   return J > ntile ? ntile : (J < 1 ? 1 : J);
 }
 static int head_check(const msgat_head_desc* d) {

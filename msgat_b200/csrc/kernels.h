@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include "plan.h"
+#include "compat.cuh"
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream);
@@ -19,7 +20,7 @@ void msgat_set_error(const char* fmt, ...);
 static inline int tc_ctas_per_sample(int B, int ntile, int waves, const char* env) {
   const char* e = getenv(env);
   if (e && atoi(e) > 0) waves = atoi(e);
-  int J = (148 * waves) / B;
+  int J = (msgat_sm_count() * waves) / B;
   if (J > ntile) J = ntile;
   return J < 1 ? 1 : J;
 }

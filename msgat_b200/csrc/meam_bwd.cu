@@ -923,14 +923,14 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
     if (occ > 2048 / T) occ = 2048 / T;
     if (occ > 65536 / (T * 128)) occ = 65536 / (T * 128);
     if (occ < 1) occ = 1;
-    L.J = pick_J(p.B, p.ntile_b, 148 * occ);
+    L.J = pick_J(p.B, p.ntile_b, msgat_sm_count() * occ);
   }
 #ifndef MSGAT_EMU
   if (tc_dgrad_supported(p)) L.J = tc_dgrad_blocks_per_sample(p);   // the tensor-core data-gradient kernel writes the per-block partials
 #endif
   L.nblk = L.J * p.B;
   L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
-  L.J4 = pick_J(p.B, L.ntile4, 148 * 4); L.nblk4 = L.J4 * p.B;
+  L.J4 = pick_J(p.B, L.ntile4, msgat_sm_count() * 4); L.nblk4 = L.J4 * p.B;
   L.nfin = (p.N + 127) / 128;
   int64_t o = 0;
   const int64_t BN = (int64_t)p.B * p.N;
@@ -990,7 +990,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     if (!out) { msgat_set_error("MEAM backward: forward output needed for the ReLU mask"); return -32; }
     const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
     int blocks = (int)((n4 + 255) / 256);
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
     MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)dout, (const float4*)out,
                  (float4*)(scratch + L.o_G), n4);
     G = scratch + L.o_G;

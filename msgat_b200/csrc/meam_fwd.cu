@@ -448,7 +448,7 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     if (occ > 2048 / nthr) occ = 2048 / nthr;
     if (occ > 65536 / (nthr * 128)) occ = 65536 / (nthr * 128);
     if (occ < 1) occ = 1;
-    int J = (2 * 148 * occ) / p.B;  // about two full waves of resident blocks
+    int J = (2 * msgat_sm_count() * occ) / p.B;  // about two full waves of resident blocks
     if (J > p.ntile_a) J = p.ntile_a;
     if (J < 1) J = 1;
     a.J = J;

@@ -130,9 +130,15 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
   // masked attention at the adjacency non-zeros of this row (attention.py:36: att * adjacency)
   const int e1 = a.row_ptr[n + 1];
   for (int e = a.row_ptr[n]; e < e1; ++e) {
+    // the score of the pair in EXACTLY the arithmetic of the dense pass above (same FFMA2 pairing and order):
+    // for the row's arg-max s - M is then 0.0 and not the rounding difference of two summation orders, which
+    // at |s| of several hundred (peaked weights) would be 1e-5 of the dominant attention weight
     const float* qi = qb + (int64_t)a.col_idx[e] * 12;
-    float s = 0.f;
-    for (int t = 0; t < 12; ++t) s = fmaf(U[t], qi[t], s);
+    const float4 q0 = ld4(qi), q1 = ld4(qi + 4), q2 = ld4(qi + 8);
+    float2 s2 = fmul2(U2[0], lo2(q0));
+    s2 = ffma2(U2[1], hi2(q0), s2); s2 = ffma2(U2[2], lo2(q1), s2); s2 = ffma2(U2[3], hi2(q1), s2);
+    s2 = ffma2(U2[4], lo2(q2), s2); s2 = ffma2(U2[5], hi2(q2), s2);
+    const float s = s2.x + s2.y;
     a.pw[(int64_t)b * a.nnz + e] = expf(s - M) * inv * a.val[e];
   }
 }

@@ -26,6 +26,12 @@ class FlatGradients:
     def zero(self):
         self.flat.zero_()
 
+    def all_reduce_sum(self):
+        """Sum over ranks only: the 1 / world_size of the mean is folded into the optimizer's gradient read
+        (``optim.FlatAdam(grad_scale=1 / world)``), which saves a pass over the buffer."""
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+
     def all_reduce_mean(self):
         """Sum over ranks, divide by the world size: the loss is a mean over the global
         batch (loss.py:51-52) and every rank holds an equal shard."""

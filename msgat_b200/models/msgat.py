@@ -226,6 +226,8 @@ class MSGAT(nn.Module):
         else:
             gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(len(self.tpcs))]
         out = None
+        if X.is_cuda:
+            ops.sparse_adjacency(self.adj)   # built on the caller's stream, before any component stream reads it
         if X.is_cuda and self.concurrent_components and len(self.tpcs) > 1:
             # The M components are independent up to the gated sum (msgat.py:204): each MEAM stack runs on
             # its own stream, so the small per-sample kernels of one component (32 CTAs) and the tail waves

@@ -9,6 +9,7 @@ path runs in the hand-written kernels of ``csrc/``.
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from typing import Dict, Optional, Sequence
 
 import torch
@@ -49,17 +50,25 @@ class SparseAdjacency:
                                                                  self.csc_row, self.csc_eid)])
 
 
-_ADJ_CACHE: Dict[tuple, SparseAdjacency] = {}
+_ADJ_CACHE: Dict[int, tuple] = {}
 
 
 def sparse_adjacency(adj: torch.Tensor) -> SparseAdjacency:
-    """Cached per (storage, version): the adjacency is a frozen parameter."""
-    key = (adj.data_ptr(), adj._version, str(adj.device), tuple(adj.shape))
-    sp = _ADJ_CACHE.get(key)
-    if sp is None:
-        if len(_ADJ_CACHE) > 64:
-            _ADJ_CACHE.clear()
-        sp = _ADJ_CACHE[key] = SparseAdjacency(adj)
+    """CSR/CSC of ``adj``, cached per tensor OBJECT: an entry holds a weak reference to the tensor it was built
+    from and that tensor's version counter, and is used only while both still match.  (Keying on the storage
+    address alone would hand a new model whose adjacency the caching allocator placed at a freed model's
+    address the old graph's CSR.)  The adjacency is a frozen parameter (msgat.py:190), so a model builds its
+    view once."""
+    key = id(adj)
+    ent = _ADJ_CACHE.get(key)
+    if ent is not None:
+        ref, version, ptr, sp = ent
+        if ref() is adj and version == adj._version and ptr == adj.data_ptr():
+            return sp
+    for k in [k for k, e in _ADJ_CACHE.items() if e[0]() is None]:   # drop entries of dead tensors
+        del _ADJ_CACHE[k]
+    sp = SparseAdjacency(adj)
+    _ADJ_CACHE[key] = (weakref.ref(adj), adj._version, adj.data_ptr(), sp)
     return sp
 
 

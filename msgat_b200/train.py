@@ -15,7 +15,8 @@ class GraphedStep:
     """``step = GraphedStep(model, loss_fn, optimizer, grads, example_batch)``; then
     ``loss = step(X, H, D, Y)`` copies the batch into the captured input buffers, replays the graph
     and returns the (device) loss of that step.  The optimizer must be capturable
-    (``torch.optim.Adam(..., fused=True, capturable=True)``), gradients live in ``grads.flat``."""
+    (``msgat_b200.optim.FlatAdam``, or ``torch.optim.Adam(..., fused=True, capturable=True)``), gradients live in
+    ``grads.flat``."""
 
     def __init__(self, model: torch.nn.Module, loss_fn: Callable, optimizer: torch.optim.Optimizer, grads: FlatGradients,
                  example: Sequence[torch.Tensor], warmup: int = 3):
@@ -38,7 +39,10 @@ class GraphedStep:
         loss = self.loss_fn(out, Y)
         self.grads.zero()
         loss.backward()
-        self.grads.all_reduce_mean()
+        if getattr(self.opt, "grad_scale", None) is not None:
+            self.grads.all_reduce_sum()      # optim.FlatAdam divides by the world size while it reads the gradients
+        else:
+            self.grads.all_reduce_mean()
         self.opt.step()
         return loss.detach()
 

@@ -194,6 +194,21 @@ def huber(pred: torch.Tensor, target: torch.Tensor, delta: float) -> torch.Tenso
     return torch.where(r <= delta, 0.5 * r * r, delta * r - 0.5 * delta * delta).mean()
 
 
+def metrics_update(state: Dict[str, float], pred: torch.Tensor, true: torch.Tensor, mask_value: float = 0.0):
+    """``Metrics.update`` metrics.py:20-35: running sums n, AE, APE, SE and the derived MAE / MAPE / RMSE
+    (MAPE divides by ALL elements, not by the number of unmasked ones, as the reference does)."""
+    state["n"] = state.get("n", 0) + true.nelement()
+    state["AE"] = state.get("AE", 0.0) + float(torch.abs(pred - true).sum())
+    mask = true > mask_value
+    mp, mt = pred[mask], true[mask]
+    state["APE"] = state.get("APE", 0.0) + 100 * float(torch.abs((mp - mt) / mt).sum())
+    state["SE"] = state.get("SE", 0.0) + float(torch.square(pred - true).sum())
+    state["MAE"] = state["AE"] / state["n"]
+    state["MAPE"] = state["APE"] / state["n"]
+    state["RMSE"] = (state["SE"] / state["n"]) ** 0.5
+    return state
+
+
 MODEL_DILATIONS = {  # msgat.py:220-229
     "msgat48": [[1, 2], [2, 4]],
     "msgat72": [[1, 2], [2, 4]],

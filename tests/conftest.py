@@ -52,3 +52,16 @@ def rel_l2(a, b):
 @pytest.fixture
 def golden():
     return Golden
+
+
+def pytest_terminal_summary(terminalreporter):
+    """Worst error / noise and error / tolerance per tensor class over the session (tests/parity.py)."""
+    try:
+        import parity
+    except Exception:
+        return
+    if not parity.RATIOS:
+        return
+    terminalreporter.write_line("parity margins (worst over the session): class  n  err/noise  err/tol")
+    for cls, r in sorted(parity.RATIOS.items()):
+        terminalreporter.write_line(f"  {cls:12s} {r['n']:5d}  {r['err_over_noise']:9.2f}  {r['err_over_tol']:7.3f}")

@@ -1,9 +1,11 @@
 """Shared tolerance protocol: per-tensor rel-L2 against the reference's fp64
 result.
 
-fp32 path: error <= max(1e-5, 4 x the reference's own fp32-vs-fp64 error of that tensor,
-4 x the WORST fp32-vs-fp64 error the reference shows on any tensor of the same case).
-The last term is the conditioning envelope of the case.  The attention-weight scalars
+fp32 path: error <= max(1e-5, 4 x the reference's own fp32-vs-fp64 error of that tensor).
+Forward outputs, input gradients and every conv / residual / fc / W weight gradient are held to
+exactly that.  ONLY the attention-weight scalars additionally get 4 x the WORST fp32-vs-fp64
+error the reference shows on any tensor of the same case (the conditioning envelope of the
+case).  The attention-weight scalars
 (alpha, Wg, Wc, Wt) are ill-conditioned reductions: by Euler's identity their gradient is
 sum(dS * S) with every row of dS summing to zero, so fp32 noise that the UPSTREAM gradient
 already carries (1-2e-6 rel-L2 on dx in the reference's own fp32 run, 1.2e-5 in the peaked
@@ -19,10 +21,40 @@ FP32_TOL = 1e-5
 TC_TOL = 2e-3
 NOISE_MULT = 4.0
 ENVELOPE_MULT = 4.0
+# the cancellation-heavy attention scalars: the only tensors the case envelope applies to
+SCALAR_SUFFIXES = ("alpha", "Wg", "Wc", "Wt1", "Wt2")
 
 
-def tolerance(noise, envelope, floor=FP32_TOL):
-    return max(floor, NOISE_MULT * noise, ENVELOPE_MULT * envelope)
+def is_attention_scalar(name: str) -> bool:
+    return name.split(".")[-1] in SCALAR_SUFFIXES
+
+
+def tolerance(noise, envelope, floor=FP32_TOL, scalar=False):
+    """per tensor max(1e-5, 4 x the reference's own fp32-vs-fp64 error of THAT tensor).  Only the
+    attention scalars (alpha, Wg, Wc, Wt1, Wt2) additionally get 4 x the worst noise of the case (see above)."""
+    tol = max(floor, NOISE_MULT * noise)
+    return max(tol, ENVELOPE_MULT * envelope) if scalar else tol
+
+
+# worst error / noise and error / tolerance seen per tensor class, printed at the end of the session
+# (tests/conftest.py) so that a reader of pytest.log sees how much margin each class has
+RATIOS = {}
+
+
+def record(cls, err, noise, tol):
+    r = RATIOS.setdefault(cls, {"err_over_noise": 0.0, "err_over_tol": 0.0, "n": 0})
+    r["n"] += 1
+    if noise > 0:
+        r["err_over_noise"] = max(r["err_over_noise"], err / noise)
+    r["err_over_tol"] = max(r["err_over_tol"], err / tol)
+
+
+def tensor_class(label: str) -> str:
+    if label == "out":
+        return "out"
+    if label.startswith("dinput") or label == "dX":
+        return "dX"
+    return "scalar-grad" if is_attention_scalar(label.split(" ")[-1]) else "weight-grad"
 
 
 def check_case(G, out, grads, gin, floor=FP32_TOL, noise_mult=NOISE_MULT, cond=None):
@@ -32,7 +64,7 @@ def check_case(G, out, grads, gin, floor=FP32_TOL, noise_mult=NOISE_MULT, cond=N
 
     cond = cond or {}
 
-    def one(label, got, want, noise):
+    def one(label, got, want, noise, scalar=False):
         nonlocal worst
         if got is None:
             fails.append(f"{label}: missing")
@@ -41,14 +73,15 @@ def check_case(G, out, grads, gin, floor=FP32_TOL, noise_mult=NOISE_MULT, cond=N
         worst = max(worst, e)
         # a one-element alpha (single input channel) only rescales the scores: its gradient is
         # (2/alpha) sum(dS * S) with every row of dS summing to zero -- pure cancellation, twice the margin
-        nm = noise_mult * (2.0 if want.numel() == 1 else 1.0)
-        tol = max(floor, nm * noise, ENVELOPE_MULT * envelope, 2.0 * cond.get(label, 0.0))
+        nm = noise_mult * (2.0 if (scalar and want.numel() == 1) else 1.0)
+        tol = max(floor, nm * noise, ENVELOPE_MULT * envelope if scalar else 0.0, 2.0 * cond.get(label, 0.0))
+        record(tensor_class(label), e, noise, tol)
         if not e < tol:
             fails.append(f"{label}: rel-L2 {e:.3e} > tol {tol:.3e} (reference fp32 noise {noise:.2e})")
 
     one("out", out, G.out, G.noise("out"))
     for name, g in G.grads.items():
-        one("grad " + name, grads.get(name), g, G.noise("g", name))
+        one("grad " + name, grads.get(name), g, G.noise("g", name), scalar=is_attention_scalar(name))
     for name, g in G.gin.items():
         if name == "adjacency":
             continue

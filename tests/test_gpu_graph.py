@@ -8,21 +8,22 @@ pytestmark = pytest.mark.gpu
 def _setup(seed):
     from msgat_b200 import models, synthetic
     from msgat_b200.distributed import FlatGradients
+    from msgat_b200.optim import FlatAdam
     shape = synthetic.PEMS_SHAPES["pemsd8"]
     torch.manual_seed(seed)
     adj = synthetic.make_adjacency("pemsd8")
     model = models.msgat72(n_components=shape["M"], in_channels=shape["C"], in_timesteps=12, out_timesteps=12, use_te=True,
                            adj=adj.clone()).cuda()
     fg = FlatGradients(model)
-    opt = torch.optim.Adam(fg.params, lr=1e-3, weight_decay=5e-4, fused=True, capturable=True)
+    opt = FlatAdam(fg, lr=1e-3, weight_decay=5e-4)
     b = synthetic.make_batch(3, shape["M"], shape["C"], shape["N"], seed=7)
     return model, fg, opt, [t.cuda() for t in (b.X, b.H, b.D, b.Y)]
 
 
 def test_graphed_step_matches_eager_steps():
     from msgat_b200.train import GraphedStep
-    from oracle.msgat_oracle import huber
-    loss_fn = lambda o, y: huber(o, y, 50.0)  # noqa: E731
+    from msgat_b200.loss import huber_loss
+    loss_fn = lambda o, y: huber_loss(o, y, 50.0)  # noqa: E731
     m1, fg1, opt1, batch = _setup(0)
     m2, fg2, opt2, _ = _setup(0)
     g = GraphedStep(m1, loss_fn, opt1, fg1, batch, warmup=2)      # 2 warm-up steps + 1 captured (not run)
