@@ -29,6 +29,7 @@ extern "C" {
 #define MSGAT_T 12        /* in_timesteps is always timesteps_per_hour = 12 (main.py:45) */
 #define MSGAT_RANK 10     /* hard-coded rank of Wt1/Wt2 (attention.py:58-59) */
 #define MSGAT_MAX_CONV 4  /* longest TACN chain: msgat96 [1,1,2,2] (msgat.py:229) */
+#define MSGAT_MAX_GROUP 8 /* components (TPCs) one grouped call may carry: `-i 1,2,3,24,168` has 5 (main.py:28) */
 
 /* msgat_meam_desc.flags */
 #define MSGAT_F_LN 1          /* LayerNorm([T]) on the input first          (msgat.py:122) */
@@ -57,8 +58,11 @@ typedef struct msgat_meam_desc {
   int32_t n_conv;       /* TACN: number of dilated causal convs, 0..MSGAT_MAX_CONV */
   int32_t dil[MSGAT_MAX_CONV];
   int32_t precision;    /* MSGAT_PREC_* */
-  int32_t reserved;
+  int32_t M;            /* grouped call: number of same-shaped components (0 or 1 = one operator).  MSGAT.forward
+                           loops over M independent TPCs (msgat.py:203-204); a grouped call runs the same layer
+                           of all of them in one launch per kernel, component m with its own parameters. */
   int64_t x_sb, x_sc;   /* element strides of x over batch and channel */
+  int64_t x_sm;         /* element stride of x over components (grouped call; X[:, m] of [B,M,C,N,12] is x_sm = C*N*12) */
 } msgat_meam_desc;
 
 /* Parameters, named after the reference state_dict. */
@@ -113,15 +117,19 @@ int msgat_adj_fill(const float *adj, int32_t N, const int32_t *row_ptr, const in
                    int32_t *col_idx, float *val, int32_t *csc_row, int32_t *csc_eid, void *stream);
 
 /* Sizes, in floats, of the `saved` buffer (forward -> backward) and of `scratch`
- * (max of forward and backward needs) for this descriptor and adjacency nnz. */
+ * (max of forward and backward needs) for this descriptor and adjacency nnz, PER COMPONENT:
+ * a grouped call (desc.M > 1) takes M times as much of each, component-major. */
 int msgat_meam_sizes(const msgat_meam_desc *d, int32_t nnz, int64_t *saved_floats, int64_t *scratch_floats);
 
-/* Forward of the MEAM-shaped operator: x [B,C,N,12] -> out [B,Oc+Ot+Os,N,12] (contiguous). */
+/* Forward of the MEAM-shaped operator: x [B,C,N,12] -> out [B,Oc+Ot+Os,N,12] (contiguous).
+ * Grouped (desc.M > 1): `p` points to M parameter structs, component m reads x + m * x_sm and writes
+ * out[m] of [M,B,O,N,12]; saved / scratch are M consecutive per-component buffers. */
 int msgat_meam_forward(const msgat_meam_desc *d, const msgat_meam_params *p, const msgat_adj *adj,
                        const float *x, float *out, float *saved, float *scratch, void *stream);
 
 /* Backward: dout [B,O,N,12] contiguous -> dx [B,C,N,12] contiguous and parameter grads.
- * `out` is the forward output (ReLU mask) and may be null when DOUT_MASKED or no RELU. */
+ * `out` is the forward output (ReLU mask) and may be null when DOUT_MASKED or no RELU.
+ * Grouped: dout / out are [M,B,O,N,12], dx is [M,B,C,N,12], `p` and `g` point to M structs. */
 int msgat_meam_backward(const msgat_meam_desc *d, const msgat_meam_params *p, const msgat_adj *adj,
                         const float *x, const float *out, const float *dout, const float *saved,
                         float *scratch, float *dx, const msgat_meam_grads *g, void *stream);

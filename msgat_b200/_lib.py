@@ -16,6 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(HERE, "csrc", "libmsgat_sm100.so")
 
 MAX_CONV = 4
+MAX_GROUP = 8
 F_LN, F_RES, F_RELU, F_CMIX, F_SMIX, F_DOUT_MASKED, F_X_IS_RELU = 1, 2, 4, 8, 16, 32, 64
 PREC_FP32, PREC_TF32 = 0, 1
 
@@ -26,8 +27,8 @@ class MeamDesc(C.Structure):
     _fields_ = [("B", C.c_int32), ("C", C.c_int32), ("N", C.c_int32),
                 ("Oc", C.c_int32), ("Ot", C.c_int32), ("Os", C.c_int32),
                 ("flags", C.c_int32), ("n_conv", C.c_int32), ("dil", C.c_int32 * MAX_CONV),
-                ("precision", C.c_int32), ("reserved", C.c_int32),
-                ("x_sb", C.c_int64), ("x_sc", C.c_int64)]
+                ("precision", C.c_int32), ("M", C.c_int32),
+                ("x_sb", C.c_int64), ("x_sc", C.c_int64), ("x_sm", C.c_int64)]
 
 
 _PARAM_FIELDS = ["ln_w", "ln_b", "res_w", "res_b", "ca_Wc", "ca_alpha", "ca_w", "ca_b",

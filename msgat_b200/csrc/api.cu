@@ -213,12 +213,21 @@ int msgat_meam_sizes(const msgat_meam_desc* d, int32_t nnz, int64_t* saved_float
   return 0;
 }
 
+// floats between the scratch buffers of consecutive components: what msgat_meam_sizes reported
+static int set_scratch_stride(Plan& p) {
+  const int64_t bs = meam_backward_scratch(p);
+  if (bs < 0) { msgat_set_error("unsupported MEAM descriptor for backward (code %lld)", (long long)bs); return (int)bs; }
+  p.scratch_sm = p.fwd_scratch > bs ? p.fwd_scratch : bs;
+  return 0;
+}
+
 int msgat_meam_forward(const msgat_meam_desc* d, const msgat_meam_params* prm, const msgat_adj* adj, const float* x,
                        float* out, float* saved, float* scratch, void* stream) {
   Plan p;
   int rc = make_plan(d, adj ? adj->nnz : 0, &p);
   if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
   if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  if ((rc = set_scratch_stride(p))) return rc;
   msgat_prof_tag("@C%dO%d", p.C, p.O);
   rc = meam_forward_impl(p, prm, adj, x, out, saved, scratch, stream);
   if (rc) return rc;
@@ -232,6 +241,7 @@ int msgat_meam_backward(const msgat_meam_desc* d, const msgat_meam_params* prm, 
   int rc = make_plan(d, adj ? adj->nnz : 0, &p);
   if (rc) { msgat_set_error("unsupported MEAM descriptor (code %d)", rc); return rc; }
   if (p.Os && !adj) { msgat_set_error("spatial branch needs an adjacency"); return -20; }
+  if ((rc = set_scratch_stride(p))) return rc;
   msgat_prof_tag("@C%dO%d", p.C, p.O);
   rc = meam_backward_impl(p, prm, adj, x, out, dout, saved, scratch, dx, g, stream);
   if (rc) return rc;

@@ -104,6 +104,18 @@ MSGAT_DEV float exp_neg(float x) {
 }
 #endif
 
+// 1 / sqrt(v) of the LayerNorm rows to ~1 ulp: MUFU.RSQ (2 ulp, a relative error that is COMMON to the 12 values of a
+// row and to its whole gradient, so it does not average out in the cancelling sums behind bias / LayerNorm-affine
+// gradients) followed by one Newton step.  The reference's ATen LayerNorm divides by a correctly rounded sqrt.
+#ifdef MSGAT_EMU
+MSGAT_DEV float rsqrt_ln(float v) { return 1.0f / sqrtf(v); }
+#else
+MSGAT_DEV float rsqrt_ln(float v) {
+  const float y = rsqrtf(v);
+  return y * fmaf(-0.5f * v * y, y, 1.5f);
+}
+#endif
+
 // two fp32 FMAs in one instruction (FFMA2, sm_100): halves the issue slots of the FMA-dense inner loops
 #ifdef MSGAT_EMU
 MSGAT_DEV float2 ffma2(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }

@@ -230,7 +230,7 @@ MSGAT_DEV void row_normalise(const Row12& x, float (&xh)[12], float& rs_out) {
   a.x -= mu; a.y -= mu; a.z -= mu; a.w -= mu; b.x -= mu; b.y -= mu; b.z -= mu; b.w -= mu;
   d.x -= mu; d.y -= mu; d.z -= mu; d.w -= mu;
   const float var = (dot4(a, a) + dot4(b, b) + dot4(d, d)) * (1.0f / 12.0f);
-  const float rs = rsqrtf(var + LN_EPS);
+  const float rs = rsqrt_ln(var + LN_EPS);
   xh[0] = a.x * rs; xh[1] = a.y * rs; xh[2] = a.z * rs; xh[3] = a.w * rs;
   xh[4] = b.x * rs; xh[5] = b.y * rs; xh[6] = b.z * rs; xh[7] = b.w * rs;
   xh[8] = d.x * rs; xh[9] = d.y * rs; xh[10] = d.z * rs; xh[11] = d.w * rs;
@@ -544,15 +544,17 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   const int nparts = nblk * d->B;
   auto add = [&](float* dst, const float* src, int n) {
     if (!dst) return;
-    r.j[nj] = RJob{dst, src, n, nparts, 1, 0, (int64_t)a.pstride, 0};
+    RJob jb = {};
+    jb.dst[0] = dst; jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = 1; jb.doff = 0; jb.pstride = (int64_t)a.pstride; jb.f64 = 0;
+    r.j[nj] = jb;
     r.starts[nj] = tot; tot += n; ++nj;
   };
   add(d_fc_w, scratch, nW);
   add(d_fc_b, scratch + nW, d->Tout);
   add(d_ln_w, scratch + nW + d->Tout, 12);
   add(d_ln_b, scratch + nW + d->Tout + 12, 12);
-  r.starts[nj] = tot; r.njobs = nj;
-  if (tot > 0) LAUNCH_REDUCE(tot, stream, r);
+  r.starts[nj] = tot; r.njobs = nj; r.sc_sm = 0;
+  if (tot > 0) LAUNCH_REDUCE(tot, 1, stream, r);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { msgat_set_error("head_backward: %s", cudaGetErrorString(e)); return -100; }
   return 0;

@@ -24,6 +24,17 @@ static inline int tc_ctas_per_sample(int B, int ntile, int waves, const char* en
   if (J > ntile) J = ntile;
   return J < 1 ? 1 : J;
 }
+// first-layer streaming kernels, meam_l1.cu (C = 1..4, full MEAM, two convs), natively grouped
+bool l1_fwd_supported(const Plan& p);
+int launch_l1_fwd(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
+                  float* saved, void* stream);
+bool l1_bwd_supported(const Plan& p);
+int l1_bwd_blocks_per_sample(const Plan& p);
+int l1_bwd_qsz(const Plan& p);
+int launch_l1_bwd(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G, int64_t g_sm,
+                  const float* saved, float* DH, float* DXR, float* DA, float* delta, float* dSnz, float* dMc_part,
+                  float* dPt_part, float* Qpart, void* stream);
+int launch_l1_wfin(const Plan& p, const msgat_meam_params* prm, const msgat_meam_grads* g, const float* Qpart, int nparts, void* stream);
 // tensor-core (tcgen05 kind::tf32) kernels, tc_*.cu: MSGAT_PREC_TF32 on the layer-2 MEAM shape
 bool tc_apply_supported(const Plan& p);
 bool tc_apply3_supported(const Plan& p);

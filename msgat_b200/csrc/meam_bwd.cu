@@ -519,10 +519,12 @@ MSGAT_KERNEL MSGAT_LB((RBT == 2 ? 512 : 384), 1) k_bwd_main(BwdArgs a) {
 //   dU[n,:] = sum_e dSnz[e] q[i_e,:] - delta[n] E[n,:]
 //   dq[n,:] = dq_dense[n,:] + sum_{k in col n} dSnz[eid_k] U[row_k,:] + dU[n,:] Wg^T
 //   dWg    += q[n,:]^T dU[n,:]
-struct SFinArgs {
+struct SFinArgs {   // grouped: blockIdx.z = component (saved buffers sv_sm apart, scratch buffers sc_sm apart)
   int N, nnz;
-  const float *qs, *Wg, *delta, *dSnz, *dq_dense;
-  const double* E;
+  int64_t sv_sm, sc_sm;
+  const float* Wg[MSGAT_MAX_GROUP];
+  const float *qs, *delta, *dSnz, *dq_dense;
+  const float* E;   // (as doubles)
   const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
   float *dqs, *Wg_part;
 };
@@ -532,9 +534,12 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
   float* WG = reinterpret_cast<float*>(smem_raw);  // [144]
   float* QD = WG + 144;                            // [128][24]: q, dU of every node of the block
   const int b = blockIdx.y, n = blockIdx.x * blockDim.x + threadIdx.x;
-  const float* qb = a.qs + (int64_t)b * a.N * 12;
-  const float* ds = a.dSnz + (int64_t)b * a.nnz;
-  for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = a.Wg[i];
+  const int64_t mo = (int64_t)blockIdx.z * a.sv_sm, so = (int64_t)blockIdx.z * a.sc_sm;
+  const float* qb = a.qs + mo + (int64_t)b * a.N * 12;
+  const float* ds = a.dSnz + so + (int64_t)b * a.nnz;
+  const double* Eb = reinterpret_cast<const double*>(a.E + mo);
+  const float* Wgm = a.Wg[blockIdx.z];
+  for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = Wgm[i];
   __syncthreads();
   float q[12], dq[12];
   double dU[12];  // sum_e dSnz q_i and delta E nearly cancel
@@ -542,9 +547,9 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
   for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.0; dq[t] = 0.f; }
   if (n < a.N) {
     const int64_t g = (int64_t)b * a.N + n;
-    const double dl = (double)a.delta[g];
+    const double dl = (double)a.delta[so + g];
     MSGAT_UNROLL
-    for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * a.E[g * 12 + t]; dq[t] = a.dq_dense[g * 12 + t]; }
+    for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * Eb[g * 12 + t]; dq[t] = a.dq_dense[so + g * 12 + t]; }
     for (int e = a.row_ptr[n]; e < a.row_ptr[n + 1]; ++e) {
       const double w = (double)ds[e];
       const float* qi = qb + (int64_t)a.col_idx[e] * 12;
@@ -567,7 +572,7 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
       double s = 0.0;
       MSGAT_UNROLL
       for (int t2 = 0; t2 < 12; ++t2) s = fma(dU[t2], (double)WG[t * 12 + t2], s);
-      a.dqs[g * 12 + t] = (float)((double)dq[t] + s);
+      a.dqs[so + g * 12 + t] = (float)((double)dq[t] + s);
     }
   }
   MSGAT_UNROLL
@@ -577,21 +582,37 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
     const int t = i / 12, t2 = i - t * 12;
     float s = 0.f;
     for (int k = 0; k < (int)blockDim.x; ++k) s = fmaf(QD[k * 24 + t], QD[k * 24 + 12 + t2], s);
-    a.Wg_part[((int64_t)b * gridDim.x + blockIdx.x) * 144 + i] = s;
+    a.Wg_part[so + ((int64_t)b * gridDim.x + blockIdx.x) * 144 + i] = s;
   }
 }
 
 // ---------------------------------------------------------------------------------------
-struct BSmallArgs {
+struct BSmallArgs {   // grouped: blockIdx.y = component
   int C, Oc, Ot, cmix, J, Jm;
-  const float *dMc_part, *Pc, *qc, *Wc, *ca_w, *Pt, *K;
-  const double* dPt_part;
+  int64_t sv_sm, sc_sm;
+  const float* Wc[MSGAT_MAX_GROUP];
+  const float* ca_w[MSGAT_MAX_GROUP];
+  const float *dMc_part, *Pc, *qc, *Pt, *K;
+  const float* dPt_part;   // (as doubles)
   float *caw_part, *Wc_part, *dqc, *dK;
 };
 
 MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.x, T = blockDim.x, tid = threadIdx.x;
+  const int64_t mo = (int64_t)blockIdx.y * a.sv_sm, so = (int64_t)blockIdx.y * a.sc_sm;
+  const float* const Wc_m = a.Wc[blockIdx.y];
+  const float* const caw_m = a.ca_w[blockIdx.y];
+  const float* const g_qc = a.qc + mo;
+  const float* const g_Pc = a.Pc + mo;
+  const float* const g_Pt = a.Pt + mo;
+  const float* const g_K = a.K + mo;
+  const float* const g_dMc = a.dMc_part + so;
+  const double* const g_dPt = reinterpret_cast<const double*>(a.dPt_part + so);
+  float* const o_caw = a.caw_part + so;
+  float* const o_Wc = a.Wc_part + so;
+  float* const o_dqc = a.dqc + so;
+  float* const o_dK = a.dK + so;
   float* sp = reinterpret_cast<float*>(smem_raw);
   float* qc = sp; sp += C * 12;
   float* A1 = sp; sp += C * 12;
@@ -602,11 +623,11 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
   float* dMc = sp; sp += a.Oc * C;
   float* TP = sp; sp += 144 * 2 + 240;  // Pt, dSt, K
   if (a.Oc) {
-    for (int i = tid; i < C * 12; i += T) qc[i] = a.qc[(int64_t)b * C * 12 + i];
-    for (int i = tid; i < C * C; i += T) Pc[i] = a.Pc[(int64_t)b * C * C + i];
+    for (int i = tid; i < C * 12; i += T) qc[i] = g_qc[(int64_t)b * C * 12 + i];
+    for (int i = tid; i < C * C; i += T) Pc[i] = g_Pc[(int64_t)b * C * C + i];
     for (int i = tid; i < a.Oc * C; i += T) {
       double s = 0.0;
-      for (int j = 0; j < a.Jm; ++j) s += a.dMc_part[((int64_t)b * a.Jm + j) * a.Oc * C + i];
+      for (int j = 0; j < a.Jm; ++j) s += g_dMc[((int64_t)b * a.Jm + j) * a.Oc * C + i];
       dMc[i] = s;
     }
     __syncthreads();
@@ -615,12 +636,12 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
         const int o = i / C, c = i - o * C;
         double s = 0.0;
         for (int k = 0; k < C; ++k) s += (double)(dMc[o * C + k]) * (double)(Pc[c * C + k]);
-        a.caw_part[(int64_t)b * a.Oc * C + i] = s;
+        o_caw[(int64_t)b * a.Oc * C + i] = s;
       }
       for (int i = tid; i < C * C; i += T) {
         const int c = i / C, k = i - c * C;
         double s = 0.0;
-        for (int o = 0; o < a.Oc; ++o) s += (double)(__ldg(a.ca_w + o * C + c)) * (double)(dMc[o * C + k]);
+        for (int o = 0; o < a.Oc; ++o) s += (double)(__ldg(caw_m + o * C + c)) * (double)(dMc[o * C + k]);
         dS[i] = s;
       }
     } else {
@@ -637,8 +658,8 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
       double s1 = 0.0, s2 = 0.0;
       MSGAT_UNROLL
       for (int u = 0; u < 12; ++u) {
-        s1 += (double)(__ldg(a.Wc + t * 12 + u)) * (double)(qc[c * 12 + u]);   // (qc Wc^T)[c][t]
-        s2 += (double)(qc[c * 12 + u]) * (double)(__ldg(a.Wc + u * 12 + t));   // (qc Wc)[c][t]
+        s1 += (double)(__ldg(Wc_m + t * 12 + u)) * (double)(qc[c * 12 + u]);   // (qc Wc^T)[c][t]
+        s2 += (double)(qc[c * 12 + u]) * (double)(__ldg(Wc_m + u * 12 + t));   // (qc Wc)[c][t]
       }
       A1[i] = s1; A2[i] = s2;
     }
@@ -651,7 +672,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
         s += (double)(dS[k * C + c]) * (double)(A2[k * 12 + t]);
         s3 += (double)(dS[c * C + k]) * (double)(qc[k * 12 + t]);
       }
-      a.dqc[(int64_t)b * C * 12 + i] = s;
+      o_dqc[(int64_t)b * C * 12 + i] = s;
       T2[i] = s3;
     }
     __syncthreads();
@@ -659,19 +680,19 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
       const int t = i / 12, u = i - t * 12;
       double s = 0.0;
       for (int c = 0; c < C; ++c) s += (double)(qc[c * 12 + t]) * (double)(T2[c * 12 + u]);
-      a.Wc_part[(int64_t)b * 144 + i] = s;
+      o_Wc[(int64_t)b * 144 + i] = s;
     }
   }
   if (a.Ot) {
     float *Pt = TP, *dSt = TP + 144, *K = TP + 288;
     __syncthreads();
     for (int i = tid; i < 144; i += T) {
-      Pt[i] = a.Pt[(int64_t)b * 144 + i];
+      Pt[i] = g_Pt[(int64_t)b * 144 + i];
       double s = 0.0;
-      for (int j = 0; j < a.J; ++j) s += a.dPt_part[((int64_t)b * a.J + j) * 144 + i];
+      for (int j = 0; j < a.J; ++j) s += g_dPt[((int64_t)b * a.J + j) * 144 + i];
       dSt[i] = s;
     }
-    for (int i = tid; i < 240; i += T) K[i] = a.K[(int64_t)b * 240 + i];
+    for (int i = tid; i < 240; i += T) K[i] = g_K[(int64_t)b * 240 + i];
     __syncthreads();
     if (tid < 12) {
       double s = 0.0;
@@ -686,14 +707,26 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
       double s = 0.0;
       if (r < 10) { for (int k = 0; k < 12; ++k) s += (double)(dSt[t * 12 + k]) * (double)(K[k * 20 + 10 + r]); }   // dK1 = dS K2
       else { for (int k = 0; k < 12; ++k) s += (double)(dSt[k * 12 + t]) * (double)(K[k * 20 + r - 10]); }         // dK2 = dS^T K1
-      a.dK[(int64_t)b * 240 + i] = s;
+      o_dK[(int64_t)b * 240 + i] = s;
     }
   }
 }
 
 // dWt1[r][n] = sum_{b,t} dK1[b,t,r] q_t[b,n,t]   (attention.py:65)
-MSGAT_KERNEL k_dwt(const float* dK, const float* qt, int B, int N, float* dWt1, float* dWt2) {
+struct DwtArgs {   // grouped: blockIdx.y = component
+  const float *dK, *qt;
+  int64_t sv_sm, sc_sm;
+  int B, N;
+  float* dWt1[MSGAT_MAX_GROUP];
+  float* dWt2[MSGAT_MAX_GROUP];
+};
+MSGAT_KERNEL k_dwt(DwtArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int B = a.B, N = a.N;
+  const float* dK = a.dK + (int64_t)blockIdx.y * a.sc_sm;
+  const float* qt = a.qt + (int64_t)blockIdx.y * a.sv_sm;
+  float* dWt1 = a.dWt1[blockIdx.y];
+  float* dWt2 = a.dWt2[blockIdx.y];
   if (i >= N * 20) return;
   const int n = i / 20, r = i - n * 20;
   float s = 0.f;
@@ -708,12 +741,20 @@ MSGAT_KERNEL k_dwt(const float* dK, const float* qt, int B, int N, float* dWt1, 
 // second pass: dh2[c,n,t] = alpha_n[n] dqc[b,c,t] + alpha_t[c] dqt[b,t,n] + alpha_s[c] dqs[b,n,t]
 // (the gradients of the three query reductions, attention.py:92,63,33), through the
 // LayerNorm backward, added to dx; gradients of the three alphas.
-struct FixArgs {
-  const float* x; int64_t x_sb, x_sc;
+struct FixArgs {   // grouped: blockIdx.z = component (x: x_sm, dx: dx_sm, scratch: sc_sm apart)
+  const float* x; int64_t x_sb, x_sc, x_sm, dx_sm, sc_sm;
   int C, N, Oc, Ot, Os, flags, ntile, J;
-  const float *ln_w, *ln_b, *ca_alpha, *ta_alpha, *sa_alpha, *Wt1, *Wt2, *dqc, *dK, *dqs;
+  msgat_meam_params prm[MSGAT_MAX_GROUP];
+  const float *dqc, *dK, *dqs;
   float *dx, *pa_n, *ln_part;
-  double *pa_t, *pa_s;
+  float *pa_t, *pa_s;   // (as doubles)
+  // First-layer mode (meam_l1.cu): the main pass left the pre-LayerNorm gradient DH, the residual gradient DXR and
+  // d(aggregated h) DA in scratch ([B,C,N,12] each) instead of a partial dx; this kernel adds the transposed sparse
+  // aggregation sum_n A[n,i] DA[n] (CSC view) and the alpha terms, runs the LayerNorm backward ONCE and writes dx.
+  const float *DH, *DXR, *DA, *pw;
+  const int32_t *csc_ptr, *csc_row, *csc_eid;
+  int nnz;
+  int64_t sv_sm;
 };
 
 template <int NT>
@@ -722,6 +763,17 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
   const bool do_ln = a.flags & MSGAT_F_LN;
+  const msgat_meam_params& PM = a.prm[blockIdx.z];
+  const int64_t so = (int64_t)blockIdx.z * a.sc_sm;
+  const float* const xm = a.x + (int64_t)blockIdx.z * a.x_sm;
+  float* const dxm = a.dx + (int64_t)blockIdx.z * a.dx_sm;
+  const float* const g_dqc = a.dqc + so;
+  const float* const g_dK = a.dK + so;
+  const float* const g_dqs = a.dqs + so;
+  const float* const g_DH = a.DH ? a.DH + so : nullptr;
+  const float* const g_DXR = a.DH ? a.DXR + so : nullptr;
+  const float* const g_DA = a.DH ? a.DA + so : nullptr;
+  const float* const g_pw = a.DH ? a.pw + (int64_t)blockIdx.z * a.sv_sm + (int64_t)b * a.nnz : nullptr;
   float* sp = reinterpret_cast<float*>(smem_raw);
   float* DQC = sp; sp += C * 12;
   float* DQT = sp; sp += P;
@@ -732,9 +784,9 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   float* DK = sp; sp += 240;
   float* LW = sp; sp += 24;
   float* RED = sp;  // [T/32][24]
-  if (a.Oc) for (int i = tid; i < C * 12; i += T) DQC[i] = a.dqc[(int64_t)b * C * 12 + i];
-  if (a.Ot) for (int i = tid; i < 240; i += T) DK[i] = a.dK[(int64_t)b * 240 + i];
-  if (tid < 12) { LW[tid] = do_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? a.ln_b[tid] : 0.f; }
+  if (a.Oc) for (int i = tid; i < C * 12; i += T) DQC[i] = g_dqc[(int64_t)b * C * 12 + i];
+  if (a.Ot) for (int i = tid; i < 240; i += T) DK[i] = g_dK[(int64_t)b * 240 + i];
+  if (tid < 12) { LW[tid] = do_ln ? PM.ln_w[tid] : 1.f; LW[12 + tid] = do_ln ? PM.ln_b[tid] : 0.f; }
   double at_acc = 0.0, as_acc = 0.0;
   float lnw_acc[12], lnb_acc[12];
   MSGAT_UNROLL
@@ -748,10 +800,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
       if (n < a.N) {
         if (a.Ot)
           for (int r = 0; r < 10; ++r) {
-            s = fmaf(DK[t * 20 + r], __ldg(a.Wt1 + (int64_t)r * a.N + n), s);
-            s = fmaf(DK[t * 20 + 10 + r], __ldg(a.Wt2 + (int64_t)r * a.N + n), s);
+            s = fmaf(DK[t * 20 + r], __ldg(PM.ta_Wt1 + (int64_t)r * a.N + n), s);
+            s = fmaf(DK[t * 20 + 10 + r], __ldg(PM.ta_Wt2 + (int64_t)r * a.N + n), s);
           }
-        if (a.Os) q = a.dqs[((int64_t)b * a.N + n) * 12 + t];
+        if (a.Os) q = g_dqs[((int64_t)b * a.N + n) * 12 + t];
       }
       DQT[p] = s; DQS[p] = q;
     }
@@ -760,7 +812,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
       const int c = r / NT, nl = r - c * NT, n = n0 + nl;
       double v1 = 0.0, v2 = 0.0, v3 = 0.0;
       if (n < a.N) {
-        const float* src = a.x + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
+        const float* src = xm + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
         float xv[12], xh[12], h[12], dh[12];
         float4 u = ld4(src), v = ld4(src + 4), w = ld4(src + 8);
         xv[0] = u.x; xv[1] = u.y; xv[2] = u.z; xv[3] = u.w; xv[4] = v.x; xv[5] = v.y; xv[6] = v.z; xv[7] = v.w;
@@ -773,21 +825,34 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
           float var = 0.f;
           MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { const float d = xv[t] - mu; var = fmaf(d, d, var); }
-          rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
+          rs = rsqrt_ln(var * (1.0f / 12.0f) + LN_EPS);
           MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { xh[t] = (xv[t] - mu) * rs; h[t] = xh[t] * LW[t] + LW[12 + t]; }
         } else {
           MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) { xh[t] = 0.f; h[t] = xv[t]; }
         }
-        const float an = a.Oc ? __ldg(a.ca_alpha + n) : 0.f;
-        const float att = a.Ot ? __ldg(a.ta_alpha + c) : 0.f;
-        const float as = a.Os ? __ldg(a.sa_alpha + c) : 0.f;
+        const float an = a.Oc ? __ldg(PM.ca_alpha + n) : 0.f;
+        const float att = a.Ot ? __ldg(PM.ta_alpha + c) : 0.f;
+        const float as = a.Os ? __ldg(PM.sa_alpha + c) : 0.f;
         MSGAT_UNROLL
         for (int t = 0; t < 12; ++t) {
           const float dqc = a.Oc ? DQC[c * 12 + t] : 0.f, dqt = DQT[nl * 12 + t], dqs = DQS[nl * 12 + t];
           dh[t] = an * dqc + att * dqt + as * dqs;
           v1 += (double)dqc * h[t]; v2 += (double)dqt * h[t]; v3 += (double)dqs * h[t];
+        }
+        const int64_t rowo = (((int64_t)b * C + c) * a.N + n) * 12;
+        if (g_DH) {
+          const float4 p0 = ld4(g_DH + rowo), p1 = ld4(g_DH + rowo + 4), p2 = ld4(g_DH + rowo + 8);
+          float4 s0 = p0, s1 = p1, s2 = p2;
+          const int k1 = a.csc_ptr[n + 1];
+          for (int k = a.csc_ptr[n]; k < k1; ++k) {   // dh[c,i] += sum_n A[n,i] DA[c,n]   (attention.py:36 transposed)
+            const float w = g_pw[a.csc_eid[k]];
+            const float* dr = g_DA + (((int64_t)b * C + c) * a.N + a.csc_row[k]) * 12;
+            fma4(s0, w, ld4(dr)); fma4(s1, w, ld4(dr + 4)); fma4(s2, w, ld4(dr + 8));
+          }
+          dh[0] += s0.x; dh[1] += s0.y; dh[2] += s0.z; dh[3] += s0.w; dh[4] += s1.x; dh[5] += s1.y; dh[6] += s1.z; dh[7] += s1.w;
+          dh[8] += s2.x; dh[9] += s2.y; dh[10] += s2.z; dh[11] += s2.w;
         }
         float out[12];
         if (do_ln) {
@@ -809,8 +874,18 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         if (a.flags & MSGAT_F_X_IS_RELU)
           MSGAT_UNROLL
           for (int t = 0; t < 12; ++t) out[t] = xv[t] > 0.f ? out[t] : 0.f;
-        float* d = a.dx + (((int64_t)b * C + c) * a.N + n) * 12;
-        float4 d0 = ld4(d), d1 = ld4(d + 4), d2 = ld4(d + 8);
+        float* d = dxm + (((int64_t)b * C + c) * a.N + n) * 12;
+        float4 d0, d1, d2;
+        if (g_DH) {   // first-layer mode: dx = LN^T(dh) + Wres^T G, written once (the residual is not behind the ReLU of x)
+          d0 = ld4(g_DXR + rowo); d1 = ld4(g_DXR + rowo + 4); d2 = ld4(g_DXR + rowo + 8);
+          if (a.flags & MSGAT_F_X_IS_RELU) {
+            d0.x = xv[0] > 0.f ? d0.x : 0.f; d0.y = xv[1] > 0.f ? d0.y : 0.f; d0.z = xv[2] > 0.f ? d0.z : 0.f; d0.w = xv[3] > 0.f ? d0.w : 0.f;
+            d1.x = xv[4] > 0.f ? d1.x : 0.f; d1.y = xv[5] > 0.f ? d1.y : 0.f; d1.z = xv[6] > 0.f ? d1.z : 0.f; d1.w = xv[7] > 0.f ? d1.w : 0.f;
+            d2.x = xv[8] > 0.f ? d2.x : 0.f; d2.y = xv[9] > 0.f ? d2.y : 0.f; d2.z = xv[10] > 0.f ? d2.z : 0.f; d2.w = xv[11] > 0.f ? d2.w : 0.f;
+          }
+        } else {
+          d0 = ld4(d); d1 = ld4(d + 4); d2 = ld4(d + 8);
+        }
         d0.x += out[0]; d0.y += out[1]; d0.z += out[2]; d0.w += out[3];
         d1.x += out[4]; d1.y += out[5]; d1.z += out[6]; d1.w += out[7];
         d2.x += out[8]; d2.y += out[9]; d2.z += out[10]; d2.w += out[11];
@@ -823,7 +898,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
       if (n0 + nl < a.N) {
         float s = 0.f;
         for (int c = 0; c < C; ++c) s += V1[c * NT + nl];
-        a.pa_n[(int64_t)b * a.N + n0 + nl] = s;
+        a.pa_n[so + (int64_t)b * a.N + n0 + nl] = s;
       }
     }
     for (int c = tid; c < C; c += T) {  // a thread owns channel c for the whole kernel (needs T >= C)
@@ -833,7 +908,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
     }
   }
   const int blk = b * a.J + blockIdx.x;
-  if (tid < C) { a.pa_t[(int64_t)blk * C + tid] = at_acc; a.pa_s[(int64_t)blk * C + tid] = as_acc; }
+  if (tid < C) {
+    reinterpret_cast<double*>(a.pa_t + so)[(int64_t)blk * C + tid] = at_acc;
+    reinterpret_cast<double*>(a.pa_s + so)[(int64_t)blk * C + tid] = as_acc;
+  }
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31, nwarp = T >> 5;
   MSGAT_UNROLL
@@ -845,7 +923,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
   if (tid < 24) {
     float s = 0.f;
     for (int w = 0; w < nwarp; ++w) s += RED[w * 24 + tid];
-    a.ln_part[(int64_t)blk * 24 + tid] = s;
+    a.ln_part[so + (int64_t)blk * 24 + tid] = s;
   }
 }
 
@@ -858,7 +936,8 @@ struct BwdLayout {
   int64_t WGT;  // floats of weight-gradient partial per thread block
   int64_t off_job[NJOBS];
   int64_t o_G, o_wg, o_bias, o_ln, o_dMc, o_dPt, o_delta, o_dSnz, o_dqd, o_dqs, o_dK, o_dqc, o_caw, o_Wc, o_Wg,
-      o_pat, o_pas, o_pan, o_tcA, total;
+      o_pat, o_pas, o_pan, o_tcA, o_l1, o_q, total;
+  int l1;   // first-layer kernels (meam_l1.cu) serve this shape
   WJob jobs[NJOBS];
 };
 
@@ -928,6 +1007,8 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
 #ifndef MSGAT_EMU
   if (tc_dgrad_supported(p)) L.J = tc_dgrad_blocks_per_sample(p);   // the tensor-core data-gradient kernel writes the per-block partials
 #endif
+  L.l1 = l1_bwd_supported(p) ? 1 : 0;
+  if (L.l1) { L.J = l1_bwd_blocks_per_sample(p); L.S = 1; }
   L.nblk = L.J * p.B;
   L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
   L.J4 = pick_J(p.B, L.ntile4, msgat_sm_count() * 4); L.nblk4 = L.J4 * p.B;
@@ -959,8 +1040,10 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   L.o_pan = o; o += rup4l(BN);
   L.o_tcA = o;
 #ifndef MSGAT_EMU
-  if (tc_wgrad_supported(p)) o += rup4l(BN * 12 * 3 * p.Ot);
+  if (tc_wgrad_supported(p) && !L.l1) o += rup4l(BN * 12 * 3 * p.Ot);
 #endif
+  L.o_l1 = o; if (L.l1) o += 3 * rup4l(BN * 12 * p.C);                       // DH | DXR | DA
+  L.o_q = o; if (L.l1) o += rup4l((int64_t)L.nblk * l1_bwd_qsz(p));          // feature-correlation partials
   L.total = o;
   return 0;
 }
@@ -972,12 +1055,127 @@ int64_t meam_backward_scratch(Plan& p) {
   return L.total;
 }
 
+// The per-sample and reduction kernels behind the main passes, each ONE launch for all components of a grouped call.
+static int meam_backward_tail(Plan& p, BwdLayout& L, int Jw, const msgat_meam_params* prm, const msgat_adj* adj, const float* x,
+                              const float* saved, float* scratch, float* dx, const msgat_meam_grads* g, void* stream) {
+  const int M = p.M;
+  const int64_t sv_sm = p.saved_total, sc_sm = p.scratch_sm, dx_sm = (int64_t)p.B * p.C * p.N * 12;
+  if (p.Os) {
+    launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
+    SFinArgs a;
+    a.N = p.N; a.nnz = p.nnz; a.sv_sm = sv_sm; a.sc_sm = sc_sm; a.qs = saved + p.o_qs; a.E = saved + p.o_E;
+    for (int m = 0; m < M; ++m) a.Wg[m] = prm[m].sa_Wg;
+    a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dq_dense = scratch + L.o_dqd;
+    a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+    a.dqs = scratch + L.o_dqs; a.Wg_part = scratch + L.o_Wg;
+    MSGAT_LAUNCH(k_sfin, dim3(L.nfin, p.B, M), dim3(128), (144 + 128 * 24) * 4, stream, a);
+  }
+  if (p.Oc || p.Ot) {
+    BSmallArgs a;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = Jw;
+    a.sv_sm = sv_sm; a.sc_sm = sc_sm;
+    a.dMc_part = scratch + L.o_dMc; a.dPt_part = scratch + L.o_dPt; a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
+    for (int m = 0; m < M; ++m) { a.Wc[m] = prm[m].ca_Wc; a.ca_w[m] = prm[m].ca_w; }
+    a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
+    a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
+    size_t smem = ((size_t)p.C * 48 + 2 * (size_t)p.C * p.C + (size_t)p.Oc * p.C + 528) * 4;
+    const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
+    MSGAT_LAUNCH(k_bwd_small, dim3(p.B, M), dim3(smT), smem, stream, a);
+  }
+  if (p.Ot && (g->ta_Wt1 || g->ta_Wt2)) {
+    DwtArgs a;
+    a.dK = scratch + L.o_dK; a.qt = saved + p.o_qt; a.sv_sm = sv_sm; a.sc_sm = sc_sm; a.B = p.B; a.N = p.N;
+    for (int m = 0; m < M; ++m) { a.dWt1[m] = g[m].ta_Wt1; a.dWt2[m] = g[m].ta_Wt2; }
+    MSGAT_LAUNCH(k_dwt, dim3((p.N * 20 + 255) / 256, M), dim3(256), 0, stream, a);
+  }
+  {
+    FixArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.dx_sm = dx_sm; a.sc_sm = sc_sm;
+    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.flags = p.flags; a.ntile = L.ntile4; a.J = L.J4;
+    for (int m = 0; m < M; ++m) a.prm[m] = prm[m];
+    a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK; a.dqs = scratch + L.o_dqs;
+    a.dx = dx; a.pa_n = scratch + L.o_pan; a.pa_t = scratch + L.o_pat; a.pa_s = scratch + L.o_pas;
+    a.DH = a.DXR = a.DA = a.pw = nullptr; a.csc_ptr = a.csc_row = a.csc_eid = nullptr; a.nnz = p.nnz; a.sv_sm = sv_sm;
+    if (L.l1) {
+      const int64_t sz = rup4l((int64_t)p.B * p.N * 12 * p.C);
+      a.DH = scratch + L.o_l1; a.DXR = scratch + L.o_l1 + sz; a.DA = scratch + L.o_l1 + 2 * sz; a.pw = saved + p.o_pw;
+      a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
+    }
+    a.ln_part = scratch + L.o_ln + (int64_t)L.nblk * 24;
+    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 5 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
+    // 128-thread blocks, four per SM (a thread owns channel tid across the tiles: at least C threads): more
+    // independent blocks hide the barriers between the phases of a tile (C = 1: 35 -> 25 us, C = 72: 118 -> 114 us)
+    const int fixT = p.C > 128 ? ((p.C + 31) & ~31) : 128;
+    MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B, M), dim3(fixT), smem, stream, a);
+  }
+  {
+    ReduceArgs r;
+    int nj = 0, tot = 0;
+    r.sc_sm = sc_sm;
+    // `field`: the gradient tensor of component 0 selects the job; every component's own pointer is taken from g[m]
+    auto add = [&](float* msgat_meam_grads::* field, int conv, int which, const float* src, int n, int nparts, int64_t pstride,
+                   int dmul, int doff, int f64 = 0) {
+      auto get = [&](int m) -> float* {
+        if (conv < 0) return g[m].*field;
+        return which ? g[m].conv_b[conv] : g[m].conv_w[conv];
+      };
+      if (!get(0) || n <= 0 || nj >= MAX_RJOBS) return;
+      RJob jb;
+      for (int m = 0; m < MSGAT_MAX_GROUP; ++m) jb.dst[m] = m < M ? get(m) : nullptr;
+      jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = dmul; jb.doff = doff; jb.pstride = pstride; jb.f64 = f64;
+      r.j[nj] = jb;
+      r.starts[nj] = tot; tot += n; ++nj;
+    };
+    typedef msgat_meam_grads GR;
+    const float* wg = scratch + L.o_wg;
+    const float* bp = scratch + L.o_bias;
+    if ((p.flags & MSGAT_F_RES) && !L.l1) {
+      add(&GR::res_w, -1, 0, wg + L.off_job[JOB_RES], p.O * p.C, p.B * Jw, L.WGT, 1, 0);
+      add(&GR::res_b, -1, 0, bp, p.O, L.nblk, L.nbias, 1, 0);
+    }
+    if (p.Os && (p.flags & MSGAT_F_SMIX) && !L.l1) add(&GR::sa_W, -1, 0, wg + L.off_job[JOB_WS], p.Os * p.C, p.B * Jw, L.WGT, 1, 0);
+    for (int i = 0; i < p.n_conv && !L.l1; ++i) {
+      const int K = i == 0 ? p.C : p.Ot;
+      add(nullptr, i, 0, wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, p.B * Jw, L.WGT, 2, 0);
+      add(nullptr, i, 0, wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, p.B * Jw, L.WGT, 2, 1);
+      add(nullptr, i, 1, i + 1 == p.n_conv ? bp + p.Oc : bp + p.O + i * p.Ot, p.Ot, L.nblk, L.nbias, 1, 0);
+    }
+    if (p.flags & MSGAT_F_LN) {
+      // first-layer mode: the LayerNorm backward runs once, in k_bwd_fix, whose partials follow the main pass's slots
+      const float* lp = scratch + L.o_ln + (L.l1 ? (int64_t)L.nblk * 24 : 0);
+      const int np = L.l1 ? L.nblk4 : L.nblk + L.nblk4;
+      add(&GR::ln_w, -1, 0, lp, 12, np, 24, 1, 0);
+      add(&GR::ln_b, -1, 0, lp + 12, 12, np, 24, 1, 0);
+    }
+    if (p.Oc) {
+      if (p.flags & MSGAT_F_CMIX) {
+        add(&GR::ca_w, -1, 0, scratch + L.o_caw, p.Oc * p.C, p.B, (int64_t)p.Oc * p.C, 1, 0);
+        if (!L.l1) add(&GR::ca_b, -1, 0, bp, p.Oc, L.nblk, L.nbias, 1, 0);
+      }
+      add(&GR::ca_Wc, -1, 0, scratch + L.o_Wc, 144, p.B, 144, 1, 0);
+      add(&GR::ca_alpha, -1, 0, scratch + L.o_pan, p.N, p.B, p.N, 1, 0);
+    }
+    if (p.Ot) add(&GR::ta_alpha, -1, 0, scratch + L.o_pat, p.C, L.nblk4, p.C, 1, 0, 1);
+    if (p.Os) {
+      add(&GR::sa_alpha, -1, 0, scratch + L.o_pas, p.C, L.nblk4, p.C, 1, 0, 1);
+      add(&GR::sa_Wg, -1, 0, scratch + L.o_Wg, 144, p.B * L.nfin, 144, 1, 0);
+    }
+    r.starts[nj] = tot; r.njobs = nj;
+    if (tot > 0) LAUNCH_REDUCE(tot, M, stream, r);
+  }
+  if (L.l1) launch_l1_wfin(p, prm, g, scratch + L.o_q, L.nblk, stream);
+  return 0;
+}
+
 int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* out,
                        const float* dout, const float* saved, float* scratch, float* dx, const msgat_meam_grads* g,
                        void* stream) {
   BwdLayout L;
   int rc = bwd_layout(p, L);
   if (rc) { msgat_set_error("MEAM backward: unsupported shape (code %d)", rc); return rc; }
+  const int M = p.M;
+  const int64_t sv_sm = p.saved_total, sc_sm = p.scratch_sm, out_sm = (int64_t)p.B * p.O * p.N * 12,
+                dx_sm = (int64_t)p.B * p.C * p.N * 12;
   const bool need_mask = (p.flags & MSGAT_F_RELU) && !(p.flags & MSGAT_F_DOUT_MASKED);
   bool tc_w = false, tc_d = false;
 #ifndef MSGAT_EMU
@@ -985,138 +1183,87 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
   tc_d = tc_dgrad_supported(p);
 #endif
   const int Jw = tc_w ? tc_wgrad_blocks_per_sample(p) : L.J * L.S;  // weight-gradient partials per sample
-  const float* G = dout;
-  if (need_mask) {
-    if (!out) { msgat_set_error("MEAM backward: forward output needed for the ReLU mask"); return -32; }
-    const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
-    int blocks = (int)((n4 + 255) / 256);
-    if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
-    MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)dout, (const float4*)out,
-                 (float4*)(scratch + L.o_G), n4);
-    G = scratch + L.o_G;
-  }
-#ifndef MSGAT_EMU
-  if (tc_d) {
-    rc = launch_tc_dgrad(p, prm, adj, x, G, saved, scratch + L.o_tcA, dx, scratch + L.o_delta, scratch + L.o_dSnz, scratch + L.o_bias,
-                         L.nbias, scratch + L.o_ln, reinterpret_cast<double*>(scratch + L.o_dPt), stream);
+  if (need_mask && !out) { msgat_set_error("MEAM backward: forward output needed for the ReLU mask"); return -32; }
+  if (L.l1) {   // first layer: one grouped streaming pass (meam_l1.cu), masked gradient from dout or from a masking pre-pass
+    const float* G = dout;
+    int64_t g_sm = out_sm;
+    if (need_mask) {
+      const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
+      int blocks = (int)((n4 + 255) / 256);
+      if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
+      for (int m = 0; m < M; ++m)
+        MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)(dout + m * out_sm),
+                     (const float4*)(out + m * out_sm), (float4*)(scratch + m * sc_sm + L.o_G), n4);
+      G = scratch + L.o_G; g_sm = sc_sm;
+    }
+    const int64_t sz = rup4l((int64_t)p.B * p.N * 12 * p.C);
+    rc = launch_l1_bwd(p, prm, adj, x, G, g_sm, saved, scratch + L.o_l1, scratch + L.o_l1 + sz, scratch + L.o_l1 + 2 * sz,
+                       scratch + L.o_delta, scratch + L.o_dSnz, scratch + L.o_dMc, scratch + L.o_dPt, scratch + L.o_q, stream);
     if (rc) return rc;
+    return meam_backward_tail(p, L, L.J, prm, adj, x, saved, scratch, dx, g, stream);
   }
-#endif
-  if (!tc_d) {
-    BwdArgs a;
-    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
-    a.C = p.C; a.N = p.N; a.O = p.O; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre;
-    a.flags = p.flags; a.n_conv = p.n_conv; a.ntile = p.ntile_b; a.J = L.J; a.nnz = p.nnz;
-    for (int i = 0; i < MSGAT_MAX_CONV; ++i) { a.dil[i] = p.dil[i]; a.conv_w[i] = prm->conv_w[i]; a.conv_b[i] = prm->conv_b[i]; }
-    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.sa_W = prm->sa_W;
-    a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw;
-    a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr;
-    a.csc_ptr = adj ? adj->csc_ptr : nullptr; a.csc_row = adj ? adj->csc_row : nullptr; a.csc_eid = adj ? adj->csc_eid : nullptr;
-    for (int q = 0; q < NJOBS; ++q) {
-      a.jobs[q] = L.jobs[q];
-      if (q == JOB_MC) { a.jobs[q].out = scratch + L.o_dMc; a.jobs[q].blk_stride = (int64_t)p.Oc * p.C; }
-      else { a.jobs[q].out = scratch + L.o_wg + L.off_job[q]; a.jobs[q].blk_stride = L.WGT; }
+  // ---- the passes over the activations: still one launch per component (buffers by pointer offset)
+  for (int m = 0; m < M; ++m) {
+    const float* xm = x + m * p.x_sm;
+    const float* savedm = saved + m * sv_sm;
+    float* scr = scratch + m * sc_sm;
+    float* dxm = dx + m * dx_sm;
+    const msgat_meam_params* prmm = prm + m;
+    const float* G = dout + m * out_sm;
+    if (need_mask) {
+      const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
+      int blocks = (int)((n4 + 255) / 256);
+      if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
+      MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)G, (const float4*)(out + m * out_sm),
+                   (float4*)(scr + L.o_G), n4);
+      G = scr + L.o_G;
     }
-    a.bias_part = scratch + L.o_bias; a.ln_part = scratch + L.o_ln; a.dPt_part = reinterpret_cast<double*>(scratch + L.o_dPt);
-    a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dx = dx;
-    a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
-    size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
-    a.S = L.S;
-    a.skip_wgrad = tc_w ? 1 : 0;
-    a.resident = (tc_w && bwd_resident_floats(p) > 0) ? 1 : 0;
-    a.tcA = tc_w ? scratch + L.o_tcA : nullptr;
-#define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
-    if (L.RBT == 2) {
-      if (L.NT == 16) BWD_CASE(16, 2); else if (L.NT == 8) BWD_CASE(8, 2); else BWD_CASE(4, 2);
-    } else {
-      if (L.NT == 16) BWD_CASE(16, 4); else if (L.NT == 8) BWD_CASE(8, 4); else BWD_CASE(4, 4);
-    }
-#undef BWD_CASE
-  }
 #ifndef MSGAT_EMU
-  if (tc_w) {
-    float* wg = scratch + L.o_wg;
-    launch_tc_wgrad(p, prm, adj, x, G, saved, scratch + L.o_tcA, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
-                    wg + L.off_job[JOB_CONV + 1], wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT,
-                    scratch + L.o_dMc, (int64_t)p.Oc * p.C, stream);
-  }
+    if (tc_d) {
+      rc = launch_tc_dgrad(p, prmm, adj, xm, G, savedm, scr + L.o_tcA, dxm, scr + L.o_delta, scr + L.o_dSnz, scr + L.o_bias,
+                           L.nbias, scr + L.o_ln, reinterpret_cast<double*>(scr + L.o_dPt), stream);
+      if (rc) return rc;
+    }
 #endif
-  if (p.Os) {
-    launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
-    SFinArgs a;
-    a.N = p.N; a.nnz = p.nnz; a.qs = saved + p.o_qs; a.Wg = prm->sa_Wg; a.E = reinterpret_cast<const double*>(saved + p.o_E);
-    a.delta = scratch + L.o_delta; a.dSnz = scratch + L.o_dSnz; a.dq_dense = scratch + L.o_dqd;
-    a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
-    a.dqs = scratch + L.o_dqs; a.Wg_part = scratch + L.o_Wg;
-    MSGAT_LAUNCH(k_sfin, dim3(L.nfin, p.B), dim3(128), (144 + 128 * 24) * 4, stream, a);
-  }
-  if (p.Oc || p.Ot) {
-    BSmallArgs a;
-    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.J = L.J; a.Jm = Jw;
-    a.dMc_part = scratch + L.o_dMc; a.dPt_part = reinterpret_cast<const double*>(scratch + L.o_dPt); a.Pc = saved + p.o_Pc; a.qc = saved + p.o_qc;
-    a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w; a.Pt = saved + p.o_Pt; a.K = saved + p.o_K;
-    a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
-    size_t smem = ((size_t)p.C * 48 + 2 * (size_t)p.C * p.C + (size_t)p.Oc * p.C + 528) * 4;
-    const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
-    MSGAT_LAUNCH(k_bwd_small, dim3(p.B), dim3(smT), smem, stream, a);
-  }
-  if (p.Ot && (g->ta_Wt1 || g->ta_Wt2))
-    MSGAT_LAUNCH(k_dwt, dim3((p.N * 20 + 255) / 256), dim3(256), 0, stream, (const float*)(scratch + L.o_dK),
-                 saved + p.o_qt, p.B, p.N, g->ta_Wt1, g->ta_Wt2);
-  {
-    FixArgs a;
-    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
-    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.flags = p.flags; a.ntile = L.ntile4; a.J = L.J4;
-    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.ca_alpha = prm->ca_alpha; a.ta_alpha = prm->ta_alpha; a.sa_alpha = prm->sa_alpha;
-    a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK; a.dqs = scratch + L.o_dqs;
-    a.dx = dx; a.pa_n = scratch + L.o_pan; a.pa_t = reinterpret_cast<double*>(scratch + L.o_pat); a.pa_s = reinterpret_cast<double*>(scratch + L.o_pas);
-    a.ln_part = scratch + L.o_ln + (int64_t)L.nblk * 24;
-    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 5 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
-    // 128-thread blocks, four per SM (a thread owns channel tid across the tiles: at least C threads): more
-    // independent blocks hide the barriers between the phases of a tile (C = 1: 35 -> 25 us, C = 72: 118 -> 114 us)
-    const int fixT = p.C > 128 ? ((p.C + 31) & ~31) : 128;
-    MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B), dim3(fixT), smem, stream, a);
-  }
-  {
-    ReduceArgs r;
-    int nj = 0, tot = 0;
-    auto add = [&](float* dst, const float* src, int n, int nparts, int64_t pstride, int dmul, int doff, int f64 = 0) {
-      if (!dst || n <= 0 || nj >= MAX_RJOBS) return;
-      r.j[nj] = RJob{dst, src, n, nparts, dmul, doff, pstride, f64};
-      r.starts[nj] = tot; tot += n; ++nj;
-    };
-    const float* wg = scratch + L.o_wg;
-    const float* bp = scratch + L.o_bias;
-    if (p.flags & MSGAT_F_RES) {
-      add(g->res_w, wg + L.off_job[JOB_RES], p.O * p.C, p.B * Jw, L.WGT, 1, 0);
-      add(g->res_b, bp, p.O, L.nblk, L.nbias, 1, 0);
-    }
-    if (p.Os && (p.flags & MSGAT_F_SMIX)) add(g->sa_W, wg + L.off_job[JOB_WS], p.Os * p.C, p.B * Jw, L.WGT, 1, 0);
-    for (int i = 0; i < p.n_conv; ++i) {
-      const int K = i == 0 ? p.C : p.Ot;
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i], p.Ot * K, p.B * Jw, L.WGT, 2, 0);
-      add(g->conv_w[i], wg + L.off_job[JOB_CONV + 2 * i + 1], p.Ot * K, p.B * Jw, L.WGT, 2, 1);
-      add(g->conv_b[i], i + 1 == p.n_conv ? bp + p.Oc : bp + p.O + i * p.Ot, p.Ot, L.nblk, L.nbias, 1, 0);
-    }
-    if (p.flags & MSGAT_F_LN) {
-      add(g->ln_w, scratch + L.o_ln, 12, L.nblk + L.nblk4, 24, 1, 0);
-      add(g->ln_b, scratch + L.o_ln + 12, 12, L.nblk + L.nblk4, 24, 1, 0);
-    }
-    if (p.Oc) {
-      if (p.flags & MSGAT_F_CMIX) {
-        add(g->ca_w, scratch + L.o_caw, p.Oc * p.C, p.B, (int64_t)p.Oc * p.C, 1, 0);
-        add(g->ca_b, bp, p.Oc, L.nblk, L.nbias, 1, 0);
+    if (!tc_d) {
+      BwdArgs a;
+      a.x = xm; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
+      a.C = p.C; a.N = p.N; a.O = p.O; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre;
+      a.flags = p.flags; a.n_conv = p.n_conv; a.ntile = p.ntile_b; a.J = L.J; a.nnz = p.nnz;
+      for (int i = 0; i < MSGAT_MAX_CONV; ++i) { a.dil[i] = p.dil[i]; a.conv_w[i] = prmm->conv_w[i]; a.conv_b[i] = prmm->conv_b[i]; }
+      a.ln_w = prmm->ln_w; a.ln_b = prmm->ln_b; a.res_w = prmm->res_w; a.sa_W = prmm->sa_W;
+      a.Mc = savedm + p.o_Mc; a.Pt = savedm + p.o_Pt; a.Z = savedm + p.o_Z; a.pw = savedm + p.o_pw;
+      a.row_ptr = adj ? adj->row_ptr : nullptr; a.col_idx = adj ? adj->col_idx : nullptr;
+      a.csc_ptr = adj ? adj->csc_ptr : nullptr; a.csc_row = adj ? adj->csc_row : nullptr; a.csc_eid = adj ? adj->csc_eid : nullptr;
+      for (int q = 0; q < NJOBS; ++q) {
+        a.jobs[q] = L.jobs[q];
+        if (q == JOB_MC) { a.jobs[q].out = scr + L.o_dMc; a.jobs[q].blk_stride = (int64_t)p.Oc * p.C; }
+        else { a.jobs[q].out = scr + L.o_wg + L.off_job[q]; a.jobs[q].blk_stride = L.WGT; }
       }
-      add(g->ca_Wc, scratch + L.o_Wc, 144, p.B, 144, 1, 0);
-      add(g->ca_alpha, scratch + L.o_pan, p.N, p.B, p.N, 1, 0);
+      a.bias_part = scr + L.o_bias; a.ln_part = scr + L.o_ln; a.dPt_part = reinterpret_cast<double*>(scr + L.o_dPt);
+      a.delta = scr + L.o_delta; a.dSnz = scr + L.o_dSnz; a.dx = dxm;
+      a.nbias = L.nbias; a.arena_floats = bwd_arena_floats(p, L.T);
+      size_t smem = (size_t)bwd_smem_floats(p, L.NT, L.T) * 4;
+      a.S = L.S;
+      a.skip_wgrad = tc_w ? 1 : 0;
+      a.resident = (tc_w && bwd_resident_floats(p) > 0) ? 1 : 0;
+      a.tcA = tc_w ? scr + L.o_tcA : nullptr;
+#define BWD_CASE(NTV, RBV) MSGAT_LAUNCH((k_bwd_main<NTV, RBV>), dim3(L.J, p.B), dim3(L.T), smem, stream, a)
+      if (L.RBT == 2) {
+        if (L.NT == 16) BWD_CASE(16, 2); else if (L.NT == 8) BWD_CASE(8, 2); else BWD_CASE(4, 2);
+      } else {
+        if (L.NT == 16) BWD_CASE(16, 4); else if (L.NT == 8) BWD_CASE(8, 4); else BWD_CASE(4, 4);
+      }
+#undef BWD_CASE
     }
-    if (p.Ot) add(g->ta_alpha, scratch + L.o_pat, p.C, L.nblk4, p.C, 1, 0, 1);
-    if (p.Os) {
-      add(g->sa_alpha, scratch + L.o_pas, p.C, L.nblk4, p.C, 1, 0, 1);
-      add(g->sa_Wg, scratch + L.o_Wg, 144, p.B * L.nfin, 144, 1, 0);
+#ifndef MSGAT_EMU
+    if (tc_w) {
+      float* wg = scr + L.o_wg;
+      launch_tc_wgrad(p, prmm, adj, xm, G, savedm, scr + L.o_tcA, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
+                      wg + L.off_job[JOB_CONV + 1], wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT,
+                      scr + L.o_dMc, (int64_t)p.Oc * p.C, stream);
     }
-    r.starts[nj] = tot; r.njobs = nj;
-    if (tot > 0) LAUNCH_REDUCE(tot, stream, r);
+#endif
   }
-  return 0;
+  return meam_backward_tail(p, L, Jw, prm, adj, x, saved, scratch, dx, g, stream);
 }

@@ -15,12 +15,14 @@
 #include "tile_ops.cuh"
 
 // ---------------------------------------------------------------------------------------
+// Grouped launch: blockIdx.z = component m; every pointer below is component 0's, component m's buffers lie
+// x_sm / sv_sm / sc_sm floats further (x, saved, scratch), its parameters are prm[m].
 struct PrepArgs {
-  const float* x; int64_t x_sb, x_sc;
+  const float* x; int64_t x_sb, x_sc, x_sm, sv_sm, sc_sm;
   int C, N, Oc, Ot, Os, Cz, s_pre, do_ln, ntile;
-  const float *ln_w, *ln_b, *sa_alpha, *ta_alpha, *ca_alpha, *Wt1, *Wt2, *sa_W;
+  msgat_meam_params prm[MSGAT_MAX_GROUP];
   float *qs, *qt, *Z;
-  double *pqc, *pK;  // per-tile partial sums kept in fp64: they feed softmaxes whose scores reach O(100)
+  float *pqc, *pK;  // (as doubles) per-tile partial sums kept in fp64: they feed softmaxes whose scores reach O(100)
 };
 
 template <int NT>
@@ -31,26 +33,32 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
   float* QT = H + a.C * PS;                       // [P]
   float* LW = QT + P;                             // ln w,b [24]
   float* WsT = LW + 24;                           // [C][rup4(Os)] when s_pre
-  const int tile = blockIdx.x, b = blockIdx.y, n0 = tile * NT;
+  const int tile = blockIdx.x, b = blockIdx.y, m = blockIdx.z, n0 = tile * NT;
+  const msgat_meam_params& PM = a.prm[m];
+  float* const qs_m = a.qs + m * a.sv_sm;
+  float* const qt_m = a.qt + m * a.sv_sm;
+  float* const Z_m = a.Z + m * a.sv_sm;
+  double* const pqc_m = reinterpret_cast<double*>(a.pqc + m * a.sc_sm);
+  double* const pK_m = reinterpret_cast<double*>(a.pK + m * a.sc_sm);
   const int WS = (a.Os + 3) & ~3;
   if (threadIdx.x < 12) {
-    LW[threadIdx.x] = a.do_ln ? a.ln_w[threadIdx.x] : 1.f;
-    LW[12 + threadIdx.x] = a.do_ln ? a.ln_b[threadIdx.x] : 0.f;
+    LW[threadIdx.x] = a.do_ln ? PM.ln_w[threadIdx.x] : 1.f;
+    LW[12 + threadIdx.x] = a.do_ln ? PM.ln_b[threadIdx.x] : 0.f;
   }
-  if (a.s_pre) stage_wT(WsT, a.sa_W, a.Os, a.C, WS, 1, 0);
+  if (a.s_pre) stage_wT(WsT, PM.sa_W, a.Os, a.C, WS, 1, 0);
   __syncthreads();
-  tile_load_ln(a.x + b * a.x_sb, a.x_sc, a.C, a.N, n0, NT, PS, nullptr, H, LW, LW + 12, a.do_ln, nullptr);
+  tile_load_ln(a.x + m * a.x_sm + b * a.x_sb, a.x_sc, a.C, a.N, n0, NT, PS, nullptr, H, LW, LW + 12, a.do_ln, nullptr);
   __syncthreads();
   // spatial / temporal queries: q[n,t] = sum_c alpha[c] h[c,n,t]   (attention.py:33,63)
   for (int p = threadIdx.x; p < P; p += blockDim.x) {
     const int nl = p / 12, n = n0 + nl;
     float s = 0.f, t = 0.f;
-    if (a.Os) for (int c = 0; c < a.C; ++c) s = fmaf(__ldg(a.sa_alpha + c), H[c * PS + p], s);
-    if (a.Ot) for (int c = 0; c < a.C; ++c) t = fmaf(__ldg(a.ta_alpha + c), H[c * PS + p], t);
+    if (a.Os) for (int c = 0; c < a.C; ++c) s = fmaf(__ldg(PM.sa_alpha + c), H[c * PS + p], s);
+    if (a.Ot) for (int c = 0; c < a.C; ++c) t = fmaf(__ldg(PM.ta_alpha + c), H[c * PS + p], t);
     QT[p] = t;
     if (n < a.N) {
-      if (a.Os) a.qs[((int64_t)b * a.N + n0) * 12 + p] = s;
-      if (a.Ot) a.qt[((int64_t)b * a.N + n0) * 12 + p] = t;
+      if (a.Os) qs_m[((int64_t)b * a.N + n0) * 12 + p] = s;
+      if (a.Ot) qt_m[((int64_t)b * a.N + n0) * 12 + p] = t;
     }
   }
   // Z for the spatial aggregation: W h when that narrows the rows (msgat.py:27 commuted in
@@ -70,27 +78,27 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
       if (n < a.N)
         MSGAT_UNROLL
         for (int j = 0; j < 4; ++j)
-          if (o0 + j < a.Cz) st4(a.Z + (((int64_t)b * a.Cz + o0 + j) * a.N + n) * 12 + t0, acc[j]);
+          if (o0 + j < a.Cz) st4(Z_m + (((int64_t)b * a.Cz + o0 + j) * a.N + n) * 12 + t0, acc[j]);
     }
   }
   // per-tile partial of the channel query q_c[c,t] = sum_n alpha[n] h[c,n,t]  (attention.py:92)
   if (a.Oc) {
-    double* dst = a.pqc + ((int64_t)b * a.ntile + tile) * a.C * 12;
+    double* dst = pqc_m + ((int64_t)b * a.ntile + tile) * a.C * 12;
     for (int i = threadIdx.x; i < a.C * 12; i += blockDim.x) {
       const int c = i / 12, t = i - c * 12;
       double s = 0.0;
       for (int nl = 0; nl < NT; ++nl)
-        if (n0 + nl < a.N) s += (double)__ldg(a.ca_alpha + n0 + nl) * (double)H[c * PS + nl * 12 + t];
+        if (n0 + nl < a.N) s += (double)__ldg(PM.ca_alpha + n0 + nl) * (double)H[c * PS + nl * 12 + t];
       dst[i] = s;
     }
   }
   __syncthreads();
   // per-tile partial of the temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T  (attention.py:65)
   if (a.Ot) {
-    double* dst = a.pK + ((int64_t)b * a.ntile + tile) * 240;
+    double* dst = pK_m + ((int64_t)b * a.ntile + tile) * 240;
     for (int i = threadIdx.x; i < 240; i += blockDim.x) {
       const int t = i / 20, r = i - t * 20;
-      const float* W = (r < 10) ? a.Wt1 + (int64_t)r * a.N : a.Wt2 + (int64_t)(r - 10) * a.N;
+      const float* W = (r < 10) ? PM.ta_Wt1 + (int64_t)r * a.N : PM.ta_Wt2 + (int64_t)(r - 10) * a.N;
       double s = 0.0;
       for (int nl = 0; nl < NT; ++nl)
         if (n0 + nl < a.N) s += (double)__ldg(W + n0 + nl) * (double)QT[nl * 12 + t];
@@ -100,10 +108,11 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------
-struct SmallArgs {
+struct SmallArgs {   // grouped like PrepArgs: blockIdx.y = component
   int C, Oc, Ot, cmix, ntile;
-  const double *pqc, *pK;
-  const float *Wc, *ca_w;
+  int64_t sv_sm, sc_sm;
+  const float *pqc, *pK;   // (as doubles)
+  msgat_meam_params prm[MSGAT_MAX_GROUP];
   float *qc, *Pc, *Mc, *K, *Pt;
 };
 
@@ -112,7 +121,16 @@ struct SmallArgs {
 // fp32 score carries 1e-5 of relative error straight into the attention matrix.
 MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  const int C = a.C, b = blockIdx.x;
+  const int C = a.C, b = blockIdx.x, m = blockIdx.y;
+  const float* const Wc_m = a.prm[m].ca_Wc;
+  const float* const caw_m = a.prm[m].ca_w;
+  const double* const pqc_m = reinterpret_cast<const double*>(a.pqc + m * a.sc_sm);
+  const double* const pK_m = reinterpret_cast<const double*>(a.pK + m * a.sc_sm);
+  float* const qc_o = a.qc + m * a.sv_sm;
+  float* const Pc_o = a.Pc + m * a.sv_sm;
+  float* const Mc_o = a.Mc + m * a.sv_sm;
+  float* const K_o = a.K + m * a.sv_sm;
+  float* const Pt_o = a.Pt + m * a.sv_sm;
   double* qc = reinterpret_cast<double*>(smem_raw);  // [C][12]
   double* tmp = qc + C * 12;                         // [C][12]
   double* S = tmp + C * 12;                          // [C][C]
@@ -121,17 +139,17 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
   if (a.Oc) {
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
       double s = 0.0;
-      for (int tl = 0; tl < a.ntile; ++tl) s += a.pqc[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
       qc[i] = s;
-      a.qc[(int64_t)b * C * 12 + i] = (float)s;
+      qc_o[(int64_t)b * C * 12 + i] = (float)s;
     }
   }
   if (a.Ot) {
     for (int i = threadIdx.x; i < 240; i += blockDim.x) {
       double s = 0.0;
-      for (int tl = 0; tl < a.ntile; ++tl) s += a.pK[((int64_t)b * a.ntile + tl) * 240 + i];
+      for (int tl = 0; tl < a.ntile; ++tl) s += pK_m[((int64_t)b * a.ntile + tl) * 240 + i];
       K[i] = s;
-      a.K[(int64_t)b * 240 + i] = (float)s;
+      K_o[(int64_t)b * 240 + i] = (float)s;
     }
   }
   __syncthreads();
@@ -141,7 +159,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
       const int c = i / 12, t2 = i - c * 12;
       double s = 0.0;
       MSGAT_UNROLL
-      for (int t = 0; t < 12; ++t) s += qc[c * 12 + t] * (double)__ldg(a.Wc + t * 12 + t2);
+      for (int t = 0; t < 12; ++t) s += qc[c * 12 + t] * (double)__ldg(Wc_m + t * 12 + t2);
       tmp[i] = s;
     }
     __syncthreads();
@@ -162,18 +180,18 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
       for (int j = 0; j < C; ++j) S[c * C + j] *= inv;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < C * C; i += blockDim.x) a.Pc[(int64_t)b * C * C + i] = (float)S[i];
+    for (int i = threadIdx.x; i < C * C; i += blockDim.x) Pc_o[(int64_t)b * C * C + i] = (float)S[i];
     // fold the 1x1 conv of CACN (msgat.py:94) into the attention: Mc = W1 Pc
     for (int i = threadIdx.x; i < a.Oc * C; i += blockDim.x) {
       const int o = i / C, j = i - o * C;
       double s;
       if (a.cmix) {
         s = 0.0;
-        for (int c = 0; c < C; ++c) s += (double)__ldg(a.ca_w + o * C + c) * S[c * C + j];
+        for (int c = 0; c < C; ++c) s += (double)__ldg(caw_m + o * C + c) * S[c * C + j];
       } else {
         s = S[o * C + j];
       }
-      a.Mc[(int64_t)b * a.Oc * C + i] = (float)s;
+      Mc_o[(int64_t)b * a.Oc * C + i] = (float)s;
     }
   }
   if (a.Ot) {
@@ -195,7 +213,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
       for (int j = 0; j < 12; ++j) { e[j] = exp(St[t * 12 + j] - m); l += e[j]; }
       const double inv = 1.0 / l;
       MSGAT_UNROLL
-      for (int j = 0; j < 12; ++j) a.Pt[(int64_t)b * 144 + t * 12 + j] = (float)(e[j] * inv);
+      for (int j = 0; j < 12; ++j) Pt_o[(int64_t)b * 144 + t * 12 + j] = (float)(e[j] * inv);
     }
   }
 }
@@ -391,37 +409,8 @@ static int pick_threads(int items, int cap) {
   return t < 64 ? 64 : t;
 }
 
-int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
-                      float* saved, float* scratch, void* stream) {
-  const bool do_ln = p.flags & MSGAT_F_LN;
-  {
-    PrepArgs a;
-    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
-    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre; a.do_ln = do_ln;
-    a.ntile = p.ntile_p;
-    a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.sa_alpha = prm->sa_alpha; a.ta_alpha = prm->ta_alpha;
-    a.ca_alpha = prm->ca_alpha; a.Wt1 = prm->ta_Wt1; a.Wt2 = prm->ta_Wt2; a.sa_W = prm->sa_W;
-    a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
-    a.pqc = reinterpret_cast<double*>(scratch + p.o_pqc); a.pK = reinterpret_cast<double*>(scratch + p.o_pK);
-    constexpr int NT = 16;
-    size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
-    MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B), dim3(256), smem, stream, a);
-  }
-  if (p.Oc || p.Ot) {
-    SmallArgs a;
-    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = p.ntile_p;
-    a.pqc = reinterpret_cast<const double*>(scratch + p.o_pqc); a.pK = reinterpret_cast<const double*>(scratch + p.o_pK);
-    a.Wc = prm->ca_Wc; a.ca_w = prm->ca_w;
-    a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
-    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 8;
-    const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
-    MSGAT_LAUNCH(k_small, dim3(p.B), dim3(smT), smem, stream, a);
-  }
-  if (p.Os) launch_sstats(p, prm, adj, saved, stream);
-#ifndef MSGAT_EMU
-  if (tc_apply_supported(p)) return launch_tc_apply(p, prm, adj, x, out, saved, stream);
-  if (tc_apply3_supported(p)) return launch_tc_apply3(p, prm, adj, x, out, saved, stream);
-#endif
+static void apply_launch(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
+                         float* saved, void* stream) {
   {
     ApplyArgs a;
     a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc;
@@ -458,6 +447,50 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
       case 4: MSGAT_LAUNCH(k_apply<4>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
       default: MSGAT_LAUNCH(k_apply<2>, dim3(J, p.B), dim3(nthr), smem, stream, a); break;
     }
+  }
+}
+
+int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
+                      float* saved, float* scratch, void* stream) {
+  const bool do_ln = p.flags & MSGAT_F_LN;
+  const int M = p.M;
+  const int64_t sv_sm = p.saved_total, sc_sm = p.scratch_sm, out_sm = (int64_t)p.B * p.O * p.N * 12;
+  {   // one launch for all components
+    PrepArgs a;
+    a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.sv_sm = sv_sm; a.sc_sm = sc_sm;
+    a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre; a.do_ln = do_ln;
+    a.ntile = p.ntile_p;
+    for (int m = 0; m < M; ++m) a.prm[m] = prm[m];
+    a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
+    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
+    constexpr int NT = 16;
+    size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
+    MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
+  }
+  if (p.Oc || p.Ot) {
+    SmallArgs a;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = p.ntile_p;
+    a.sv_sm = sv_sm; a.sc_sm = sc_sm;
+    a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
+    for (int m = 0; m < M; ++m) a.prm[m] = prm[m];
+    a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
+    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 8;
+    const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
+    MSGAT_LAUNCH(k_small, dim3(p.B, M), dim3(smT), smem, stream, a);
+  }
+  if (p.Os) launch_sstats(p, prm, adj, saved, stream);
+  if (l1_fwd_supported(p)) return launch_l1_fwd(p, prm, adj, x, out, saved, stream);   // first layer: one grouped launch
+  // the apply pass: still one launch per component (the component's buffers by pointer offset)
+  for (int m = 0; m < M; ++m) {
+    const float* xm = x + m * p.x_sm;
+    float* outm = out + m * out_sm;
+    float* savedm = saved + m * sv_sm;
+    const msgat_meam_params* prmm = prm + m;
+#ifndef MSGAT_EMU
+    if (tc_apply_supported(p)) { int rc = launch_tc_apply(p, prmm, adj, xm, outm, savedm, stream); if (rc) return rc; continue; }
+    if (tc_apply3_supported(p)) { int rc = launch_tc_apply3(p, prmm, adj, xm, outm, savedm, stream); if (rc) return rc; continue; }
+#endif
+    apply_launch(p, prmm, adj, xm, outm, savedm, stream);
   }
   return 0;
 }

@@ -8,7 +8,9 @@
 
 struct Plan {
   int B, C, N, O, Oc, Ot, Os, flags, n_conv, dil[MSGAT_MAX_CONV], nnz, precision;
-  int64_t x_sb, x_sc;
+  int M;                            // components of a grouped call (>= 1)
+  int64_t x_sb, x_sc, x_sm;
+  int64_t scratch_sm;               // floats between the scratch buffers of consecutive components (filled by api.cu)
   int s_pre;  // spatial branch aggregates Z = W h (Os channels) instead of h (C channels)
   int Cz;     // channels of the Z buffer the spatial gather reads
   // forward tiles
@@ -46,6 +48,8 @@ static inline int make_plan(const msgat_meam_desc* d, int nnz, Plan* p) {
   p->B = d->B; p->C = d->C; p->N = d->N; p->Oc = d->Oc; p->Ot = d->Ot; p->Os = d->Os;
   p->O = d->Oc + d->Ot + d->Os; p->flags = d->flags; p->n_conv = d->n_conv; p->nnz = nnz;
   p->precision = d->precision; p->x_sb = d->x_sb; p->x_sc = d->x_sc;
+  p->M = d->M > 1 ? d->M : 1; p->x_sm = d->x_sm; p->scratch_sm = 0;
+  if (p->M > MSGAT_MAX_GROUP) return -8;
   for (int i = 0; i < MSGAT_MAX_CONV; ++i) p->dil[i] = d->dil[i];
   if (d->B <= 0 || d->C <= 0 || d->N <= 0 || p->O <= 0) return -1;
   if (d->n_conv < 0 || d->n_conv > MSGAT_MAX_CONV) return -2;

@@ -9,10 +9,11 @@
 
 #define MAX_RJOBS 28
 #define RED_WARPS 8
-struct RJob { float* dst; const float* src; int n, nparts, dmul, doff; int64_t pstride; int f64; };  // f64: src holds doubles (pstride in doubles)
-struct ReduceArgs { RJob j[MAX_RJOBS]; int starts[MAX_RJOBS + 1]; int njobs; };
-#define LAUNCH_REDUCE(tot, stream, r) \
-  MSGAT_LAUNCH(k_reduce, dim3(((tot) + 31) / 32), dim3(32 * RED_WARPS), RED_WARPS * 32 * sizeof(double), stream, r)
+// Grouped: blockIdx.y = component m writes dst[m] from src + m * sc_sm (floats).
+struct RJob { float* dst[MSGAT_MAX_GROUP]; const float* src; int n, nparts, dmul, doff; int64_t pstride; int f64; };  // f64: src holds doubles (pstride in doubles)
+struct ReduceArgs { RJob j[MAX_RJOBS]; int starts[MAX_RJOBS + 1]; int njobs; int64_t sc_sm; };
+#define LAUNCH_REDUCE(tot, M, stream, r) \
+  MSGAT_LAUNCH(k_reduce, dim3(((tot) + 31) / 32, (M)), dim3(32 * RED_WARPS), RED_WARPS * 32 * sizeof(double), stream, r)
 
 MSGAT_KERNEL MSGAT_LB(32 * RED_WARPS, 4) k_reduce(ReduceArgs a) {
   MSGAT_DYN_SMEM(red_raw);
@@ -25,7 +26,7 @@ MSGAT_KERNEL MSGAT_LB(32 * RED_WARPS, 4) k_reduce(ReduceArgs a) {
   if (live) {
     while (idx >= a.starts[q + 1]) ++q;
     e = idx - a.starts[q];
-    const float* src = a.j[q].src + e;
+    const float* src = a.j[q].src + (int64_t)blockIdx.y * a.sc_sm + e;
     const int64_t ps = a.j[q].pstride;
     const int np = a.j[q].nparts;
     int p = a.j[q].f64 ? np : w;
@@ -37,7 +38,7 @@ MSGAT_KERNEL MSGAT_LB(32 * RED_WARPS, 4) k_reduce(ReduceArgs a) {
     }
     for (; p < np; p += RED_WARPS) s0 += (double)src[(int64_t)p * ps];
     if (a.j[q].f64) {
-      const double* sd = reinterpret_cast<const double*>(a.j[q].src) + e;
+      const double* sd = reinterpret_cast<const double*>(a.j[q].src + (int64_t)blockIdx.y * a.sc_sm) + e;
       s0 = s1 = s2 = s3 = 0.0;
       for (p = w; p < np; p += RED_WARPS) s0 += sd[(int64_t)p * ps];
     }
@@ -49,6 +50,6 @@ MSGAT_KERNEL MSGAT_LB(32 * RED_WARPS, 4) k_reduce(ReduceArgs a) {
     double t = 0.0;
     for (int k = 0; k < RED_WARPS; ++k) t += part[k][lane];
     const RJob& jb = a.j[q];
-    jb.dst[(int64_t)e * jb.dmul + jb.doff] = (float)t;
+    jb.dst[blockIdx.y][(int64_t)e * jb.dmul + jb.doff] = (float)t;
   }
 }

@@ -14,12 +14,14 @@
 #define SS_QUART 4
 #define SS_CHUNK 256
 
-struct SStatsArgs {
+struct SStatsArgs {   // grouped: blockIdx.z = component m, buffers sv_sm floats apart, Wg per component
   int N, nnz;
-  const float *qs, *Wg, *val;
+  int64_t sv_sm;
+  const float* Wg[MSGAT_MAX_GROUP];
+  const float *qs, *val;
   const int32_t *row_ptr, *col_idx;
   float *m, *U, *pw;
-  double *l, *E;  // kept in fp64: the backward subtracts delta * E and delta / l * P from sums they nearly cancel
+  float *l, *E;  // (as doubles) kept in fp64: the backward subtracts delta * E and delta / l * P from sums they nearly cancel
 };
 
 // Thread map: a block owns SS_ROWS = 64 rows; a warp is 32 rows x ONE column quarter, so the q row of a
@@ -34,8 +36,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
   const int b = blockIdx.y, rl = threadIdx.x % SS_ROWS, cq = threadIdx.x / SS_ROWS;
   const int n = blockIdx.x * SS_ROWS + rl;
   const bool live = n < a.N;
-  const float* qb = a.qs + (int64_t)b * a.N * 12;
-  for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = a.Wg[i];
+  const int64_t mo = (int64_t)blockIdx.z * a.sv_sm;
+  const float* qb = a.qs + mo + (int64_t)b * a.N * 12;
+  const float* Wgm = a.Wg[blockIdx.z];
+  for (int i = threadIdx.x; i < 144; i += blockDim.x) WG[i] = Wgm[i];
   __syncthreads();
   // U[n,:] = q[n,:] Wg   (k @ Wg, attention.py:34)
   float U[12];
@@ -123,10 +127,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
   }
   const double invd = 1.0 / l;
   const float inv = (float)invd;
-  a.m[(int64_t)b * a.N + n] = M;
-  a.l[(int64_t)b * a.N + n] = l;
-  for (int t = 0; t < 12; ++t) a.E[((int64_t)b * a.N + n) * 12 + t] = E[t] * invd;
-  for (int t = 0; t < 12; ++t) a.U[((int64_t)b * a.N + n) * 12 + t] = U[t];  // reused by k_scol
+  a.m[mo + (int64_t)b * a.N + n] = M;
+  reinterpret_cast<double*>(a.l + mo)[(int64_t)b * a.N + n] = l;
+  for (int t = 0; t < 12; ++t) reinterpret_cast<double*>(a.E + mo)[((int64_t)b * a.N + n) * 12 + t] = E[t] * invd;
+  for (int t = 0; t < 12; ++t) a.U[mo + ((int64_t)b * a.N + n) * 12 + t] = U[t];  // reused by k_scol
   // masked attention at the adjacency non-zeros of this row (attention.py:36: att * adjacency)
   const int e1 = a.row_ptr[n + 1];
   for (int e = a.row_ptr[n]; e < e1; ++e) {
@@ -139,18 +143,20 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
     s2 = ffma2(U2[1], hi2(q0), s2); s2 = ffma2(U2[2], lo2(q1), s2); s2 = ffma2(U2[3], hi2(q1), s2);
     s2 = ffma2(U2[4], lo2(q2), s2); s2 = ffma2(U2[5], hi2(q2), s2);
     const float s = s2.x + s2.y;
-    a.pw[(int64_t)b * a.nnz + e] = expf(s - M) * inv * a.val[e];
+    a.pw[mo + (int64_t)b * a.nnz + e] = expf(s - M) * inv * a.val[e];
   }
 }
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream) {
   SStatsArgs a;
   a.N = p.N; a.nnz = p.nnz;
-  a.qs = saved + p.o_qs; a.Wg = prm->sa_Wg; a.val = adj->val;
+  a.sv_sm = p.saved_total;
+  for (int m = 0; m < p.M; ++m) a.Wg[m] = prm[m].sa_Wg;
+  a.qs = saved + p.o_qs; a.val = adj->val;
   a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx;
-  a.m = saved + p.o_m; a.l = reinterpret_cast<double*>(saved + p.o_l); a.E = reinterpret_cast<double*>(saved + p.o_E);
+  a.m = saved + p.o_m; a.l = saved + p.o_l; a.E = saved + p.o_E;
   a.U = saved + p.o_U; a.pw = saved + p.o_pw;
-  dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B);
+  dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B, p.M);
   size_t smem = (SS_CHUNK * 12 + 144) * sizeof(float) + (size_t)SS_QUART * SS_ROWS * 14 * sizeof(double);
   MSGAT_LAUNCH(k_sstats, grid, dim3(256), smem, stream, a);
   return 0;
@@ -161,10 +167,11 @@ int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* 
 // part of dq[i,:] = sum_n dS[n,i] U[n,:] is  -sum_n P[n,i] delta[n] U[n,:]  over ALL rows n:
 //   dq_dense[i,:] = -sum_n exp(q[i].U[n] - m[n]) * (delta[n]/l[n]) * U[n,:]
 // One thread group per column i, rows streamed through shared memory as (U[n,:], m[n], w[n]).
-struct SColArgs {
+struct SColArgs {   // grouped: blockIdx.z = component; saved buffers sv_sm apart, scratch buffers sc_sm apart
   int N;
+  int64_t sv_sm, sc_sm;
   const float *qs, *U, *m, *delta;
-  const double* l;
+  const float* l;   // (as doubles)
   float* dq;  // [B,N,12]  written (dense part)
 };
 
@@ -175,8 +182,12 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
   const int b = blockIdx.y, rl = threadIdx.x % SS_ROWS, cq = threadIdx.x / SS_ROWS;   // same thread map as k_sstats
   const int i = blockIdx.x * SS_ROWS + rl;
   const bool live = i < a.N;
-  const float* qb = a.qs + (int64_t)b * a.N * 12;
-  const float* Ub = a.U + (int64_t)b * a.N * 12;
+  const int64_t mo = (int64_t)blockIdx.z * a.sv_sm, so = (int64_t)blockIdx.z * a.sc_sm;
+  const float* qb = a.qs + mo + (int64_t)b * a.N * 12;
+  const float* Ub = a.U + mo + (int64_t)b * a.N * 12;
+  const float* mb = a.m + mo;
+  const double* lb = reinterpret_cast<const double*>(a.l + mo);
+  const float* deltab = a.delta + so;
   float qi[12];
   double acc[12];  // the dense sum cancels against the sparse part of dq: keep it in fp64
   for (int t = 0; t < 12; ++t) { qi[t] = live ? qb[(int64_t)i * 12 + t] : 0.f; acc[t] = 0.0; }
@@ -192,8 +203,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     }
     for (int r = threadIdx.x; r < len; r += blockDim.x) {
       const int64_t g = (int64_t)b * a.N + n0 + r;
-      UR[r * 16 + 12] = a.m[g];
-      UR[r * 16 + 13] = (float)((double)a.delta[g] / a.l[g]);
+      UR[r * 16 + 12] = mb[g];
+      UR[r * 16 + 13] = (float)((double)deltab[g] / lb[g]);
     }
     __syncthreads();
     // four consecutive rows per step, summed in fp32 inside the group and in fp64 across groups (see k_sstats)
@@ -231,13 +242,14 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
     const double* o = MG + ((int64_t)k * SS_ROWS + rl) * 12;
     for (int t = 0; t < 12; ++t) acc[t] += o[t];
   }
-  for (int t = 0; t < 12; ++t) a.dq[((int64_t)b * a.N + i) * 12 + t] = (float)(-acc[t]);
+  for (int t = 0; t < 12; ++t) a.dq[so + ((int64_t)b * a.N + i) * 12 + t] = (float)(-acc[t]);
 }
 
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream) {
   SColArgs a;
-  a.N = p.N; a.qs = saved + p.o_qs; a.U = saved + p.o_U; a.m = saved + p.o_m; a.l = reinterpret_cast<const double*>(saved + p.o_l); a.delta = delta; a.dq = dq;
-  dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B);
+  a.N = p.N; a.sv_sm = p.saved_total; a.sc_sm = p.scratch_sm;
+  a.qs = saved + p.o_qs; a.U = saved + p.o_U; a.m = saved + p.o_m; a.l = saved + p.o_l; a.delta = delta; a.dq = dq;
+  dim3 grid((p.N + SS_ROWS - 1) / SS_ROWS, p.B, p.M);
   size_t smem = (SS_CHUNK * 16) * sizeof(float) + (size_t)SS_QUART * SS_ROWS * 12 * sizeof(double);
   MSGAT_LAUNCH(k_scol, grid, dim3(256), smem, stream, a);
   return 0;

@@ -75,9 +75,21 @@ TC_DEV void td_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float 
 TC_DEV void td_mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64_t dbl, uint32_t ka, uint32_t kb, uint32_t idesc,
                     uint32_t acc) {
   const uint64_t oa = (uint64_t)(ka * 64u), ob = (uint64_t)(kb * 64u);
+  // hi*hi into the main accumulator, the three correction terms (2^-11 of it) into a second one 256 columns further:
+  // the tensor core truncates when it adds into the fp32 accumulator, so the error grows with the number of
+  // accumulations at full magnitude (see tc_fwd3.cu); the readers add the two accumulators in fp32.
   umma_tf32(d, dah + oa, dbh + ob, idesc, acc);
-  umma_tf32(d, dah + oa, dbl + ob, idesc, 1u);
-  umma_tf32(d, dal + oa, dbh + ob, idesc, 1u);
+  umma_tf32(d + 256u, dah + oa, dbl + ob, idesc, acc);
+  umma_tf32(d + 256u, dal + oa, dbh + ob, idesc, 1u);
+  umma_tf32(d + 256u, dal + oa, dbl + ob, idesc, 1u);
+}
+TC_DEV void td_ld8_sum(uint32_t addr, float (&v)[8]) {
+  uint32_t r0[8], r1[8];
+  tmem_ld8_nowait(addr, r0);
+  tmem_ld8_nowait(addr + 256u, r1);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r0[i]) + __uint_as_float(r1[i]);
 }
 
 __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
@@ -137,7 +149,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   }
   if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
   if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
-  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 256);
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -276,7 +288,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int c0 = 0; c0 < 2 * b; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;   // warp-uniform
         float v[8];
-        tmem_ld8(Dy + lane_base + c0, v);
+        td_ld8_sum(Dy + lane_base + c0, v);
         if (l < TD_P) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) PRE[(c0 + j) * TD_PITCH + l] = v[j];
@@ -407,7 +419,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int c0 = 0; c0 < C; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;
         float v[8];
-        tmem_ld8(Dh + lane_base + c0, v);
+        td_ld8_sum(Dh + lane_base + c0, v);
         if (l < TD_P) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) STG[(c0 + j) * TD_PITCH + l] = v[j];
@@ -436,7 +448,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
           float var = 0.f;
 #pragma unroll
           for (int t = 0; t < 12; ++t) { xh[t] -= mu; var = fmaf(xh[t], xh[t], var); }
-          const float rs = rsqrtf(var * (1.0f / 12.0f) + LN_EPS);
+          const float rs = rsqrt_ln(var * (1.0f / 12.0f) + LN_EPS);
           float* qrow = STG + c * TD_PITCH + nl * 12;
           float gg[12], m1 = 0.f, m2 = 0.f;
           const float4 d0 = ld4(qrow), d1 = ld4(qrow + 4), d2 = ld4(qrow + 8);
@@ -469,7 +481,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int c0 = 0; c0 < C; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;
         float r[8];
-        tmem_ld8(Dx + lane_base + c0, r);
+        td_ld8_sum(Dx + lane_base + c0, r);
         if (live) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -508,7 +520,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     for (int w = 0; w < TD_THREADS / 32; ++w) s += RED[w * 24 + tid];
     a.ln_part[(int64_t)blk * 24 + tid] = s;
   }
-  if (warp == 0) tmem_dealloc(tm, 256);
+  if (warp == 0) tmem_dealloc(tm, 512);
 }
 
 bool tc_dgrad_supported(const Plan& p) {

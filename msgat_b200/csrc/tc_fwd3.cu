@@ -62,9 +62,22 @@ TC_DEV void tf3_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float
 // start-address field (16-byte units).
 TC_DEV void mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64_t dbl, uint32_t ks, uint32_t idesc, uint32_t acc) {
   const uint64_t o = (uint64_t)(ks * 64u);
+  // The tensor core adds each MMA's products into the fp32 accumulator with truncation, not round-to-nearest: the
+  // error grows with the NUMBER of accumulations at full magnitude.  The hi*hi terms therefore go to one accumulator
+  // (one rounding per k-step) and the three correction terms, 2^-11 of it, to a second one 256 columns further;
+  // the epilogue adds the two in fp32.
   umma_tf32(d, dah + o, dbh + o, idesc, acc);
-  umma_tf32(d, dah + o, dbl + o, idesc, 1u);
-  umma_tf32(d, dal + o, dbh + o, idesc, 1u);
+  umma_tf32(d + 256u, dah + o, dbl + o, idesc, acc);
+  umma_tf32(d + 256u, dal + o, dbh + o, idesc, 1u);
+  umma_tf32(d + 256u, dal + o, dbl + o, idesc, 1u);
+}
+TC_DEV void tmem_ld8_sum(uint32_t addr, float (&v)[8]) {
+  uint32_t r0[8], r1[8];
+  tmem_ld8_nowait(addr, r0);
+  tmem_ld8_nowait(addr + 256u, r1);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r0[i]) + __uint_as_float(r1[i]);
 }
 
 __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
@@ -121,7 +134,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
   }
   if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
   if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
-  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 256);
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -206,7 +219,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
           float mu = (u.x + u.y + u.z + u.w + v.x + v.y + v.z + v.w + w.x + w.y + w.z + w.w) * (1.0f / 12.0f);
           u.x -= mu; u.y -= mu; u.z -= mu; u.w -= mu; v.x -= mu; v.y -= mu; v.z -= mu; v.w -= mu;
           w.x -= mu; w.y -= mu; w.z -= mu; w.w -= mu;
-          const float rs = rsqrtf((dot4(u, u) + dot4(v, v) + dot4(w, w)) * (1.0f / 12.0f) + LN_EPS);
+          const float rs = rsqrt_ln((dot4(u, u) + dot4(v, v) + dot4(w, w)) * (1.0f / 12.0f) + LN_EPS);
           u.x = u.x * rs * LW[0] + LW[12]; u.y = u.y * rs * LW[1] + LW[13]; u.z = u.z * rs * LW[2] + LW[14]; u.w = u.w * rs * LW[3] + LW[15];
           v.x = v.x * rs * LW[4] + LW[16]; v.y = v.y * rs * LW[5] + LW[17]; v.z = v.z * rs * LW[6] + LW[18]; v.w = v.w * rs * LW[7] + LW[19];
           w.x = w.x * rs * LW[8] + LW[20]; w.y = w.y * rs * LW[9] + LW[21]; w.z = w.z * rs * LW[10] + LW[22]; w.w = w.w * rs * LW[11] + LW[23];
@@ -231,7 +244,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
       for (int c0 = 0; c0 < 2 * b; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;   // warp-uniform
         float v[8];
-        tmem_ld8(D2 + lane_base + b + c0, v);
+        tmem_ld8_sum(D2 + lane_base + b + c0, v);
         if (l < TF3_P) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) STG[(c0 + j) * TF3_PITCH + l] = v[j];
@@ -308,13 +321,13 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
       for (int c0 = 0; c0 < O; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;   // warp-uniform
         float r[8], v[8];
-        tmem_ld8(D1 + lane_base + c0, r);
+        tmem_ld8_sum(D1 + lane_base + c0, r);
         if (c0 < b) {
-          tmem_ld8(D2 + lane_base + c0, v);
+          tmem_ld8_sum(D2 + lane_base + c0, v);
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] += caB[c0 + j];
         } else if (c0 < 2 * b) {
-          tmem_ld8(D3 + lane_base + (c0 - b), v);
+          tmem_ld8_sum(D3 + lane_base + (c0 - b), v);
 #pragma unroll
           for (int j = 0; j < 8; ++j) v[j] += c2B[c0 - b + j];
         } else {
@@ -330,7 +343,7 @@ __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
     tc_fence_before_sync();
     __syncthreads();
   }
-  if (warp == 0) tmem_dealloc(tm, 256);
+  if (warp == 0) tmem_dealloc(tm, 512);
 }
 
 bool tc_apply3_supported(const Plan& p) {

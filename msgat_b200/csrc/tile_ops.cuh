@@ -36,7 +36,7 @@ MSGAT_DEV void tile_load_ln(const float* MSGAT_RESTRICT xb, int64_t x_sc, int C,
         a.x -= mu; a.y -= mu; a.z -= mu; a.w -= mu; b.x -= mu; b.y -= mu; b.z -= mu; b.w -= mu;
         d.x -= mu; d.y -= mu; d.z -= mu; d.w -= mu;
         float var = (dot4(a, a) + dot4(b, b) + dot4(d, d)) * (1.0f / 12.0f);
-        float rs = rsqrtf(var + LN_EPS);
+        float rs = rsqrt_ln(var + LN_EPS);
         if (stats) { stats[2 * r] = mu; stats[2 * r + 1] = rs; }
         a.x = a.x * rs * lnw[0] + lnb[0]; a.y = a.y * rs * lnw[1] + lnb[1];
         a.z = a.z * rs * lnw[2] + lnb[2]; a.w = a.w * rs * lnw[3] + lnb[3];

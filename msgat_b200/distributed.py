@@ -13,15 +13,19 @@ class FlatGradients:
     buffer, so that the exchange is a single collective and the optimizer sees reduced
     gradients.  ``zero()`` clears the buffer in place (do not use ``set_to_none``)."""
 
+    ALIGN = 64  # floats: every parameter starts on a 256-byte boundary (the kernels read parameters with 128-bit loads)
+
     def __init__(self, model: torch.nn.Module):
         self.params = [p for p in model.parameters() if p.requires_grad]
-        n = sum(p.numel() for p in self.params)
+        self.offsets = []
+        n = 0
+        for p in self.params:
+            self.offsets.append(n)
+            n += (p.numel() + self.ALIGN - 1) // self.ALIGN * self.ALIGN
         dev = self.params[0].device
         self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
-        o = 0
-        for p in self.params:
+        for p, o in zip(self.params, self.offsets):
             p.grad = self.flat[o:o + p.numel()].view_as(p)
-            o += p.numel()
 
     def zero(self):
         self.flat.zero_()

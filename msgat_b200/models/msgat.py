@@ -9,8 +9,6 @@ call into the sm_100a kernels (``msgat_b200.ops``).
 """
 from typing import List
 
-import os
-
 import torch
 from torch import nn
 
@@ -136,15 +134,17 @@ class MEAM(nn.Module):
     def forward(self, signals: torch.Tensor, adjacency: torch.Tensor) -> torch.Tensor:
         return self._run(signals, adjacency, False, False)
 
-    def _run(self, signals, adjacency, dout_masked: bool, x_is_relu: bool):
-        """``dout_masked`` / ``x_is_relu`` are set only by TPC for MEAMs chained inside it
-        (see ``ops.MeamConfig``); the public ``forward`` has plain autograd semantics."""
+    def config(self, dout_masked: bool = False, x_is_relu: bool = False) -> "ops.MeamConfig":
         b = self.out_channels // 3
         if abs(float(self.ln.eps) - 1e-5) > 0:
             raise ValueError("kernels assume the LayerNorm default eps=1e-5 (msgat.py:115)")
-        cfg = ops.MeamConfig(b, b, b, F.F_LN | F.F_RES | F.F_RELU | F.F_CMIX | F.F_SMIX, self.dilations,
-                             precision=self.precision, dout_masked=dout_masked, x_is_relu=x_is_relu)
-        return ops.meam_op(signals, cfg, ops.sparse_adjacency(adjacency), self.slots())
+        return ops.MeamConfig(b, b, b, F.F_LN | F.F_RES | F.F_RELU | F.F_CMIX | F.F_SMIX, self.dilations,
+                              precision=self.precision, dout_masked=dout_masked, x_is_relu=x_is_relu)
+
+    def _run(self, signals, adjacency, dout_masked: bool, x_is_relu: bool):
+        """``dout_masked`` / ``x_is_relu`` are set only by TPC / MSGAT for MEAMs chained inside them
+        (see ``ops.MeamConfig``); the public ``forward`` has plain autograd semantics."""
+        return ops.meam_op(signals, self.config(dout_masked, x_is_relu), ops.sparse_adjacency(adjacency), self.slots())
 
     def extra_repr(self) -> str:
         return (f"in_channels={self.in_channels}, out_channels={self.out_channels}, n_nodes={self.n_nodes}, "
@@ -210,8 +210,6 @@ class MSGAT(nn.Module):
                 dilations=c["dilations"]) for c in components
         ])
         self.reset_parameters()
-        self.concurrent_components = os.environ.get("MSGAT_STREAMS", "1") != "0"
-        self._streams = {}
 
     def set_precision(self, precision: int):
         for tpc in self.tpcs:
@@ -220,44 +218,39 @@ class MSGAT(nn.Module):
         return self
 
     def forward(self, X: torch.Tensor, H: torch.Tensor, D: torch.Tensor) -> torch.Tensor:
+        M = len(self.tpcs)
         if self.te is not None:
             G = self.te(H, D).float()  # [B, M, N, Tout]
-            gates = [G[:, m] for m in range(len(self.tpcs))]
+            gates = [G[:, m] for m in range(M)]
         else:
-            gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(len(self.tpcs))]
+            gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(M)]
         out = None
-        if X.is_cuda:
-            ops.sparse_adjacency(self.adj)   # built on the caller's stream, before any component stream reads it
-        if X.is_cuda and self.concurrent_components and len(self.tpcs) > 1:
-            # The M components are independent up to the gated sum (msgat.py:204): each MEAM stack runs on
-            # its own stream, so the small per-sample kernels of one component (32 CTAs) and the tail waves
-            # of the large ones overlap with the other components' work, forward and backward (autograd
-            # runs a node's backward on the stream of its forward).  The heads join on the caller's stream.
-            main = torch.cuda.current_stream(X.device)
-            streams = self._component_streams(X.device)
-            feats = []
+        if self._groupable():
+            # The M components are independent up to the gated sum (msgat.py:203-204) and have the same shape:
+            # layer j of ALL of them is one grouped operator (one launch per kernel, component m with its own
+            # parameters), so the per-sample kernels fill the GPU and there is nothing to overlap by hand.
+            sp = ops.sparse_adjacency(self.adj)
+            feats, layout = X, "bm"
+            depth = len(self.tpcs[0].tgacns)
+            for j in range(depth):
+                meams = [tpc.tgacns[j] for tpc in self.tpcs]
+                feats = ops.meam_group_op(feats, layout, meams[0].config(dout_masked=True, x_is_relu=j > 0), sp,
+                                          [mm.slots() for mm in meams])
+                layout = "mb"
+            if depth == 0:
+                feats = X.transpose(0, 1)
             for m, tpc in enumerate(self.tpcs):
-                streams[m].wait_stream(main)
-                with torch.cuda.stream(streams[m]):
-                    feats.append(tpc.features(X[:, m], self.adj))
-            for m, tpc in enumerate(self.tpcs):
-                main.wait_stream(streams[m])
-                feats[m].record_stream(main)
                 out = tpc.head(feats[m], gate=gates[m], acc=out)
             return out
         for m, tpc in enumerate(self.tpcs):
             out = tpc(X[:, m], self.adj, gate=gates[m], acc=out)
         return out
 
-    def _component_streams(self, device):
-        key = str(device)
-        if self._streams.get(key) is None:
-            self._streams[key] = [torch.cuda.Stream(device=device) for _ in self.tpcs]
-            # parameters accumulate their gradients from the component streams on purpose
-            quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
-            if quiet is not None:
-                quiet(False)
-        return self._streams[key]
+    def _groupable(self) -> bool:
+        t0 = self.tpcs[0]
+        return len(self.tpcs) <= _lib.MAX_GROUP and all(
+            t.channels == t0.channels and t.dilations == t0.dilations and
+            all(a.precision == b.precision for a, b in zip(t.tgacns, t0.tgacns)) for t in self.tpcs)
 
     def reset_parameters(self):
         """xavier-normal for matrices, U(+-1/sqrt(size0)) for vectors incl. the LayerNorm

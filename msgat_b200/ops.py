@@ -82,8 +82,7 @@ class MeamConfig:
             raise ValueError(f"TACN chains longer than {_lib.MAX_CONV} convs are not supported")
 
 
-def _desc(cfg: MeamConfig, x: torch.Tensor, backward: bool) -> _lib.MeamDesc:
-    B, Cc, N, T = x.shape
+def _desc(cfg: MeamConfig, B: int, Cc: int, N: int, M: int, x_sb: int, x_sc: int, x_sm: int, backward: bool) -> _lib.MeamDesc:
     flags = cfg.flags
     if backward:
         flags |= (_lib.F_DOUT_MASKED if cfg.dout_masked else 0) | (_lib.F_X_IS_RELU if cfg.x_is_relu else 0)
@@ -91,19 +90,20 @@ def _desc(cfg: MeamConfig, x: torch.Tensor, backward: bool) -> _lib.MeamDesc:
     for i, v in enumerate(cfg.dilations):
         d.dil[i] = v
     d.precision = cfg.precision
-    d.x_sb, d.x_sc = x.stride(0), x.stride(1)
+    d.M = M
+    d.x_sb, d.x_sc, d.x_sm = x_sb, x_sc, x_sm
     return d
 
 
 def _plane_contiguous(x: torch.Tensor) -> torch.Tensor:
-    if x.stride(3) == 1 and x.stride(2) == x.shape[3] and x.data_ptr() % 16 == 0 \
-            and x.stride(0) % 4 == 0 and x.stride(1) % 4 == 0:
+    """The (n, t) plane of every channel must be one contiguous, 16-byte aligned run; the leading strides are free."""
+    if x.stride(-1) == 1 and x.stride(-2) == x.shape[-1] and x.data_ptr() % 16 == 0 \
+            and all(st % 4 == 0 for st in x.stride()[:-2]):
         return x
     return x.contiguous()
 
 
-def _param_struct(cls, tensors: Sequence[Optional[torch.Tensor]]):
-    s = cls()
+def _param_struct(s, tensors: Sequence[Optional[torch.Tensor]]):
     byname = dict(zip(SLOTS, tensors))
     for n in _lib._PARAM_FIELDS + ["sa_W", "sa_Wg", "sa_alpha"]:
         t = byname[n]
@@ -115,29 +115,56 @@ def _param_struct(cls, tensors: Sequence[Optional[torch.Tensor]]):
     return s
 
 
-class _MeamFunction(torch.autograd.Function):
+def _param_array(cls, per_component: Sequence[Sequence[Optional[torch.Tensor]]]):
+    arr = (cls * len(per_component))()
+    for m, tensors in enumerate(per_component):
+        _param_struct(arr[m], tensors)
+    return arr
+
+
+def _strides(x: torch.Tensor, layout: str):
+    """-> (M, B, C, N, x_sm, x_sb, x_sc) of a grouped input: layout "bm" is [B, M, C, N, 12] (the X of
+    MSGAT.forward, msgat.py:202: component m is X[:, m]), "mb" is [M, B, C, N, 12] (a grouped operator's output)."""
+    if layout == "bm":
+        B, M, Cc, N, T = x.shape
+        return M, B, Cc, N, x.stride(1), x.stride(0), x.stride(2)
+    M, B, Cc, N, T = x.shape
+    return M, B, Cc, N, x.stride(0), x.stride(1), x.stride(2)
+
+
+class _MeamGroupFunction(torch.autograd.Function):
+    """The MEAM-shaped operator on M same-shaped components at once (one launch per kernel for all of them):
+    x [B,M,C,N,12] or [M,B,C,N,12] -> out [M,B,O,N,12]; ``params`` = M consecutive groups of ``len(SLOTS)``."""
+
     @staticmethod
-    def forward(ctx, x, cfg: MeamConfig, adj: Optional[SparseAdjacency], *params):
+    def forward(ctx, x, layout: str, cfg: MeamConfig, adj: Optional[SparseAdjacency], *params):
         lib = _lib.get()
         if x.dtype != torch.float32:
             x = x.float()  # the path computes in fp32 whatever autocast says (SURVEY.md 5, mixed precision)
-        if x.shape[3] != 12:
+        if x.shape[-1] != 12:
             raise ValueError("msgat_b200 kernels are specialised for 12 timesteps (main.py:45)")
         x = _plane_contiguous(x)
+        M, B, Cc, N, x_sm, x_sb, x_sc = _strides(x, layout)
+        if M > _lib.MAX_GROUP:
+            raise ValueError(f"at most {_lib.MAX_GROUP} components per grouped call")
+        ns = len(SLOTS)
+        assert len(params) == M * ns
         params = tuple(None if p is None else p.detach().float().contiguous() for p in params)
-        B, Cc, N, T = x.shape
-        d = _desc(cfg, x, backward=False)
+        per = [params[m * ns:(m + 1) * ns] for m in range(M)]
+        d = _desc(cfg, B, Cc, N, M, x_sb, x_sc, x_sm, backward=False)
         nnz = adj.nnz if adj is not None else 0
         sv, sc = C.c_int64(), C.c_int64()
         _lib.check(lib.msgat_meam_sizes(C.byref(d), nnz, C.byref(sv), C.byref(sc)), "msgat_meam_sizes")
-        saved = torch.empty(max(sv.value, 4), dtype=torch.float32, device=x.device)
-        scratch = torch.empty(max(sc.value, 4), dtype=torch.float32, device=x.device)
-        out = torch.empty(B, cfg.Oc + cfg.Ot + cfg.Os, N, T, dtype=torch.float32, device=x.device)
-        ps = _param_struct(_lib.MeamParams, params)
-        _lib.check(lib.msgat_meam_forward(C.byref(d), C.byref(ps), C.byref(adj.struct) if adj is not None else None,
+        saved = torch.empty(max(sv.value, 4) * M, dtype=torch.float32, device=x.device)
+        # the scratch of the forward is not needed again: the backward allocates its own (nothing large is pinned
+        # between the two, and nothing beyond `saved` under no_grad)
+        scratch = torch.empty(max(sc.value, 4) * M, dtype=torch.float32, device=x.device)
+        out = torch.empty(M, B, cfg.Oc + cfg.Ot + cfg.Os, N, 12, dtype=torch.float32, device=x.device)
+        ps = _param_array(_lib.MeamParams, per)
+        _lib.check(lib.msgat_meam_forward(C.byref(d), ps, C.byref(adj.struct) if adj is not None else None,
                                           _lib.ptr(x), _lib.ptr(out), _lib.ptr(saved), _lib.ptr(scratch),
                                           _lib.stream_of(x)), "msgat_meam_forward")
-        ctx.cfg, ctx.adj, ctx.scratch = cfg, adj, scratch
+        ctx.cfg, ctx.adj, ctx.layout, ctx.scratch_floats = cfg, adj, layout, max(sc.value, 4) * M
         ctx.save_for_backward(x, out, saved, *[p for p in params if p is not None])
         ctx.present = [p is not None for p in params]
         return out
@@ -148,25 +175,38 @@ class _MeamFunction(torch.autograd.Function):
         x, out, saved, *rest = ctx.saved_tensors
         it = iter(rest)
         params = tuple(next(it) if pr else None for pr in ctx.present)
-        cfg, adj = ctx.cfg, ctx.adj
+        cfg, adj, layout = ctx.cfg, ctx.adj, ctx.layout
+        M, B, Cc, N, x_sm, x_sb, x_sc = _strides(x, layout)
+        ns = len(SLOTS)
         dout = dout.float().contiguous()
-        d = _desc(cfg, x, backward=True)
-        dx = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+        d = _desc(cfg, B, Cc, N, M, x_sb, x_sc, x_sm, backward=True)
+        dx = torch.empty(M, B, Cc, N, 12, dtype=torch.float32, device=x.device)
         grads = [None if p is None else torch.empty_like(p) for p in params]
-        ps = _param_struct(_lib.MeamParams, params)
-        gs = _param_struct(_lib.MeamGrads, grads)
-        _lib.check(lib.msgat_meam_backward(C.byref(d), C.byref(ps), C.byref(adj.struct) if adj is not None else None,
+        scratch = torch.empty(ctx.scratch_floats, dtype=torch.float32, device=x.device)
+        ps = _param_array(_lib.MeamParams, [params[m * ns:(m + 1) * ns] for m in range(M)])
+        gs = _param_array(_lib.MeamGrads, [grads[m * ns:(m + 1) * ns] for m in range(M)])
+        _lib.check(lib.msgat_meam_backward(C.byref(d), ps, C.byref(adj.struct) if adj is not None else None,
                                            _lib.ptr(x), _lib.ptr(out), _lib.ptr(dout), _lib.ptr(saved),
-                                           _lib.ptr(ctx.scratch), _lib.ptr(dx), C.byref(gs), _lib.stream_of(x)),
+                                           _lib.ptr(scratch), _lib.ptr(dx), gs, _lib.stream_of(x)),
                    "msgat_meam_backward")
-        return (dx, None, None, *grads)
+        if layout == "bm":
+            dx = dx.permute(1, 0, 2, 3, 4)
+        return (dx, None, None, None, *grads)
+
+
+def meam_group_op(x: torch.Tensor, layout: str, cfg: MeamConfig, adj: Optional[SparseAdjacency],
+                  params: Sequence[Dict[str, Optional[torch.Tensor]]]) -> torch.Tensor:
+    """The same layer of M components (the loop of msgat.py:203-204) as one grouped operator.
+    ``x`` is [B,M,C,N,12] (``layout="bm"``) or [M,B,C,N,12] (``"mb"``); returns [M,B,O,N,12]."""
+    flat = [p.get(n) for p in params for n in SLOTS]
+    with torch.autocast(device_type=x.device.type, enabled=False):
+        return _MeamGroupFunction.apply(x, layout, cfg, adj, *flat)
 
 
 def meam_op(x: torch.Tensor, cfg: MeamConfig, adj: Optional[SparseAdjacency],
             params: Dict[str, Optional[torch.Tensor]]) -> torch.Tensor:
-    """Run the MEAM-shaped operator; ``params`` maps slot names (``SLOTS``) to tensors."""
-    with torch.autocast(device_type=x.device.type, enabled=False):
-        return _MeamFunction.apply(x, cfg, adj, *[params.get(n) for n in SLOTS])
+    """Run the MEAM-shaped operator on one component; ``params`` maps slot names (``SLOTS``) to tensors."""
+    return meam_group_op(x.unsqueeze(0), "mb", cfg, adj, [params])[0]
 
 
 class _HeadFunction(torch.autograd.Function):

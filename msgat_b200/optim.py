@@ -20,13 +20,11 @@ class FlatAdam:
         self.grads = grads
         self.lr, self.betas, self.eps, self.weight_decay, self.grad_scale = lr, betas, eps, weight_decay, grad_scale
         flat_g = grads.flat
-        self.flat_p = torch.empty_like(flat_g)
-        o = 0
-        for p in grads.params:
+        self.flat_p = torch.zeros_like(flat_g)   # same (256-byte aligned, zero padded) layout as the gradients
+        for p, o in zip(grads.params, grads.offsets):
             n = p.numel()
             self.flat_p[o:o + n].copy_(p.data.reshape(-1))
             p.data = self.flat_p[o:o + n].view_as(p)
-            o += n
         self.m = torch.zeros_like(flat_g)
         self.v = torch.zeros_like(flat_g)
         self.step_count = torch.zeros(1, dtype=torch.int32, device=flat_g.device)

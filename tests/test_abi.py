@@ -43,7 +43,7 @@ def test_no_fallback_without_device():
 
 def test_struct_sizes_match_header():
     import ctypes
-    assert ctypes.sizeof(_lib.MeamDesc) == 4 * 8 + 4 * 4 + 4 * 2 + 8 * 2
+    assert ctypes.sizeof(_lib.MeamDesc) == 4 * 8 + 4 * 4 + 4 * 2 + 8 * 3
     assert ctypes.sizeof(_lib.MeamParams) == 8 * (11 + 8 + 3)
     assert ctypes.sizeof(_lib.Adj) == 8 + 8 * 6
     assert ctypes.sizeof(_lib.HeadDesc) == 4 * 6 + 8

@@ -28,7 +28,7 @@ def _worker(rank, world, port, ret):
     fg.zero()
     ((model(X[lo:hi]) - Y[lo:hi]) ** 2).mean().backward()
     fg.all_reduce_mean()
-    got = fg.flat.clone()
+    got = torch.cat([fg.flat[o:o + q.numel()] for q, o in zip(fg.params, fg.offsets)]).clone()
     ref_model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3))
     ref_model.load_state_dict(model.state_dict())
     ((ref_model(X) - Y) ** 2).mean().backward()

@@ -20,8 +20,19 @@ def test_kernels_match_reference_golden(case):
     out, grads, gin = run_case(G, device="cuda")
     fails, _ = check_case(G, out, grads, gin)
     if fails:  # is the reference itself that sensitive to sign flips of near-zero ReLU inputs?
+        _note(f"[relu-conditioning probe] {case}: " + "; ".join(fails))
         fails, _ = check_case(G, out, grads, gin, cond=_golden_conditioning(G))
     assert not fails, "\n".join(fails)
+
+
+def _note(msg):
+    """Cases that needed the ReLU-conditioning probe are listed in gpurun_out/parity_notes.log (when that directory exists)."""
+    import os
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "parity_notes.log"), "a") as f:
+            f.write(msg + "\n")
+    print(msg)
 
 
 def _golden_conditioning(G):
@@ -96,6 +107,8 @@ def test_full_model_matches_oracle_fp64(name, B):
     huber_loss(out, batch.Y.cuda(), 50.0).backward()
     fails = compare_with_oracle(model, out, X, ref, ref32, X64, X32, p, p32)
     if fails:  # is the reference itself that sensitive to sign flips of near-zero ReLU inputs?
+        _note(f"[relu-conditioning probe] full model {name}: " + "; ".join(fails))
+
         def run():
             q = {k: v.detach().clone().requires_grad_(v.requires_grad) for k, v in p.items()}
             Xq = batch.X.double().requires_grad_(True)
@@ -226,8 +239,8 @@ def test_static_gate_use_te_false_matches_oracle():
     batch = synthetic.make_batch(B, M, C, N, seed=5)
     res = {}
     for dt in (torch.float64, torch.float32):
-        p = {k: v.detach().to(dt).requires_grad_(v.is_floating_point() and k != "adj") for k, v in model.state_dict().items()}
-        X = batch.X.to(dt).requires_grad_(True)
+        p = {k: v.detach().clone().to(dt).requires_grad_(v.is_floating_point() and k != "adj") for k, v in model.state_dict().items()}
+        X = batch.X.detach().clone().to(dt).requires_grad_(True)
         ref = sum(O.tpc(X[:, m], p["adj"], p, f"tpcs.{m}.", O.MODEL_DILATIONS["msgat72"]) * p["W"][m] for m in range(M))
         O.huber(ref, batch.Y.to(dt), 50.0).backward()
         res[dt] = (ref.detach(), X.grad, p)
@@ -271,8 +284,8 @@ def _meam_vs_oracle(C, N, adj, B, dil, precision, floor, seed=0, res_bias_shift=
     R = torch.randn(B, 72, N, 12, generator=g)
     res = {}
     for dt in (torch.float64, torch.float32):
-        p = {k: v.detach().to(dt).requires_grad_(True) for k, v in mod.state_dict().items()}
-        xr = x.to(dt).requires_grad_(True)
+        p = {k: v.detach().clone().to(dt).requires_grad_(True) for k, v in mod.state_dict().items()}
+        xr = x.detach().clone().to(dt).requires_grad_(True)
         ref = O.meam(xr, adj.to(dt), p, "", dil)
         (ref * R.to(dt)).sum().backward()
         res[dt] = (ref.detach(), xr.grad, p)
@@ -308,8 +321,8 @@ def test_n4096_full_model_matches_oracle_fp64():
     batch = synthetic.make_batch(1, 1, 3, 4096, seed=21)
     res = {}
     for dt in (torch.float64, torch.float32):
-        p = {k: v.detach().to(dt).requires_grad_(v.is_floating_point() and k != "adj") for k, v in model.state_dict().items()}
-        X = batch.X.to(dt).requires_grad_(True)
+        p = {k: v.detach().clone().to(dt).requires_grad_(v.is_floating_point() and k != "adj") for k, v in model.state_dict().items()}
+        X = batch.X.detach().clone().to(dt).requires_grad_(True)
         ref = O.msgat(X, batch.H, batch.D, p, O.MODEL_DILATIONS["msgat72"])
         O.huber(ref, batch.Y.to(dt), 50.0).backward()
         res[dt] = (ref.detach(), X, p)
