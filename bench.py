@@ -223,7 +223,7 @@ class Run:
                                                  out_timesteps=12, use_te=True, adj=adj.clone()).to(self.dev)
         if args.precision == "tf32":
             self.model.set_precision(_lib.PREC_TF32)
-        self.fg = FlatGradients(self.model)
+        self.fg = FlatGradients(self.model, direct=True)
         self.opt = FlatAdam(self.fg, lr=1e-3, weight_decay=5e-4, grad_scale=1.0 / world)   # engine.py:106
         self.metrics = Metrics()
         self.loss_fn = lambda o, y: huber_loss(o, y, DELTA, self.metrics)                  # engine.py:56,70

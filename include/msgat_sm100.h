@@ -152,6 +152,25 @@ int msgat_head_backward(const msgat_head_desc *d, const float *x, const float *l
                         float *dx, float *d_ln_w, float *d_ln_b, float *d_fc_w, float *d_fc_b,
                         float *d_gate, float *scratch, void *stream);
 
+/* Grouped heads: the heads of all M components of MSGAT.forward (msgat.py:203-204) and the gated sum over them.
+ * x is [M,B,C,N,12] with component stride x_sm; gate [B,M,N,Tout] with batch stride gate_sb and component stride
+ * gate_sm (null = 1); head_out [M,B,N,Tout] keeps the un-gated heads for the backward; out [B,N,Tout].
+ * The parameter arguments are host arrays of M device pointers.  Backward: dx [M,B,C,N,12], d_gate with the
+ * gate's strides (may be null), scratch = M * msgat_heads_scratch_floats() floats. */
+typedef struct msgat_heads_desc {
+  int32_t B, C, N, Tout, M;
+  int32_t x_is_relu;
+  int64_t x_sm, gate_sb, gate_sm;
+} msgat_heads_desc;
+int msgat_heads_forward(const msgat_heads_desc *d, const float *x, const float *const *ln_w, const float *const *ln_b,
+                        const float *const *fc_w, const float *const *fc_b, const float *gate, float *head_out, float *out,
+                        void *stream);
+int64_t msgat_heads_scratch_floats(const msgat_heads_desc *d);
+int msgat_heads_backward(const msgat_heads_desc *d, const float *x, const float *const *ln_w, const float *const *ln_b,
+                         const float *const *fc_w, const float *gate, const float *head_out, const float *dout, float *dx,
+                         float *const *d_ln_w, float *const *d_ln_b, float *const *d_fc_w, float *const *d_fc_b, float *d_gate,
+                         float *scratch, void *stream);
+
 /* Step plumbing on the device.
  * msgat_loss_forward: Huber loss of engine.py:56 (loss.py:51-52): loss[0] = mean over n elements of
  *   0.5 r^2 if |r| <= delta else delta |r| - 0.5 delta^2, r = pred - target; dpred (may be null) = d loss / d pred;

@@ -54,10 +54,16 @@ class HeadDesc(C.Structure):
                 ("accumulate", C.c_int32), ("x_is_relu", C.c_int32), ("gate_sb", C.c_int64)]
 
 
+class HeadsDesc(C.Structure):
+    _fields_ = [("B", C.c_int32), ("C", C.c_int32), ("N", C.c_int32), ("Tout", C.c_int32), ("M", C.c_int32),
+                ("x_is_relu", C.c_int32), ("x_sm", C.c_int64), ("gate_sb", C.c_int64), ("gate_sm", C.c_int64)]
+
+
 EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_launch_count", "msgat_profile",
            "msgat_profile_report", "msgat_adj_count", "msgat_adj_fill",
            "msgat_meam_sizes", "msgat_meam_forward", "msgat_meam_backward", "msgat_head_forward",
            "msgat_head_scratch_floats", "msgat_head_backward", "msgat_tc_probe",
+           "msgat_heads_forward", "msgat_heads_scratch_floats", "msgat_heads_backward",
            "msgat_loss_scratch_bytes", "msgat_loss_forward", "msgat_loss_backward", "msgat_adam_step"]
 
 _LIB = None
@@ -69,6 +75,7 @@ def _declare(lib):
     lib.msgat_last_error.restype = C.c_char_p
     lib.msgat_device_check.restype = C.c_int
     lib.msgat_head_scratch_floats.restype = C.c_int64
+    lib.msgat_heads_scratch_floats.restype = C.c_int64
     lib.msgat_launch_count.restype = C.c_longlong
     lib.msgat_loss_scratch_bytes.restype = C.c_int64
     lib.msgat_loss_forward.argtypes = [_fp, _fp, C.c_int64, C.c_float, C.c_float, _fp, _fp, _fp, _fp, _fp]

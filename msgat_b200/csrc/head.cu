@@ -15,7 +15,32 @@ struct HeadArgs {
   float *head_out, *out;
   // backward
   const float* dout; float *dx, *d_gate, *part; int pstride;
+  int64_t dgate_sb;   // batch stride of d_gate ((n, o) contiguous)
 };
+
+// Grouped call: blockIdx.z = component m of M same-shaped heads (msgat.py:203-204).  The per-component buffers of
+// HeadArgs (component 0) lie a fixed stride further for component m; parameters come from the tables.
+struct HeadGrp {
+  int M;
+  int64_t x_sm, ho_sm, gate_sm, dx_sm, dgate_sm, part_sm;
+  const float* ln_w[MSGAT_MAX_GROUP];
+  const float* ln_b[MSGAT_MAX_GROUP];
+  const float* fc_w[MSGAT_MAX_GROUP];
+  const float* fc_b[MSGAT_MAX_GROUP];
+};
+MSGAT_DEV HeadArgs head_component(const HeadArgs& a0, const HeadGrp& g) {
+  HeadArgs a = a0;
+  if (g.M > 0) {
+    const int m = blockIdx.z;
+    a.x += m * g.x_sm; a.head_out += m * g.ho_sm;
+    if (a.gate) a.gate += m * g.gate_sm;
+    if (a.dx) a.dx += m * g.dx_sm;
+    if (a.d_gate) a.d_gate += m * g.dgate_sm;
+    if (a.part) a.part += m * g.part_sm;
+    a.ln_w = g.ln_w[m]; a.ln_b = g.ln_b[m]; a.fc_w = g.fc_w[m]; a.fc_b = g.fc_b[m];
+  }
+  return a;
+}
 
 // weights staged as Wh[c][o][t] (t contiguous): fc.weight is [Tout, 12, 1, C]
 MSGAT_DEV void stage_fc(float* Wh, const float* fc_w, int C, int Tout) {
@@ -25,7 +50,8 @@ MSGAT_DEV void stage_fc(float* Wh, const float* fc_w, int C, int Tout) {
   }
 }
 
-MSGAT_KERNEL MSGAT_LB(256, 1) k_head_fwd(HeadArgs a) {
+MSGAT_KERNEL MSGAT_LB(256, 1) k_head_fwd(HeadArgs a0, HeadGrp grp) {
+  const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, To = a.Tout, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
   float* H = reinterpret_cast<float*>(smem_raw);
@@ -51,14 +77,15 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_head_fwd(HeadArgs a) {
       const int64_t g = ((int64_t)b * a.N + n) * To + o;
       a.head_out[g] = s;
       const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * To + o] : 1.f;
-      a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
+      if (a.out) a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
     }
   }
 }
 
 #define HPAIRS 5  // (c, o) pairs of the fc weight gradient per thread
 
-MSGAT_KERNEL MSGAT_LB(256, 1) k_head_bwd(HeadArgs a) {
+MSGAT_KERNEL MSGAT_LB(256, 1) k_head_bwd(HeadArgs a0, HeadGrp grp) {
+  const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, To = a.Tout, b = blockIdx.y, T = blockDim.x, tid = threadIdx.x;
   float* H = reinterpret_cast<float*>(smem_raw);
@@ -85,7 +112,7 @@ MSGAT_KERNEL MSGAT_LB(256, 1) k_head_bwd(HeadArgs a) {
         const float d = a.dout[g];
         const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * To + o] : 1.f;
         dy = d * gt;
-        if (a.d_gate) a.d_gate[g] = d * a.head_out[g];
+        if (a.d_gate) a.d_gate[g + (int64_t)b * (a.dgate_sb - (int64_t)a.N * a.Tout)] = d * a.head_out[g];
       }
       DY[it] = dy;
     }
@@ -237,7 +264,8 @@ MSGAT_DEV void row_normalise(const Row12& x, float (&xh)[12], float& rs_out) {
   rs_out = rs;
 }
 
-MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a) {
+MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a0, HeadGrp grp) {
+  const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
@@ -309,7 +337,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a) {
     const int64_t g = ((int64_t)b * a.N + n) * 12 + o;
     a.head_out[g] = s;
     const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
-    a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
+    if (a.out) a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
   }
 }
 
@@ -347,7 +375,8 @@ MSGAT_DEV void head_ln_bwd_row(const float (&dh)[12], const Row12& xr, const flo
 // ln_w[t] * sum_n dy[n][o] xh[c][n][t] + ln_b[t] * sum_n dy[n][o], is contracted over the block's 64
 // nodes by the warp that owns the channel: the normalised rows go through a per-warp buffer,
 // 27 lanes own (node third, o quad, t quad) and combine the thirds with two shuffles.
-MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a) {
+MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
+  const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
   const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
@@ -375,7 +404,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a) {
       const float d = a.dout[g];
       const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
       dy = d * gt;
-      if (a.d_gate) a.d_gate[g] = d * a.head_out[g];
+      if (a.d_gate) a.d_gate[g + (int64_t)b * (a.dgate_sb - (int64_t)a.N * a.Tout)] = d * a.head_out[g];
     }
     DY[it] = dy;
     DYT[o * HS_NODES + nl] = dy;
@@ -491,6 +520,19 @@ static int head_check(const msgat_head_desc* d) {
   return 0;
 }
 
+// out[b,n,o] = sum_m head_out[m][b][n][o] * gate[b][m][n][o]   (msgat.py:204), components in index order
+MSGAT_KERNEL k_head_combine(const float* ho, const float* gate, float* out, int M, int B, int NT, int64_t gate_sb, int64_t gate_sm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)B * NT) return;
+  const int b = (int)(i / NT), r = (int)(i - (int64_t)b * NT);
+  float s = 0.f;
+  for (int m = 0; m < M; ++m) {
+    const float y = ho[((int64_t)m * B + b) * NT + r];
+    s += gate ? y * gate[b * gate_sb + m * gate_sm + r] : y;
+  }
+  out[i] = s;
+}
+
 extern "C" {
 
 int msgat_head_forward(const msgat_head_desc* d, const float* x, const float* ln_w, const float* ln_b, const float* fc_w,
@@ -503,10 +545,10 @@ int msgat_head_forward(const msgat_head_desc* d, const float* x, const float* ln
   a.gate_sb = d->gate_sb; a.head_out = head_out; a.out = out;
   if (head_streaming(d)) {
     size_t smem = ((size_t)d->C * HS_WP + 2 * HS_WARPS * HS_NODES * 12 + 24) * 4;
-    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B), dim3(256), smem, stream, a);
+    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B), dim3(256), smem, stream, a, HeadGrp{});
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
-    MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+    MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B), dim3(256), smem, stream, a, HeadGrp{});
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { msgat_set_error("head_forward: %s", cudaGetErrorString(e)); return -100; }
@@ -528,16 +570,17 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   a.x = x; a.C = d->C; a.N = d->N; a.Tout = d->Tout; a.ntile = (d->N + HNT - 1) / HNT; a.J = head_J(d, a.ntile);
   a.x_is_relu = d->x_is_relu; a.ln_w = ln_w; a.ln_b = ln_b; a.fc_w = fc_w; a.gate = gate; a.gate_sb = d->gate_sb;
   a.head_out = const_cast<float*>(head_out); a.dout = dout; a.dx = dx; a.d_gate = d_gate; a.part = scratch;
+  a.dgate_sb = (int64_t)d->N * d->Tout;
   const int nW = d->Tout * 12 * d->C;
   a.pstride = nW + d->Tout + 24;
   int nblk = a.J;
   if (head_streaming(d)) {
     nblk = (d->N + HS_NODES - 1) / HS_NODES;
     size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
-    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B), dim3(256), smem, stream, a);
+    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B), dim3(256), smem, stream, a, HeadGrp{});
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
-    MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B), dim3(256), smem, stream, a);
+    MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B), dim3(256), smem, stream, a, HeadGrp{});
   }
   ReduceArgs r;
   int nj = 0, tot = 0;
@@ -557,6 +600,93 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   if (tot > 0) LAUNCH_REDUCE(tot, 1, stream, r);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { msgat_set_error("head_backward: %s", cudaGetErrorString(e)); return -100; }
+  return 0;
+}
+
+
+// ---- grouped heads: all M components of MSGAT.forward (msgat.py:203-204) in one launch per kernel ----------------
+int msgat_heads_forward(const msgat_heads_desc* d, const float* x, const float* const* ln_w, const float* const* ln_b,
+                        const float* const* fc_w, const float* const* fc_b, const float* gate, float* head_out, float* out,
+                        void* stream) {
+  msgat_head_desc d1 = {d->B, d->C, d->N, d->Tout, 0, d->x_is_relu, d->gate_sb};
+  if (int rc = head_check(&d1)) return rc;
+  if (d->M < 1 || d->M > MSGAT_MAX_GROUP) { msgat_set_error("heads: 1..%d components", MSGAT_MAX_GROUP); return -42; }
+  msgat_prof_tag("@C%dO%d", d->C, d->Tout);
+  HeadArgs a = {};
+  a.x = x; a.C = d->C; a.N = d->N; a.Tout = d->Tout; a.ntile = (d->N + HNT - 1) / HNT; a.J = head_J(&d1, a.ntile);
+  a.gate = nullptr; a.head_out = head_out; a.out = nullptr;   // the gated sum over the components is k_head_combine's
+  HeadGrp g = {};
+  g.M = d->M; g.x_sm = d->x_sm; g.ho_sm = (int64_t)d->B * d->N * d->Tout;
+  for (int m = 0; m < d->M; ++m) { g.ln_w[m] = ln_w[m]; g.ln_b[m] = ln_b[m]; g.fc_w[m] = fc_w[m]; g.fc_b[m] = fc_b[m]; }
+  if (head_streaming(&d1)) {
+    size_t smem = ((size_t)d->C * HS_WP + 2 * HS_WARPS * HS_NODES * 12 + 24) * 4;
+    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B, d->M), dim3(256), smem, stream, a, g);
+  } else {
+    size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
+    MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B, d->M), dim3(256), smem, stream, a, g);
+  }
+  const int64_t n = (int64_t)d->B * d->N * d->Tout;
+  int blocks = (int)((n + 255) / 256);
+  MSGAT_LAUNCH(k_head_combine, dim3(blocks), dim3(256), 0, stream, (const float*)head_out, gate, out, d->M, d->B, d->N * d->Tout,
+               d->gate_sb, d->gate_sm);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { msgat_set_error("heads_forward: %s", cudaGetErrorString(e)); return -100; }
+  return 0;
+}
+
+int64_t msgat_heads_scratch_floats(const msgat_heads_desc* d) {
+  msgat_head_desc d1 = {d->B, d->C, d->N, d->Tout, 0, d->x_is_relu, d->gate_sb};
+  return msgat_head_scratch_floats(&d1);   // per component
+}
+
+int msgat_heads_backward(const msgat_heads_desc* d, const float* x, const float* const* ln_w, const float* const* ln_b,
+                         const float* const* fc_w, const float* gate, const float* head_out, const float* dout, float* dx,
+                         float* const* d_ln_w, float* const* d_ln_b, float* const* d_fc_w, float* const* d_fc_b, float* d_gate,
+                         float* scratch, void* stream) {
+  msgat_head_desc d1 = {d->B, d->C, d->N, d->Tout, 0, d->x_is_relu, d->gate_sb};
+  if (int rc = head_check(&d1)) return rc;
+  if (d->M < 1 || d->M > MSGAT_MAX_GROUP) { msgat_set_error("heads: 1..%d components", MSGAT_MAX_GROUP); return -42; }
+  msgat_prof_tag("@C%dO%d", d->C, d->Tout);
+  HeadArgs a = {};
+  a.x = x; a.C = d->C; a.N = d->N; a.Tout = d->Tout; a.ntile = (d->N + HNT - 1) / HNT; a.J = head_J(&d1, a.ntile);
+  a.x_is_relu = d->x_is_relu; a.gate = gate; a.gate_sb = d->gate_sb;
+  a.head_out = const_cast<float*>(head_out); a.dout = dout; a.dx = dx; a.d_gate = d_gate; a.part = scratch;
+  a.dgate_sb = d->gate_sb;   // d_gate has the gate's own [B, M, N, Tout] strides
+  const int nW = d->Tout * 12 * d->C;
+  a.pstride = nW + d->Tout + 24;
+  const int64_t part_sm = msgat_head_scratch_floats(&d1);
+  HeadGrp g = {};
+  g.M = d->M; g.x_sm = d->x_sm; g.ho_sm = (int64_t)d->B * d->N * d->Tout; g.gate_sm = d->gate_sm;
+  g.dx_sm = (int64_t)d->B * d->C * d->N * 12; g.dgate_sm = d->gate_sm; g.part_sm = part_sm;
+  for (int m = 0; m < d->M; ++m) { g.ln_w[m] = ln_w[m]; g.ln_b[m] = ln_b[m]; g.fc_w[m] = fc_w[m]; g.fc_b[m] = nullptr; }
+  int nblk = a.J;
+  if (head_streaming(&d1)) {
+    nblk = (d->N + HS_NODES - 1) / HS_NODES;
+    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
+    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B, d->M), dim3(256), smem, stream, a, g);
+  } else {
+    size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
+    MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B, d->M), dim3(256), smem, stream, a, g);
+  }
+  ReduceArgs r;
+  int nj = 0, tot = 0;
+  const int nparts = nblk * d->B;
+  auto add = [&](float* const* dst, const float* src, int n) {
+    if (!dst || !dst[0]) return;
+    RJob jb = {};
+    for (int m = 0; m < d->M; ++m) jb.dst[m] = dst[m];
+    jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = 1; jb.doff = 0; jb.pstride = (int64_t)a.pstride; jb.f64 = 0;
+    r.j[nj] = jb;
+    r.starts[nj] = tot; tot += n; ++nj;
+  };
+  add(d_fc_w, scratch, nW);
+  add(d_fc_b, scratch + nW, d->Tout);
+  add(d_ln_w, scratch + nW + d->Tout, 12);
+  add(d_ln_b, scratch + nW + d->Tout + 12, 12);
+  r.starts[nj] = tot; r.njobs = nj; r.sc_sm = part_sm;
+  if (tot > 0) LAUNCH_REDUCE(tot, d->M, stream, r);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { msgat_set_error("heads_backward: %s", cudaGetErrorString(e)); return -100; }
   return 0;
 }
 

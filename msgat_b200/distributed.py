@@ -15,7 +15,10 @@ class FlatGradients:
 
     ALIGN = 64  # floats: every parameter starts on a 256-byte boundary (the kernels read parameters with 128-bit loads)
 
-    def __init__(self, model: torch.nn.Module):
+    def __init__(self, model: torch.nn.Module, direct: bool = False):
+        """``direct=True`` registers every parameter's slice of the buffer as its gradient SINK: the backward kernels
+        of this package then write the gradient there themselves and hand autograd nothing to accumulate (~200 tiny
+        add kernels per step otherwise).  The sink is overwritten, not accumulated: one backward per ``zero()``."""
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.offsets = []
         n = 0
@@ -26,6 +29,8 @@ class FlatGradients:
         self.flat = torch.zeros(n, dtype=torch.float32, device=dev)
         for p, o in zip(self.params, self.offsets):
             p.grad = self.flat[o:o + p.numel()].view_as(p)
+            if direct:
+                p._msgat_grad_sink = p.grad
 
     def zero(self):
         self.flat.zero_()

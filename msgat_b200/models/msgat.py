@@ -221,9 +221,9 @@ class MSGAT(nn.Module):
         M = len(self.tpcs)
         if self.te is not None:
             G = self.te(H, D).float()  # [B, M, N, Tout]
-            gates = [G[:, m] for m in range(M)]
         else:
-            gates = [self.W[m].unsqueeze(0).expand(X.shape[0], -1, -1) for m in range(M)]
+            G = self.W.unsqueeze(0).expand(X.shape[0], -1, -1, -1)
+        gates = [G[:, m] for m in range(M)]
         out = None
         if self._groupable():
             # The M components are independent up to the gated sum (msgat.py:203-204) and have the same shape:
@@ -239,9 +239,8 @@ class MSGAT(nn.Module):
                 layout = "mb"
             if depth == 0:
                 feats = X.transpose(0, 1)
-            for m, tpc in enumerate(self.tpcs):
-                out = tpc.head(feats[m], gate=gates[m], acc=out)
-            return out
+            return ops.heads_op(feats, G, [t.ln.weight for t in self.tpcs], [t.ln.bias for t in self.tpcs],
+                                [t.fc.weight for t in self.tpcs], [t.fc.bias for t in self.tpcs], x_is_relu=depth > 0)
         for m, tpc in enumerate(self.tpcs):
             out = tpc(X[:, m], self.adj, gate=gates[m], acc=out)
         return out

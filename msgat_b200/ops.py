@@ -72,6 +72,14 @@ def sparse_adjacency(adj: torch.Tensor) -> SparseAdjacency:
     return sp
 
 
+def _sink_of(p):
+    """The registered gradient sink of a parameter (see ``distributed.FlatGradients``), if it matches the parameter."""
+    sk = getattr(p, "_msgat_grad_sink", None) if p is not None else None
+    if sk is None or sk.shape != p.shape or sk.dtype != torch.float32 or sk.device != p.device or not sk.is_contiguous():
+        return None
+    return sk
+
+
 class MeamConfig:
     def __init__(self, Oc: int, Ot: int, Os: int, flags: int, dilations: Sequence[int] = (), precision: int = 0,
                  dout_masked: bool = False, x_is_relu: bool = False):
@@ -149,6 +157,7 @@ class _MeamGroupFunction(torch.autograd.Function):
             raise ValueError(f"at most {_lib.MAX_GROUP} components per grouped call")
         ns = len(SLOTS)
         assert len(params) == M * ns
+        ctx.sinks = [_sink_of(p) for p in params]
         params = tuple(None if p is None else p.detach().float().contiguous() for p in params)
         per = [params[m * ns:(m + 1) * ns] for m in range(M)]
         d = _desc(cfg, B, Cc, N, M, x_sb, x_sc, x_sm, backward=False)
@@ -181,7 +190,9 @@ class _MeamGroupFunction(torch.autograd.Function):
         dout = dout.float().contiguous()
         d = _desc(cfg, B, Cc, N, M, x_sb, x_sc, x_sm, backward=True)
         dx = torch.empty(M, B, Cc, N, 12, dtype=torch.float32, device=x.device)
-        grads = [None if p is None else torch.empty_like(p) for p in params]
+        # a parameter with a registered gradient sink (distributed.FlatGradients(direct=True)) gets its gradient
+        # written straight into the flat buffer by the kernels; autograd is handed None for it (no add kernel)
+        grads = [None if p is None else (sk if sk is not None else torch.empty_like(p)) for p, sk in zip(params, ctx.sinks)]
         scratch = torch.empty(ctx.scratch_floats, dtype=torch.float32, device=x.device)
         ps = _param_array(_lib.MeamParams, [params[m * ns:(m + 1) * ns] for m in range(M)])
         gs = _param_array(_lib.MeamGrads, [grads[m * ns:(m + 1) * ns] for m in range(M)])
@@ -191,7 +202,7 @@ class _MeamGroupFunction(torch.autograd.Function):
                    "msgat_meam_backward")
         if layout == "bm":
             dx = dx.permute(1, 0, 2, 3, 4)
-        return (dx, None, None, None, *grads)
+        return (dx, None, None, None, *[None if sk is not None else g for g, sk in zip(grads, ctx.sinks)])
 
 
 def meam_group_op(x: torch.Tensor, layout: str, cfg: MeamConfig, adj: Optional[SparseAdjacency],
@@ -218,6 +229,7 @@ class _HeadFunction(torch.autograd.Function):
         if T != 12:
             raise ValueError("msgat_b200 kernels are specialised for 12 timesteps (main.py:45)")
         Tout = fc_w.shape[0]
+        ctx.sinks = [_sink_of(t) for t in (ln_w, ln_b, fc_w, fc_b)]
         ln_w, ln_b, fc_w, fc_b = (t.detach().float().contiguous() for t in (ln_w, ln_b, fc_w, fc_b))
         if gate is not None:
             gate = gate.detach().float()
@@ -246,8 +258,11 @@ class _HeadFunction(torch.autograd.Function):
         Tout = fc_w.shape[0]
         d = _lib.HeadDesc(B, Cc, N, Tout, 0, 1 if ctx.x_is_relu else 0, 0 if gate is None else gate.stride(0))
         dx = torch.empty_like(x)
-        g_lnw, g_lnb, g_fcw = torch.empty_like(ln_w), torch.empty_like(ln_b), torch.empty_like(fc_w)
-        g_fcb = torch.empty(Tout, dtype=torch.float32, device=x.device)
+        sk = ctx.sinks
+        g_lnw = sk[0] if sk[0] is not None else torch.empty_like(ln_w)
+        g_lnb = sk[1] if sk[1] is not None else torch.empty_like(ln_b)
+        g_fcw = sk[2] if sk[2] is not None else torch.empty_like(fc_w)
+        g_fcb = sk[3] if sk[3] is not None else torch.empty(Tout, dtype=torch.float32, device=x.device)
         g_gate = torch.empty_like(head_out) if ctx.gate_needs_grad else None
         scratch = torch.empty(max(int(lib.msgat_head_scratch_floats(C.byref(d))), 4), dtype=torch.float32,
                               device=x.device)
@@ -256,10 +271,87 @@ class _HeadFunction(torch.autograd.Function):
                                            _lib.ptr(g_lnw), _lib.ptr(g_lnb), _lib.ptr(g_fcw), _lib.ptr(g_fcb),
                                            _lib.ptr(g_gate), _lib.ptr(scratch), _lib.stream_of(x)),
                    "msgat_head_backward")
-        return dx, g_lnw, g_lnb, g_fcw, g_fcb, g_gate, (dout if ctx.has_acc else None), None
+        ret = [None if k is not None else g for g, k in zip((g_lnw, g_lnb, g_fcw, g_fcb), sk)]
+        return (dx, *ret, g_gate, (dout if ctx.has_acc else None), None)
 
 
 def head_op(x, ln_w, ln_b, fc_w, fc_b, gate=None, acc=None, x_is_relu=False):
     """TPC head + gate (+ running sum over components): returns ``acc + head(x) * gate``."""
     with torch.autocast(device_type=x.device.type, enabled=False):
         return _HeadFunction.apply(x, ln_w, ln_b, fc_w, fc_b, gate, acc, x_is_relu)
+
+
+def _ptr_array(tensors):
+    return (C.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+
+
+class _HeadsFunction(torch.autograd.Function):
+    """The heads of all M components and the gated sum over them (msgat.py:158-160, 203-204) as grouped launches:
+    x [M,B,C,N,12], gate [B,M,N,Tout] -> [B,N,Tout]; ``params`` = ln_w * M, ln_b * M, fc_w * M, fc_b * M."""
+
+    @staticmethod
+    def forward(ctx, x, gate, x_is_relu, *params):
+        lib = _lib.get()
+        x = x.float().contiguous()
+        M, B, Cc, N, T = x.shape
+        if T != 12:
+            raise ValueError("msgat_b200 kernels are specialised for 12 timesteps (main.py:45)")
+        ctx.sinks = [_sink_of(t) for t in params]
+        params = [t.detach().float().contiguous() for t in params]
+        ln_w, ln_b, fc_w, fc_b = params[:M], params[M:2 * M], params[2 * M:3 * M], params[3 * M:]
+        Tout = fc_w[0].shape[0]
+        if gate is not None:
+            gate = gate.detach().float()
+            if gate.stride(3) != 1 or gate.stride(2) != Tout or gate.stride(0) == 0:
+                gate = gate.contiguous()
+        d = _lib.HeadsDesc(B, Cc, N, Tout, M, 1 if x_is_relu else 0, x.stride(0),
+                           0 if gate is None else gate.stride(0), 0 if gate is None else gate.stride(1))
+        head_out = torch.empty(M, B, N, Tout, dtype=torch.float32, device=x.device)
+        out = torch.empty(B, N, Tout, dtype=torch.float32, device=x.device)
+        _lib.check(lib.msgat_heads_forward(C.byref(d), _lib.ptr(x), _ptr_array(ln_w), _ptr_array(ln_b), _ptr_array(fc_w),
+                                           _ptr_array(fc_b), _lib.ptr(gate), _lib.ptr(head_out), _lib.ptr(out),
+                                           _lib.stream_of(x)), "msgat_heads_forward")
+        ctx.save_for_backward(x, head_out, *([gate] if gate is not None else []), *ln_w, *ln_b, *fc_w)
+        ctx.has_gate, ctx.x_is_relu, ctx.M = gate is not None, x_is_relu, M
+        ctx.gate_needs_grad = gate is not None and ctx.needs_input_grad[1]
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _lib.get()
+        M = ctx.M
+        x, head_out, *rest = ctx.saved_tensors
+        gate = rest.pop(0) if ctx.has_gate else None
+        ln_w, ln_b, fc_w = rest[:M], rest[M:2 * M], rest[2 * M:3 * M]
+        dout = dout.float().contiguous()
+        _, B, Cc, N, T = x.shape
+        Tout = fc_w[0].shape[0]
+        d = _lib.HeadsDesc(B, Cc, N, Tout, M, 1 if ctx.x_is_relu else 0, x.stride(0),
+                           0 if gate is None else gate.stride(0), 0 if gate is None else gate.stride(1))
+        dx = torch.empty_like(x)
+        sk = ctx.sinks
+        like = list(ln_w) + list(ln_b) + list(fc_w) + [torch.empty(0)] * M
+        grads = []
+        for i in range(4 * M):
+            if sk[i] is not None:
+                grads.append(sk[i])
+            elif i >= 3 * M:
+                grads.append(torch.empty(Tout, dtype=torch.float32, device=x.device))
+            else:
+                grads.append(torch.empty_like(like[i]))
+        g_gate = torch.empty_like(gate) if ctx.gate_needs_grad else None   # same [B,M,N,Tout] strides as the gate
+        if g_gate is not None and g_gate.stride() != gate.stride():
+            raise RuntimeError("heads backward: gate must be dense")
+        scratch = torch.empty(max(int(lib.msgat_heads_scratch_floats(C.byref(d))), 4) * M, dtype=torch.float32, device=x.device)
+        _lib.check(lib.msgat_heads_backward(C.byref(d), _lib.ptr(x), _ptr_array(ln_w), _ptr_array(ln_b), _ptr_array(fc_w),
+                                            _lib.ptr(gate), _lib.ptr(head_out), _lib.ptr(dout), _lib.ptr(dx),
+                                            _ptr_array(grads[:M]), _ptr_array(grads[M:2 * M]), _ptr_array(grads[2 * M:3 * M]),
+                                            _ptr_array(grads[3 * M:]), _lib.ptr(g_gate), _lib.ptr(scratch),
+                                            _lib.stream_of(x)), "msgat_heads_backward")
+        return (dx, g_gate, None, *[None if k is not None else g for g, k in zip(grads, sk)])
+
+
+def heads_op(x, gate, ln_w, ln_b, fc_w, fc_b, x_is_relu=False):
+    """``sum_m head_m(x[m]) * gate[:, m]`` for the M components at once; the parameter arguments are lists of M."""
+    with torch.autocast(device_type=x.device.type, enabled=False):
+        return _HeadsFunction.apply(x, gate, x_is_relu, *ln_w, *ln_b, *fc_w, *fc_b)
