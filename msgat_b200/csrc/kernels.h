@@ -35,6 +35,11 @@ int launch_l1_bwd(const Plan& p, const msgat_meam_params* prm, const msgat_adj* 
                   const float* saved, float* DH, float* DXR, float* DA, float* delta, float* dSnz, float* dMc_part,
                   float* dPt_part, float* Qpart, void* stream);
 int launch_l1_wfin(const Plan& p, const msgat_meam_params* prm, const msgat_meam_grads* g, const float* Qpart, int nparts, void* stream);
+// layer-2 pipelined tcgen05 kernels, l2_*.cu (C % 8 == 0, full MEAM, two convs), natively grouped
+bool l2_fwd_supported(const Plan& p);
+int launch_l2_mix(const Plan& p, const msgat_meam_params* prm, const float* x, float* saved, float* scratch, void* stream);
+int launch_l2_out(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out, float* saved,
+                  void* stream);
 // tensor-core (tcgen05 kind::tf32) kernels, tc_*.cu: MSGAT_PREC_TF32 on the layer-2 MEAM shape
 bool tc_apply_supported(const Plan& p);
 bool tc_apply3_supported(const Plan& p);

@@ -1,0 +1,621 @@
+// l2_fwd.cu -- forward of a layer-2 MEAM (msgat.py:121-131, C % 8 == 0) on the pipelined tcgen05 skeleton of
+// l2_common.cuh, as two passes over x (the channel attention and the temporal attention need per-sample reductions
+// over ALL nodes before anything can be applied, attention.py:65,92):
+//   k_l2_mix  h = LayerNorm_T(x);  [a_now; a_past; Z; q_s; q_t] = [W1now; W1past; Ws; alpha_s; alpha_t] h
+//             (first-conv taps BEFORE the temporal mix, which commutes with channel mixing; Z = Ws h is what the
+//             sparse spatial aggregation gathers, msgat.py:27 commuted in front of it; the two queries of
+//             attention.py:33,63 ride along as two more output columns) + per-tile partials of the channel query
+//             q_c = sum_n alpha_n h (attention.py:92).  Everything here is independent of the per-sample softmaxes.
+//   k_l2_out  (below) reads x again with the per-sample Mc = W1x1 Pc and Pt in hand.
+#include <stdlib.h>
+#include "l2_common.cuh"
+
+struct L2MixArgs {
+  const float* x; int64_t x_sb, x_sc, x_sm, sv_sm, sc_sm;
+  int B, C, N, b, ntile, TPC, KC, fp32_grade;
+  msgat_meam_params prm[MSGAT_MAX_GROUP];
+  float *qs, *qt, *Z, *A2;   // saved (component 0)
+  float* pqc;                // scratch: per-tile partials of q_c, fp32 [B][ntile][C][12]
+};
+
+// shared memory: WT hi | WT lo ([C][96] B operands) | ring of NS operand chunks (hi | lo, [KC][128]) |
+//                ring of NR raw chunks ([KC][8 nodes][12]) | LW[24] | barriers
+#define L2M_NS 4
+#define L2M_NR 6
+#define L2_RAW_ROW (L2_NT * 48 + 32)   // bytes between the raw rows of a chunk: 8 nodes x 12 floats (contiguous in HBM) + 32 of padding,
+                                     // so that the four rows a quarter-warp reads start 8 banks apart
+static size_t l2_mix_smem(int C, int KC) {
+  return (size_t)2 * C * 96 * 4 + (size_t)L2M_NS * 2 * KC * 128 * 4 + (size_t)L2M_NR * KC * L2_RAW_ROW + 24 * 4 +
+         (2 * L2M_NS + 2 * L2M_NR + 4) * L2_BAR_BYTES + 16 + 1024;
+}
+
+template <int BW>
+MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int C = a.C, b3 = 3 * a.b, KC = a.KC, nchunk = C / KC, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
+  const msgat_meam_params& PM = a.prm[m];
+  const uint32_t cbW = (uint32_t)C * 128u, cbA = (uint32_t)KC * 128u, chunk_bytes = (uint32_t)KC * 128u * 4u;
+  unsigned char* WH = smem;
+  unsigned char* WL = WH + 3 * cbW;
+  unsigned char* RING = WL + 3 * cbW;                                  // chunk i: hi at RING + i * 2 * chunk_bytes, lo after it
+  unsigned char* RAW = RING + L2M_NS * 2 * chunk_bytes;                 // raw chunk i at RAW + i * raw_bytes
+  const uint32_t raw_bytes = (uint32_t)KC * L2_RAW_ROW;
+  float* LW = reinterpret_cast<float*>(RAW + L2M_NR * raw_bytes);
+  unsigned char* BAR = reinterpret_cast<unsigned char*>(LW + 24);
+  const uint32_t bar0 = smem_u32(BAR);
+  auto FULL = [&](int i) { return bar0 + (uint32_t)i * L2_BAR_BYTES; };
+  auto EMPTY = [&](int i) { return bar0 + (uint32_t)(L2M_NS + i) * L2_BAR_BYTES; };
+  auto TFULL = [&](int i) { return bar0 + (uint32_t)(2 * L2M_NS + i) * L2_BAR_BYTES; };
+  auto TEMPTY = [&](int i) { return bar0 + (uint32_t)(2 * L2M_NS + 2 + i) * L2_BAR_BYTES; };
+  auto RFULL = [&](int i) { return bar0 + (uint32_t)(2 * L2M_NS + 4 + i) * L2_BAR_BYTES; };
+  auto REMPTY = [&](int i) { return bar0 + (uint32_t)(2 * L2M_NS + 4 + L2M_NR + i) * L2_BAR_BYTES; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(BAR + (2 * L2M_NS + 2 * L2M_NR + 4) * L2_BAR_BYTES);
+
+  // ---- one-time staging: B operand [k = input channel][n = output column], n contiguous, hi / lo, zero padded.
+  // columns 0..b-1 W1now, b..2b-1 W1past, 2b..3b-1 Ws, 3b alpha_s, 3b+1 alpha_t
+  for (int i = tid; i < C * 96; i += L2_THREADS) {
+    const int k = i / 96, n = i - k * 96;
+    float w = 0.f;
+    if (n < a.b) w = PM.conv_w[0][(n * C + k) * 2 + 1];
+    else if (n < 2 * a.b) w = PM.conv_w[0][((n - a.b) * C + k) * 2 + 0];
+    else if (n < b3) w = PM.sa_W[(n - 2 * a.b) * C + k];
+    else if (n == b3) w = PM.sa_alpha[k];
+    else if (n == b3 + 1) w = PM.ta_alpha[k];
+    l2_split1(WH, WL, sw128b32_off(k, n, cbW), w);
+  }
+  if (tid < 12) { LW[tid] = PM.ln_w[tid]; LW[12 + tid] = PM.ln_b[tid]; }
+  if (tid == 0) {
+    for (int i = 0; i < L2M_NS; ++i) { mbar_init(FULL(i), L2_CONV_WARPS); mbar_init(EMPTY(i), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(TFULL(i), 1); mbar_init(TEMPTY(i), L2_EPI_WARPS); }
+    for (int i = 0; i < L2M_NR; ++i) { mbar_init(RFULL(i), 1); mbar_init(REMPTY(i), L2_CONV_WARPS); }
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+  fence_smem_to_async();
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tm = *tmem_slot;
+  const int ncol = ((b3 + 2) + 15) & ~15;            // accumulator columns (N of the MMA)
+  const int total = a.B * a.ntile, t_lo = blockIdx.x * a.TPC, t_hi = t_lo + a.TPC < total ? t_lo + a.TPC : total;
+  const int64_t cs = (int64_t)a.N * 12;
+
+  if (warp == L2_PROD_WARP) {
+    // ================= producer: bulk copies of the raw rows, one chunk = KC channel rows of the tile =================
+    const float* xm = a.x + (int64_t)m * a.x_sm;
+    int q = 0;
+    for (int tile = t_lo; tile < t_hi; ++tile) {
+      const int bi = tile / a.ntile, n0 = (tile - bi * a.ntile) * L2_NT;
+      const int nv = a.N - n0 < L2_NT ? a.N - n0 : L2_NT;
+      for (int ch = 0; ch < nchunk; ++ch, ++q) {
+        const int rs = q % L2M_NR, use = q / L2M_NR;
+        if (use > 0) mbar_wait(REMPTY(rs), (uint32_t)((use - 1) & 1));   // every converter warp has read this slot
+        if (lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(KC * nv * 48));
+        if (lane < KC)
+          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)lane * L2_RAW_ROW,
+                   xm + (int64_t)bi * a.x_sb + (int64_t)(ch * KC + lane) * a.x_sc + (int64_t)n0 * 12, (uint32_t)(nv * 48), RFULL(rs));
+      }
+    }
+  } else if (warp >= L2_CONV_WARP0) {
+    // ================= converters =================
+    const L2Conv cv = l2_conv_thread();
+    const bool rowthr = cv.kl < KC;
+    const L2RowOff ro = l2_row_off(cbA, cv.kl, cv.nl);
+    float* pq = a.pqc + (int64_t)m * a.sc_sm;
+    const int nq = (t_hi - t_lo) * nchunk;
+    for (int q = cv.grp; q < nq; q += L2_CONV_GROUPS) {
+      {
+        const int tile = t_lo + q / nchunk, ch = q - (q / nchunk) * nchunk;
+        const int bi = tile / a.ntile, tl = tile - bi * a.ntile, n = tl * L2_NT + cv.nl;
+        const float an = (rowthr && n < a.N) ? __ldg(PM.ca_alpha + n) : 0.f;
+        const int rs = q % L2M_NR, ruse = q / L2M_NR;
+        mbar_wait(RFULL(rs), (uint32_t)(ruse & 1));
+        float4 ra = f4zero(), rb = f4zero(), rd = f4zero();
+        if (rowthr && n < a.N) {   // nodes beyond N were not copied: their rows are zero, not stale shared memory
+          const float* r = reinterpret_cast<const float*>(RAW + (size_t)rs * raw_bytes + (size_t)cv.kl * L2_RAW_ROW) + cv.nl * 12;
+          ra = ld4(r); rb = ld4(r + 4); rd = ld4(r + 8);
+        }
+        const int slot = q % L2M_NS, use = q / L2M_NS;
+        if (rowthr && n < a.N) l2_row_ln(ra, rb, rd, LW);
+        // channel-query partial of the tile: sum over its 8 nodes (lanes that differ in bits 2..4), fp32; k_small adds the tiles in fp64
+        {
+          const float v[12] = {an * ra.x, an * ra.y, an * ra.z, an * ra.w, an * rb.x, an * rb.y, an * rb.z, an * rb.w,
+                               an * rd.x, an * rd.y, an * rd.z, an * rd.w};
+          float r0, r1;
+          l2_reduce12_nodes(v, lane, r0, r1);
+          if (rowthr) {
+            const int e = ((lane & 4) ? 6 : 0) + ((lane & 8) ? 3 : 0) + ((lane & 16) ? 2 : 0);
+            float* d = pq + (((int64_t)bi * a.ntile + tl) * C + ch * KC + cv.kl) * 12 + e;
+            d[0] = r0;
+            if (!(lane & 16)) d[1] = r1;
+          }
+        }
+        if (use > 0) mbar_wait(EMPTY(slot), (uint32_t)((use - 1) & 1));   // the MMAs that read this slot have retired
+        unsigned char* hi = RING + (size_t)slot * 2 * chunk_bytes;
+        if (rowthr) l2_store_row(hi, hi + chunk_bytes, ro, cv.nl & 1, ra, rb, rd);
+        // The raw slot goes back to the producer only now that the rows' VALUES have been used.  Arriving right after
+        // issuing the shared-memory loads is not enough: measured on the B200, the next bulk copy (async proxy) could
+        // overwrite the first bytes of a row before an earlier generic-proxy load of another lane had been performed
+        // (2-3 nodes of a tile wrong in ~3 % of the launches).
+        __syncwarp();
+        if (lane == 0) mbar_arrive(REMPTY(rs));
+        fence_smem_to_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(FULL(slot));
+      }
+    }
+  } else if (warp == L2_MMA_WARP) {
+    // ================= MMA issue (one thread) =================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(128, ncol, 1, 1);
+      const uint64_t dWH = umma_desc(smem_u32(WH), cbW, 512u, 1), dWL = umma_desc(smem_u32(WL), cbW, 512u, 1);
+      int q = 0, it = 0;
+      for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+        const int buf = it & 1, ut = it >> 1;
+        const uint32_t dm = tm + (uint32_t)buf * 256u, dsm = dm + 128u;
+        if (ut > 0) mbar_wait(TEMPTY(buf), (uint32_t)((ut - 1) & 1));       // the epilogue has drained this accumulator set
+        tc_fence_after_sync();
+        for (int ch = 0; ch < nchunk; ++ch, ++q) {
+          const int slot = q % L2M_NS, use = q / L2M_NS;
+          mbar_wait(FULL(slot), (uint32_t)(use & 1));
+          tc_fence_after_sync();
+          const uint32_t base = smem_u32(RING + (size_t)slot * 2 * chunk_bytes);
+          const uint64_t dAH = umma_desc(base, cbA, 512u, 1), dAL = umma_desc(base + chunk_bytes, cbA, 512u, 1);
+          for (int ks = 0; ks < KC / 8; ++ks) {
+            const uint32_t first = (ch == 0 && ks == 0) ? 0u : 1u;
+            l2_mma(dm, dsm, dAH, dAL, dWH, dWL, (uint32_t)ks, (uint32_t)(ch * (KC / 8) + ks), idesc, first, first, a.fp32_grade);
+          }
+          umma_commit(EMPTY(slot));
+        }
+        umma_commit(TFULL(buf));
+      }
+    }
+  } else {
+    // ================= epilogue: TMEM lane = 16 * (node & 1) + t within the quarter's two nodes; the two warps of a
+    // quarter take the even / odd groups of 8 columns.  Straight-line code: one warp per scheduler has to keep up
+    // with the tensor core, so no per-column branches and no 64-bit multiplies (BW is a template parameter).
+    const int nj = lane >> 4, t = lane & 15, qtr = warp & 3, par = warp >> 2;
+    const uint32_t lane_base = (uint32_t)(qtr * 32) << 16;
+    const int64_t mo = (int64_t)m * a.sv_sm;
+    int it = 0;
+    for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+      const int buf = it & 1, ut = it >> 1;
+      const int bi = tile / a.ntile, n = (tile - bi * a.ntile) * L2_NT + qtr * 2 + nj;
+      const bool live = t < 12 && n < a.N;
+      float* A2r = a.A2 + mo + ((int64_t)bi * 2 * BW * a.N + n) * 12 + t;     // [B][2b][N][12]
+      float* Zr = a.Z + mo + ((int64_t)bi * BW * a.N + n) * 12 + t;           // [B][b][N][12]
+      float* qsr = a.qs + mo + ((int64_t)bi * a.N + n) * 12 + t;
+      float* qtr_p = a.qt + mo + ((int64_t)bi * a.N + n) * 12 + t;
+      mbar_wait(TFULL(buf), (uint32_t)(ut & 1));
+      tc_fence_after_sync();
+      const uint32_t dm = tm + (uint32_t)buf * 256u + lane_base, dsm = dm + 128u;
+      MSGAT_UNROLL
+      for (int g = 0; g < (3 * BW + 2 + 7) / 8; ++g) {
+        if ((g & 1) != par) continue;   // warp-uniform
+        float v[8];
+        l2_ld8(dm + g * 8, dsm + g * 8, a.fp32_grade, v);
+        if (live) {
+          MSGAT_UNROLL
+          for (int j = 0; j < 8; ++j) {
+            const int c = g * 8 + j;   // compile-time
+            if (c < 2 * BW) A2r[(int64_t)c * cs] = v[j];
+            else if (c < 3 * BW) Zr[(int64_t)(c - 2 * BW) * cs] = v[j];
+            else if (c == 3 * BW) *qsr = v[j];
+            else if (c == 3 * BW + 1) *qtr_p = v[j];
+          }
+        }
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(TEMPTY(buf));
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tm, 512);
+}
+
+bool l2_fwd_supported(const Plan& p) {
+  const char* off = getenv("MSGAT_L2_DISABLE");  // test switch: bit 0 = forward kernels
+  if (off && (atoi(off) & 1)) return false;
+  const int full = MSGAT_F_LN | MSGAT_F_RES | MSGAT_F_RELU | MSGAT_F_CMIX | MSGAT_F_SMIX;
+  const int b = p.Oc;
+  return (p.flags & full) == full && p.n_conv == 2 && p.s_pre && p.Oc == p.Ot && p.Ot == p.Os && b % 8 == 0 && b >= 8 && b <= 24 &&
+         p.C % 8 == 0 && p.C >= 8 && p.C <= 72 && p.O == 3 * b && p.dil[0] >= 1 && p.dil[0] < 12 && p.dil[1] >= 1 && p.dil[1] < 12;
+}
+
+static void l2_partition(const Plan& p, int& G, int& TPC) {
+  const int total = p.B * ((p.N + L2_NT - 1) / L2_NT);
+  G = msgat_sm_count() / p.M;
+  { const char* e = getenv("MSGAT_L2_MAXCTA"); if (e && atoi(e) > 0 && atoi(e) < G) G = atoi(e); }   // test switch: CTAs that span samples
+  if (G < 1) G = 1;
+  if (G > total) G = total;
+  TPC = (total + G - 1) / G;
+  G = (total + TPC - 1) / TPC;
+}
+
+int launch_l2_mix(const Plan& p, const msgat_meam_params* prm, const float* x, float* saved, float* scratch, void* stream) {
+  L2MixArgs a;
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.sv_sm = p.saved_total; a.sc_sm = p.scratch_sm;
+  a.B = p.B; a.C = p.C; a.N = p.N; a.b = p.Oc; a.ntile = (p.N + L2_NT - 1) / L2_NT; a.KC = l2_chunk_rows(p.C);
+  // always error-compensated: the queries feed softmaxes whose scores reach O(100) with trained weights, and this
+  // pass is bound by shared memory and HBM, not by the tensor pipe; MSGAT_PREC_TF32 applies to the second pass
+  a.fp32_grade = 1;
+  int G;
+  l2_partition(p, G, a.TPC);
+  for (int m = 0; m < p.M; ++m) a.prm[m] = prm[m];
+  a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z; a.A2 = saved + p.o_A2;
+  a.pqc = scratch + p.o_pqc;
+  const size_t smem = l2_mix_smem(p.C, a.KC);
+  switch (p.Oc) {
+    case 8: MSGAT_LAUNCH(k_l2_mix<8>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    case 16: MSGAT_LAUNCH(k_l2_mix<16>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    default: MSGAT_LAUNCH(k_l2_mix<24>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+  }
+  return 0;
+}
+
+// =======================================================================================
+// k_l2_out: the second pass.  Per tile of 8 nodes, with Mc = W1x1 Pc and Pt of the tile's sample:
+//   acc[p, :]  = x^T Wres^T                                  residual, all 3b outputs        msgat.py:116,131
+//   acc[p, 0:b]   += h^T Mc^T                                channel branch                  attention.py:94, msgat.py:94
+//   y1 = Pt a_now + Pt(t - d1) a_past + b1                   rows of 12 in the converters    attention.py:66, msgat.py:71-72
+//   acc[p, b:2b]  += [y1 ; y1(t - d2)]^T [W2now ; W2past]^T  second conv
+//   out = relu(acc + bias + [0 | 0 | sum_e pw[e] Z[col e]])  sparse spatial aggregation in the epilogue   attention.py:36
+// One accumulator of 96 columns per tile ([channel | temporal | spatial] branch outputs at columns 0, 32, 64): the
+// branch GEMMs accumulate straight onto the residual GEMM.  Work items per tile: C / KC "x" items (one raw chunk of x
+// rows -> an X and an H operand chunk) and one "y" item (the a_now and a_past raw chunks -> Y and shifted-Y operand
+// chunks; y1 is also saved for the backward).  Two converter groups take alternate items.
+// A CTA walks a contiguous range of the component's tiles; when the sample changes, the converters wait for the
+// tensor core to finish the old sample, restage Mc / Pt and go on.
+struct L2OutArgs {
+  const float* x; int64_t x_sb, x_sc, x_sm, sv_sm, out_sm;
+  int B, C, N, b, ntile, TPC, KC, d1, d2, nnz, fp32_grade;
+  msgat_meam_params prm[MSGAT_MAX_GROUP];
+  const float *Mc, *Pt, *Z, *pw, *A2;
+  float* Y1;
+  const int32_t *row_ptr, *col_idx;
+  float* out;
+};
+
+#define L2O_NSTG 2   // operand stages (two chunks each)
+#define L2O_NR 4     // raw chunks in flight
+static size_t l2_out_smem(int C, int KC, int b) {
+  const int RB = KC > b ? KC : b;
+  return (size_t)2 * C * 96 * 4 + (size_t)2 * C * 32 * 4 + (size_t)2 * 2 * b * 32 * 4 + (size_t)L2O_NSTG * 4 * RB * 128 * 4 +
+         (size_t)L2O_NR * RB * L2_RAW_ROW + (24 + 288 + 96 + 32) * 4 + (2 * L2O_NSTG + 2 * L2O_NR + 5) * L2_BAR_BYTES + 16 + 1024;
+}
+
+template <int BW>
+MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
+  MSGAT_DYN_SMEM(smem_raw);
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int C = a.C, KC = a.KC, nxc = C / KC, RB = KC > BW ? KC : BW, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
+  const msgat_meam_params& PM = a.prm[m];
+  const uint32_t cbW = (uint32_t)C * 128u, cbY = (uint32_t)(2 * BW) * 128u, cbX = (uint32_t)KC * 128u, cbB = (uint32_t)BW * 128u;
+  const uint32_t chunk_bytes = (uint32_t)RB * 512u, stage_bytes = 4u * chunk_bytes, raw_bytes = (uint32_t)RB * L2_RAW_ROW;
+  unsigned char* WRH = smem;                    // Wres^T  [C][96]
+  unsigned char* WRL = WRH + 3 * cbW;
+  unsigned char* WMH = WRL + 3 * cbW;           // Mc^T    [C][32]  (per sample)
+  unsigned char* WML = WMH + cbW;
+  unsigned char* W2H = WML + cbW;               // [W2now ; W2past]^T  [2b][32]
+  unsigned char* W2L = W2H + cbY;
+  unsigned char* RING = W2L + cbY;              // stage s: chunk0 hi | chunk0 lo | chunk1 hi | chunk1 lo
+  unsigned char* RAW = RING + L2O_NSTG * stage_bytes;
+  float* LW = reinterpret_cast<float*>(RAW + L2O_NR * raw_bytes);
+  float* PtS = LW + 24;                         // Pt | Pt shifted down by d1 rows
+  float* BIAS = PtS + 288;                      // per accumulator column
+  float* C1B = BIAS + 96;
+  unsigned char* BAR = reinterpret_cast<unsigned char*>(C1B + 32);
+  const uint32_t bar0 = smem_u32(BAR);
+  auto FULL = [&](int i) { return bar0 + (uint32_t)i * L2_BAR_BYTES; };
+  auto EMPTY = [&](int i) { return bar0 + (uint32_t)(L2O_NSTG + i) * L2_BAR_BYTES; };
+  auto TFULL = [&](int i) { return bar0 + (uint32_t)(2 * L2O_NSTG + i) * L2_BAR_BYTES; };
+  auto TEMPTY = [&](int i) { return bar0 + (uint32_t)(2 * L2O_NSTG + 2 + i) * L2_BAR_BYTES; };
+  auto RFULL = [&](int i) { return bar0 + (uint32_t)(2 * L2O_NSTG + 4 + i) * L2_BAR_BYTES; };
+  auto REMPTY = [&](int i) { return bar0 + (uint32_t)(2 * L2O_NSTG + 4 + L2O_NR + i) * L2_BAR_BYTES; };
+  const uint32_t WDONE = bar0 + (uint32_t)(2 * L2O_NSTG + 4 + 2 * L2O_NR) * L2_BAR_BYTES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(BAR + (2 * L2O_NSTG + 2 * L2O_NR + 5) * L2_BAR_BYTES);
+  const int64_t mo = (int64_t)m * a.sv_sm;
+  const int total = a.B * a.ntile, t_lo = blockIdx.x * a.TPC, t_hi = t_lo + a.TPC < total ? t_lo + a.TPC : total;
+  const int64_t cs = (int64_t)a.N * 12;
+
+  // per-sample staging: Mc^T as a B operand (hi / lo) and the temporal attention matrix with its d1-shifted copy
+  auto stage_sample = [&](int bi, int t0, int nthr) {
+    const float* Mcb = a.Mc + mo + (int64_t)bi * BW * C;
+    for (int i = t0; i < C * 32; i += nthr) {
+      const int k = i >> 5, n = i & 31;
+      l2_split1(WMH, WML, sw128b32_off(k, n, cbW), n < BW ? Mcb[n * C + k] : 0.f);
+    }
+    const float* Ptb = a.Pt + mo + (int64_t)bi * 144;
+    for (int i = t0; i < 144; i += nthr) {
+      const int t = i / 12, j = i - t * 12;
+      PtS[i] = Ptb[i];
+      PtS[144 + i] = t >= a.d1 ? Ptb[(t - a.d1) * 12 + j] : 0.f;
+    }
+  };
+  // ---- one-time staging (component constants)
+  for (int i = tid; i < C * 96; i += L2_THREADS) {
+    const int k = i / 96, n = i - k * 96, br = n >> 5, j = n & 31;
+    l2_split1(WRH, WRL, sw128b32_off(k, n, cbW), j < BW ? PM.res_w[(br * BW + j) * C + k] : 0.f);
+  }
+  for (int i = tid; i < 2 * BW * 32; i += L2_THREADS) {
+    const int k = i >> 5, n = i & 31;
+    float w = 0.f;
+    if (n < BW) w = k < BW ? PM.conv_w[1][(n * BW + k) * 2 + 1] : PM.conv_w[1][(n * BW + (k - BW)) * 2 + 0];
+    l2_split1(W2H, W2L, sw128b32_off(k, n, cbY), w);
+  }
+  for (int i = tid; i < 96; i += L2_THREADS) {
+    const int br = i >> 5, j = i & 31;
+    float v = 0.f;
+    if (j < BW) v = PM.res_b[br * BW + j] + (br == 0 ? PM.ca_b[j] : (br == 1 ? PM.conv_b[1][j] : 0.f));
+    BIAS[i] = v;
+  }
+  for (int i = tid; i < 32; i += L2_THREADS) C1B[i] = i < BW ? PM.conv_b[0][i] : 0.f;
+  if (tid < 12) { LW[tid] = PM.ln_w[tid]; LW[12 + tid] = PM.ln_b[tid]; }
+  if (t_lo < t_hi) stage_sample(t_lo / a.ntile, tid, L2_THREADS);
+  if (tid == 0) {
+    for (int i = 0; i < L2O_NSTG; ++i) { mbar_init(FULL(i), L2_CONV_WARPS); mbar_init(EMPTY(i), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(TFULL(i), 1); mbar_init(TEMPTY(i), L2_EPI_WARPS); }
+    for (int i = 0; i < L2O_NR; ++i) { mbar_init(RFULL(i), 1); mbar_init(REMPTY(i), L2_CONV_WARPS); }
+    mbar_init(WDONE, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+  fence_smem_to_async();
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tm = *tmem_slot;
+  const int IT = nxc + 1, NRAW = nxc + 2;   // work items and raw chunks per tile
+
+  if (warp == L2_PROD_WARP) {
+    // ================= producer =================
+    const float* xm = a.x + (int64_t)m * a.x_sm;
+    int r = 0;
+    for (int tile = t_lo; tile < t_hi; ++tile) {
+      const int bi = tile / a.ntile, n0 = (tile - bi * a.ntile) * L2_NT;
+      const int nv = a.N - n0 < L2_NT ? a.N - n0 : L2_NT;
+      const float* A2b = a.A2 + mo + (int64_t)bi * 2 * BW * cs;
+      for (int j = 0; j < NRAW; ++j, ++r) {
+        const int rs = r % L2O_NR, use = r / L2O_NR, rows = j < nxc ? KC : BW;
+        if (use > 0) mbar_wait(REMPTY(rs), (uint32_t)((use - 1) & 1));
+        if (lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(rows * nv * 48));
+        if (lane < rows) {
+          const float* src = j < nxc ? xm + (int64_t)bi * a.x_sb + (int64_t)(j * KC + lane) * a.x_sc + (int64_t)n0 * 12
+                                     : A2b + (int64_t)((j - nxc) * BW + lane) * cs + (int64_t)n0 * 12;
+          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)lane * L2_RAW_ROW, src, (uint32_t)(nv * 48), RFULL(rs));
+        }
+      }
+    }
+  } else if (warp >= L2_CONV_WARP0) {
+    // ================= converters =================
+    const L2Conv cv = l2_conv_thread();
+    const L2RowOff rox = l2_row_off(cbX, cv.kl, cv.nl), roy = l2_row_off(cbB, cv.kl, cv.nl);
+    const int ctid = cv.grp * L2_CONV_WARPS * 32 + cv.cid, NCT = L2_CONV_GROUPS * L2_CONV_WARPS * 32;
+    const int nq = (t_hi - t_lo) * IT;
+    int cur_b = t_lo < t_hi ? t_lo / a.ntile : 0, epoch = 0;
+    for (int q = cv.grp; q < nq; q += L2_CONV_GROUPS) {
+      const int ti = q / IT, item = q - ti * IT, tile = t_lo + ti;
+      const int bi = tile / a.ntile, n = (tile - bi * a.ntile) * L2_NT + cv.nl;
+      if (bi != cur_b) {
+        // the sample changes: every converter has finished the old sample's items; wait until the tensor core has
+        // read the old Mc for the last time, then restage the per-sample operands
+        named_bar_sync(1, NCT);
+        mbar_wait(WDONE, (uint32_t)(epoch & 1));
+        ++epoch;
+        stage_sample(bi, ctid, NCT);
+        fence_smem_to_async();
+        named_bar_sync(1, NCT);
+        cur_b = bi;
+      }
+      const int stg = q % L2O_NSTG, use = q / L2O_NSTG;
+      unsigned char* c0h = RING + (size_t)stg * stage_bytes;
+      unsigned char* c1h = c0h + 2 * chunk_bytes;
+      const int r0 = ti * NRAW + (item < nxc ? item : nxc);
+      if (item < nxc) {
+        const bool rowthr = cv.kl < KC;
+        const int rs = r0 % L2O_NR;
+        mbar_wait(RFULL(rs), (uint32_t)((r0 / L2O_NR) & 1));
+        float4 xa = f4zero(), xb = f4zero(), xd = f4zero();
+        if (rowthr && n < a.N) {
+          const float* r = reinterpret_cast<const float*>(RAW + (size_t)rs * raw_bytes + (size_t)cv.kl * L2_RAW_ROW) + cv.nl * 12;
+          xa = ld4(r); xb = ld4(r + 4); xd = ld4(r + 8);
+        }
+        float4 ha = xa, hb = xb, hd = xd;
+        if (rowthr && n < a.N) l2_row_ln(ha, hb, hd, LW);
+        if (use > 0) mbar_wait(EMPTY(stg), (uint32_t)((use - 1) & 1));
+        if (rowthr) {
+          l2_store_row(c0h, c0h + chunk_bytes, rox, cv.nl & 1, xa, xb, xd);
+          l2_store_row(c1h, c1h + chunk_bytes, rox, cv.nl & 1, ha, hb, hd);
+        }
+        __syncwarp();                                   // the raw rows have been consumed (their values are in the operand tiles)
+        if (lane == 0) mbar_arrive(REMPTY(rs));
+      } else {
+        const bool rowthr = cv.kl < BW;
+        const int rs0 = r0 % L2O_NR, rs1 = (r0 + 1) % L2O_NR;
+        float an[12], ap[12], y[12], ys[12];
+        MSGAT_UNROLL
+        for (int i = 0; i < 12; ++i) { an[i] = 0.f; ap[i] = 0.f; }
+        mbar_wait(RFULL(rs0), (uint32_t)((r0 / L2O_NR) & 1));
+        if (rowthr && n < a.N) {
+          const float* r = reinterpret_cast<const float*>(RAW + (size_t)rs0 * raw_bytes + (size_t)cv.kl * L2_RAW_ROW) + cv.nl * 12;
+          const float4 u = ld4(r), v = ld4(r + 4), w = ld4(r + 8);
+          an[0] = u.x; an[1] = u.y; an[2] = u.z; an[3] = u.w; an[4] = v.x; an[5] = v.y; an[6] = v.z; an[7] = v.w;
+          an[8] = w.x; an[9] = w.y; an[10] = w.z; an[11] = w.w;
+        }
+        mbar_wait(RFULL(rs1), (uint32_t)(((r0 + 1) / L2O_NR) & 1));
+        if (rowthr && n < a.N) {
+          const float* r = reinterpret_cast<const float*>(RAW + (size_t)rs1 * raw_bytes + (size_t)cv.kl * L2_RAW_ROW) + cv.nl * 12;
+          const float4 u = ld4(r), v = ld4(r + 4), w = ld4(r + 8);
+          ap[0] = u.x; ap[1] = u.y; ap[2] = u.z; ap[3] = u.w; ap[4] = v.x; ap[5] = v.y; ap[6] = v.z; ap[7] = v.w;
+          ap[8] = w.x; ap[9] = w.y; ap[10] = w.z; ap[11] = w.w;
+        }
+        // temporal attention + first conv on the mixed rows: y1[t] = b1 + sum_i Pt[t][i] a_now[i] + Pt[t-d1][i] a_past[i]
+        const float bias = C1B[rowthr ? cv.kl : 0];
+        MSGAT_UNROLL
+        for (int t = 0; t < 12; ++t) {
+          const float4 p0 = ld4(PtS + t * 12), p1 = ld4(PtS + t * 12 + 4), p2 = ld4(PtS + t * 12 + 8);
+          const float4 s0 = ld4(PtS + 144 + t * 12), s1 = ld4(PtS + 144 + t * 12 + 4), s2 = ld4(PtS + 144 + t * 12 + 8);
+          float s = bias;
+          s = fmaf(p0.x, an[0], s); s = fmaf(p0.y, an[1], s); s = fmaf(p0.z, an[2], s); s = fmaf(p0.w, an[3], s);
+          s = fmaf(p1.x, an[4], s); s = fmaf(p1.y, an[5], s); s = fmaf(p1.z, an[6], s); s = fmaf(p1.w, an[7], s);
+          s = fmaf(p2.x, an[8], s); s = fmaf(p2.y, an[9], s); s = fmaf(p2.z, an[10], s); s = fmaf(p2.w, an[11], s);
+          s = fmaf(s0.x, ap[0], s); s = fmaf(s0.y, ap[1], s); s = fmaf(s0.z, ap[2], s); s = fmaf(s0.w, ap[3], s);
+          s = fmaf(s1.x, ap[4], s); s = fmaf(s1.y, ap[5], s); s = fmaf(s1.z, ap[6], s); s = fmaf(s1.w, ap[7], s);
+          s = fmaf(s2.x, ap[8], s); s = fmaf(s2.y, ap[9], s); s = fmaf(s2.z, ap[10], s); s = fmaf(s2.w, ap[11], s);
+          y[t] = (rowthr && n < a.N) ? s : 0.f;
+          ys[t] = 0.f;
+        }
+        // shifted copy ys[t] = y[t - d2]: a switch over the uniform dilation keeps every register index static
+#define L2O_SHIFT(D) case D: _Pragma("unroll") for (int t = D; t < 12; ++t) ys[t] = y[t - D]; break;
+        switch (a.d2) {
+          L2O_SHIFT(1) L2O_SHIFT(2) L2O_SHIFT(3) L2O_SHIFT(4) L2O_SHIFT(5) L2O_SHIFT(6) L2O_SHIFT(7) L2O_SHIFT(8) L2O_SHIFT(9)
+          L2O_SHIFT(10) L2O_SHIFT(11)
+          default: break;
+        }
+#undef L2O_SHIFT
+        if (rowthr && n < a.N) {   // y1 is an operand of the second conv's weight gradient
+          float* yd = a.Y1 + mo + (((int64_t)bi * BW + cv.kl) * a.N + n) * 12;
+          st4(yd, make_float4(y[0], y[1], y[2], y[3])); st4(yd + 4, make_float4(y[4], y[5], y[6], y[7]));
+          st4(yd + 8, make_float4(y[8], y[9], y[10], y[11]));
+        }
+        if (use > 0) mbar_wait(EMPTY(stg), (uint32_t)((use - 1) & 1));
+        if (rowthr) {
+          l2_store_row(c0h, c0h + chunk_bytes, roy, cv.nl & 1, make_float4(y[0], y[1], y[2], y[3]), make_float4(y[4], y[5], y[6], y[7]),
+                       make_float4(y[8], y[9], y[10], y[11]));
+          l2_store_row(c1h, c1h + chunk_bytes, roy, cv.nl & 1, make_float4(ys[0], ys[1], ys[2], ys[3]), make_float4(ys[4], ys[5], ys[6], ys[7]),
+                       make_float4(ys[8], ys[9], ys[10], ys[11]));
+        }
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(REMPTY(rs0)); mbar_arrive(REMPTY(rs1)); }
+      }
+      fence_smem_to_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(FULL(stg));
+    }
+  } else if (warp == L2_MMA_WARP) {
+    // ================= MMA issue (one thread) =================
+    if (lane == 0) {
+      const uint32_t id96 = umma_idesc_tf32(128, 96, 1, 1), id32 = umma_idesc_tf32(128, 32, 1, 1);
+      const uint64_t dWRH = umma_desc(smem_u32(WRH), cbW, 512u, 1), dWRL = umma_desc(smem_u32(WRL), cbW, 512u, 1);
+      const uint64_t dWMH = umma_desc(smem_u32(WMH), cbW, 512u, 1), dWML = umma_desc(smem_u32(WML), cbW, 512u, 1);
+      const uint64_t dW2H = umma_desc(smem_u32(W2H), cbY, 512u, 1), dW2L = umma_desc(smem_u32(W2L), cbY, 512u, 1);
+      int q = 0, it = 0;
+      for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+        const int buf = it & 1, ut = it >> 1;
+        // columns of an accumulator set: [0, 96) residual GEMM | [96, 160) branch GEMMs (channel, temporal) | [160, 256) small
+        const uint32_t dm = tm + (uint32_t)buf * 256u, dbm = dm + 96u, dsm = dm + 160u;
+        if (ut > 0) mbar_wait(TEMPTY(buf), (uint32_t)((ut - 1) & 1));
+        tc_fence_after_sync();
+        for (int item = 0; item < IT; ++item, ++q) {
+          const int stg = q % L2O_NSTG, use = q / L2O_NSTG;
+          mbar_wait(FULL(stg), (uint32_t)(use & 1));
+          tc_fence_after_sync();
+          const uint32_t base = smem_u32(RING + (size_t)stg * stage_bytes);
+          if (item < nxc) {
+            const uint64_t dXH = umma_desc(base, cbX, 512u, 1), dXL = umma_desc(base + chunk_bytes, cbX, 512u, 1);
+            const uint64_t dHH = umma_desc(base + 2 * chunk_bytes, cbX, 512u, 1), dHL = umma_desc(base + 3 * chunk_bytes, cbX, 512u, 1);
+            for (int ks = 0; ks < KC / 8; ++ks) {
+              const uint32_t first = (item == 0 && ks == 0) ? 0u : 1u;
+              l2_mma(dm, dsm, dXH, dXL, dWRH, dWRL, (uint32_t)ks, (uint32_t)(item * (KC / 8) + ks), id96, first, first, a.fp32_grade);
+            }
+            for (int ks = 0; ks < KC / 8; ++ks)
+              l2_mma(dbm, dsm, dHH, dHL, dWMH, dWML, (uint32_t)ks, (uint32_t)(item * (KC / 8) + ks), id32, (item == 0 && ks == 0) ? 0u : 1u, 1u,
+                     a.fp32_grade);
+          } else {
+            const uint64_t dYH = umma_desc(base, cbB, 512u, 1), dYL = umma_desc(base + chunk_bytes, cbB, 512u, 1);
+            const uint64_t dSH = umma_desc(base + 2 * chunk_bytes, cbB, 512u, 1), dSL = umma_desc(base + 3 * chunk_bytes, cbB, 512u, 1);
+            for (int ks = 0; ks < BW / 8; ++ks)
+              l2_mma(dbm + 32u, dsm + 32u, dYH, dYL, dW2H, dW2L, (uint32_t)ks, (uint32_t)ks, id32, ks == 0 ? 0u : 1u, 1u, a.fp32_grade);
+            for (int ks = 0; ks < BW / 8; ++ks)
+              l2_mma(dbm + 32u, dsm + 32u, dSH, dSL, dW2H, dW2L, (uint32_t)ks, (uint32_t)(BW / 8 + ks), id32, 1u, 1u, a.fp32_grade);
+          }
+          umma_commit(EMPTY(stg));
+        }
+        umma_commit(TFULL(buf));
+        if (tile + 1 < t_hi && (tile + 1) / a.ntile != tile / a.ntile) umma_commit(WDONE);   // last tile of its sample
+      }
+    }
+  } else {
+    // ================= epilogue =================
+    const int nj = lane >> 4, t = lane & 15, qtr = warp & 3, par = warp >> 2;
+    const uint32_t lane_base = (uint32_t)(qtr * 32) << 16;
+    int it = 0;
+    for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+      const int buf = it & 1, ut = it >> 1;
+      const int bi = tile / a.ntile, n = (tile - bi * a.ntile) * L2_NT + qtr * 2 + nj;
+      const bool live = t < 12 && n < a.N;
+      // sparse spatial aggregation of this warp's spatial columns while the tensor core works on the tile
+      float sp[(BW / 8 + 1) / 2][8];
+      MSGAT_UNROLL
+      for (int i = 0; i < (BW / 8 + 1) / 2; ++i)
+        MSGAT_UNROLL
+        for (int j = 0; j < 8; ++j) sp[i][j] = 0.f;
+      if (live) {
+        const float* pwb = a.pw + mo + (int64_t)bi * a.nnz;
+        const float* Zb = a.Z + mo + (int64_t)bi * BW * cs + t;
+        const int e1 = a.row_ptr[n + 1];
+        for (int e = a.row_ptr[n]; e < e1; ++e) {
+          const float w = pwb[e];
+          const float* z = Zb + (int64_t)a.col_idx[e] * 12;
+          MSGAT_UNROLL
+          for (int g = 0; g < BW / 8; ++g) {
+            if (((8 + g) & 1) != par) continue;   // spatial column groups 8, 9, ... of 8 columns: parity split like below
+            MSGAT_UNROLL
+            for (int j = 0; j < 8; ++j) sp[g >> 1][j] = fmaf(w, z[(int64_t)(g * 8 + j) * cs], sp[g >> 1][j]);
+          }
+        }
+      }
+      mbar_wait(TFULL(buf), (uint32_t)(ut & 1));
+      tc_fence_after_sync();
+      const uint32_t dm = tm + (uint32_t)buf * 256u + lane_base, dbm = dm + 96u, dsm = dm + 160u;
+      float* ob = a.out + (int64_t)m * a.out_sm + (int64_t)bi * 3 * BW * cs + (int64_t)n * 12 + t;
+      MSGAT_UNROLL
+      for (int g = 0; g < 12; ++g) {
+        if ((g & 1) != par) continue;          // warp-uniform
+        if ((g & 3) * 8 >= BW) continue;        // padding columns of a branch (compile-time)
+        float v[8];
+        if (g < 8) l2_ld8x3(dm + g * 8, dbm + g * 8, dsm + g * 8, a.fp32_grade, v);
+        else l2_ld8(dm + g * 8, dsm + g * 8, a.fp32_grade, v);
+        if (live) {
+          MSGAT_UNROLL
+          for (int j = 0; j < 8; ++j) {
+            const int col = g * 8 + j, br = g >> 2, jj = (g & 3) * 8 + j;   // compile-time
+            if (jj >= BW) continue;
+            float r = v[j] + BIAS[col];
+            if (br == 2) r += sp[(g - 8) >> 1][j];
+            ob[(int64_t)(br * BW + jj) * cs] = fmaxf(r, 0.f);
+          }
+        }
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(TEMPTY(buf));
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tm, 512);
+}
+
+int launch_l2_out(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out, float* saved,
+                  void* stream) {
+  L2OutArgs a;
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.sv_sm = p.saved_total; a.out_sm = (int64_t)p.B * p.O * p.N * 12;
+  a.B = p.B; a.C = p.C; a.N = p.N; a.b = p.Oc; a.ntile = (p.N + L2_NT - 1) / L2_NT; a.KC = l2_chunk_rows(p.C);
+  a.d1 = p.dil[0]; a.d2 = p.dil[1]; a.nnz = p.nnz; a.fp32_grade = p.precision == MSGAT_PREC_FP32 ? 1 : 0;
+  int G;
+  l2_partition(p, G, a.TPC);
+  for (int m = 0; m < p.M; ++m) a.prm[m] = prm[m];
+  a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw; a.A2 = saved + p.o_A2; a.Y1 = saved + p.o_Y1;
+  a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out;
+  const size_t smem = l2_out_smem(p.C, a.KC, p.Oc);
+  switch (p.Oc) {
+    case 8: MSGAT_LAUNCH(k_l2_out<8>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    case 16: MSGAT_LAUNCH(k_l2_out<16>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    default: MSGAT_LAUNCH(k_l2_out<24>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+  }
+  return 0;
+}

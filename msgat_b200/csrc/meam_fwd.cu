@@ -110,6 +110,8 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
 // ---------------------------------------------------------------------------------------
 struct SmallArgs {   // grouped like PrepArgs: blockIdx.y = component
   int C, Oc, Ot, cmix, ntile;
+  int l2, N;           // l2: partials from k_l2_mix (fp32 q_c partials per 8-node tile; K from the saved q_t)
+  const float* qt;     // saved q_t [B,N,12] (l2)
   int64_t sv_sm, sc_sm;
   const float *pqc, *pK;   // (as doubles)
   msgat_meam_params prm[MSGAT_MAX_GROUP];
@@ -137,19 +139,48 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
   double* K = S + C * C;                             // [12][20]
   double* St = K + 240;                              // [144]
   if (a.Oc) {
+    const float* pqf = a.pqc + m * a.sc_sm;
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
       double s = 0.0;
-      for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      if (a.l2) for (int tl = 0; tl < a.ntile; ++tl) s += (double)pqf[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      else for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
       qc[i] = s;
       qc_o[(int64_t)b * C * 12 + i] = (float)s;
     }
   }
-  if (a.Ot) {
+  if (a.Ot && !a.l2) {
     for (int i = threadIdx.x; i < 240; i += blockDim.x) {
       double s = 0.0;
       for (int tl = 0; tl < a.ntile; ++tl) s += pK_m[((int64_t)b * a.ntile + tl) * 240 + i];
       K[i] = s;
       K_o[(int64_t)b * 240 + i] = (float)s;
+    }
+  }
+  if (a.Ot && a.l2) {
+    // temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T over all N nodes (attention.py:65) from the saved query, fp64;
+    // two halves of the nodes per output, combined through St (free until the scores are formed)
+    const float* qtb = a.qt + m * a.sv_sm + (int64_t)b * a.N * 12;
+    // thread = (node group, rank index r, quad of t): one 128-bit read of q_t and one weight per node, 4 fp64 FMAs
+    const int parts = (int)blockDim.x / 60;
+    const int part = threadIdx.x / 60, rq = threadIdx.x - part * 60, r = rq / 3, t4 = (rq - r * 3) * 4;
+    double* KP = St + 144;   // [parts][240], behind the score matrix (the launch adds the room in l2 mode)
+    if (part < parts) {
+      const float* W = (r < 10) ? a.prm[m].ta_Wt1 + (int64_t)r * a.N : a.prm[m].ta_Wt2 + (int64_t)(r - 10) * a.N;
+      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      for (int n = part; n < a.N; n += parts) {
+        const double w = (double)__ldg(W + n);
+        const float4 qv = ld4(qtb + (int64_t)n * 12 + t4);
+        s0 += w * (double)qv.x; s1 += w * (double)qv.y; s2 += w * (double)qv.z; s3 += w * (double)qv.w;
+      }
+      double* kp = KP + part * 240;
+      kp[(t4 + 0) * 20 + r] = s0; kp[(t4 + 1) * 20 + r] = s1; kp[(t4 + 2) * 20 + r] = s2; kp[(t4 + 3) * 20 + r] = s3;
+    }
+    __syncthreads();
+    if (threadIdx.x < 240) {
+      double s = 0.0;
+      for (int k = 0; k < parts; ++k) s += KP[k * 240 + threadIdx.x];
+      K[threadIdx.x] = s;
+      K_o[(int64_t)b * 240 + threadIdx.x] = (float)s;
     }
   }
   __syncthreads();
@@ -455,7 +486,11 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
   const bool do_ln = p.flags & MSGAT_F_LN;
   const int M = p.M;
   const int64_t sv_sm = p.saved_total, sc_sm = p.scratch_sm, out_sm = (int64_t)p.B * p.O * p.N * 12;
-  {   // one launch for all components
+  const bool l2 = l2_fwd_supported(p);
+  if (l2) {
+    int rc = launch_l2_mix(p, prm, x, saved, scratch, stream);
+    if (rc) return rc;
+  } else {   // one launch for all components
     PrepArgs a;
     a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.sv_sm = sv_sm; a.sc_sm = sc_sm;
     a.C = p.C; a.N = p.N; a.Oc = p.Oc; a.Ot = p.Ot; a.Os = p.Os; a.Cz = p.Cz; a.s_pre = p.s_pre; a.do_ln = do_ln;
@@ -469,17 +504,19 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
   }
   if (p.Oc || p.Ot) {
     SmallArgs a;
-    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = p.ntile_p;
+    a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = l2 ? (p.N + 7) / 8 : p.ntile_p;
+    a.l2 = l2 ? 1 : 0; a.N = p.N; a.qt = saved + p.o_qt;
     a.sv_sm = sv_sm; a.sc_sm = sc_sm;
     a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
     for (int m = 0; m < M; ++m) a.prm[m] = prm[m];
     a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
-    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144) * 8;
+    size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144 + (l2 ? 8 * 240 : 0)) * 8;
     const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
     MSGAT_LAUNCH(k_small, dim3(p.B, M), dim3(smT), smem, stream, a);
   }
   if (p.Os) launch_sstats(p, prm, adj, saved, stream);
   if (l1_fwd_supported(p)) return launch_l1_fwd(p, prm, adj, x, out, saved, stream);   // first layer: one grouped launch
+  if (l2 && !getenv("MSGAT_L2_OLD_APPLY")) return launch_l2_out(p, prm, adj, x, out, saved, stream);   // layer 2: one grouped launch
   // the apply pass: still one launch per component (the component's buffers by pointer offset)
   for (int m = 0; m < M; ++m) {
     const float* xm = x + m * p.x_sm;

@@ -46,9 +46,10 @@ struct Ctx {
   dim3 bdim, gdim;
   int lin;  // linear thread id in block
   unsigned char* smem;
+  int nb_id = 0, nb_need = 0;  // named barrier the fiber is parked at (state AT_NAMED)
 };
 
-enum { RUN = 0, AT_BLOCK = 1, AT_WARP = 2, DONE = 3 };
+enum { RUN = 0, AT_BLOCK = 1, AT_WARP = 2, DONE = 3, SPIN = 4, AT_NAMED = 5 };
 
 struct Fiber {
   ucontext_t uc;
@@ -58,6 +59,11 @@ struct Fiber {
 };
 
 struct Sched {
+  // tcgen05 / mbarrier emulation (tc_common.cuh under MSGAT_EMU): tensor memory of the running block and an event
+  // counter that every barrier arrival bumps, so that a round of pure spinning without any event is a deadlock
+  std::vector<float> tmem;          // [128 lanes][512 columns]
+  unsigned long long events = 0;
+  int named_id[16] = {0}, named_need[16] = {0};
   ucontext_t main_uc;
   std::vector<Fiber> fibers;
   std::vector<uint64_t> slots;  // one per thread, warp shuffle exchange
@@ -76,6 +82,10 @@ inline void yield_to_sched(int st) {
 }
 
 inline void syncthreads() { yield_to_sched(AT_BLOCK); }
+inline void spin_yield() { yield_to_sched(SPIN); }
+// bar.sync id, nthreads: released when `nthreads` fibers of the block wait on the same id
+inline void named_sync(int id, int nthreads) { cur()->nb_id = id; cur()->nb_need = nthreads; yield_to_sched(AT_NAMED); }
+inline void event() { sched().events++; }
 inline void syncwarp() { yield_to_sched(AT_WARP); }
 
 inline uint64_t shfl_idx(uint64_t v, int src) {
@@ -121,19 +131,25 @@ inline void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem_bytes, std::
     f.ctx.lin = t;
     f.ctx.smem = sbase;
   }
+  s.tmem.assign(128 * 512, 0.f);
+  int idle_rounds = 0;
   for (;;) {
     bool progressed = false;
     int alive = 0;
+    const unsigned long long ev0 = s.events;
     for (int t = 0; t < nt; ++t) {
       Fiber& f = s.fibers[t];
-      if (f.state == RUN) {
+      if (f.state == RUN || f.state == SPIN) {
+        const bool spinning = f.state == SPIN;
+        f.state = RUN;
         s.running = &f;
         cur() = &f.ctx;
         swapcontext(&s.main_uc, &f.uc);
-        progressed = true;
+        if (!(spinning && f.state == SPIN)) progressed = true;   // a fiber that only re-polls made no progress
       }
       if (f.state != DONE) ++alive;
     }
+    if (s.events != ev0) progressed = true;
     if (alive == 0) break;
     bool released = false;
     // block-wide barrier: every live thread must have arrived
@@ -142,6 +158,15 @@ inline void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem_bytes, std::
     if (at_block == alive) {
       for (int t = 0; t < nt; ++t) if (s.fibers[t].state == AT_BLOCK) s.fibers[t].state = RUN;
       released = true;
+    }
+    // named barriers
+    for (int id = 1; id < 16; ++id) {
+      int cnt = 0, need = 0;
+      for (int t = 0; t < nt; ++t) if (s.fibers[t].state == AT_NAMED && s.fibers[t].ctx.nb_id == id) { ++cnt; need = s.fibers[t].ctx.nb_need; }
+      if (cnt && cnt == need) {
+        for (int t = 0; t < nt; ++t) if (s.fibers[t].state == AT_NAMED && s.fibers[t].ctx.nb_id == id) s.fibers[t].state = RUN;
+        released = true;
+      }
     }
     // warp-level sync points
     for (int w = 0; w * 32 < nt; ++w) {
@@ -156,9 +181,12 @@ inline void run_block(dim3 grid, dim3 block, uint3 bid, size_t smem_bytes, std::
       }
     }
     if (!progressed && !released) {
-      fprintf(stderr, "emu: deadlock in block (%u,%u,%u): divergent barrier\n", bid.x, bid.y, bid.z);
+      if (++idle_rounds < 4) continue;   // spinners get a few more polls before the verdict
+      fprintf(stderr, "emu: deadlock in block (%u,%u,%u): divergent barrier or mbarrier wait that can never complete\n", bid.x, bid.y, bid.z);
+      for (int t = 0; t < nt; ++t) if (s.fibers[t].state != DONE) fprintf(stderr, "  thread %d state %d\n", t, s.fibers[t].state);
       abort();
     }
+    idle_rounds = 0;
   }
 }
 
