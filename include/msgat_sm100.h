@@ -189,6 +189,18 @@ int msgat_loss_backward(const float *dpred, const float *gout, int64_t n, float 
 int msgat_adam_step(float *p, const float *g, float *m, float *v, int64_t n, float lr, float beta1, float beta2,
                     float eps, float weight_decay, float grad_scale, int32_t *step, void *scratch, void *stream);
 
+/* msgat_loss_forward_static: msgat_loss_forward without the scratch argument, for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in
+ * the reference.  Same kernel, grid and result as
+ * msgat_loss_forward; its scratch is a 32 784-byte file-scope device array that every GPU loading the library holds
+ * until exit, and the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine; one 16-byte
+ * cudaMemsetAsync on `stream` clears the arrival counter).  Limit: n <= msgat_loss_static_max_n() = 2^28 elements,
+ * beyond which it returns -63 with a message.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams without an ordering between them) race; calls on one stream are safe. */
+int64_t msgat_loss_static_max_n(void);
+int msgat_loss_forward_static(const float *pred, const float *target, int64_t n, float delta, float mask_value,
+                              float *loss, float *dpred, double *metrics, void *stream);
+
 /* Self-test of the tcgen05 (kind::tf32) building block of the tensor-core path; see
  * csrc/tc_probe.cu.  mode 0: D[256,N] = A[K,256]^T B[K,N]; mode 1: D[128,N] = A[Ra,P] B[Rb,P]^T. */
 int msgat_tc_probe(int mode, const float *A, const float *B, float *D, int K, int N, int Ra, int Rb, int P,

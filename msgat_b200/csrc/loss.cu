@@ -166,3 +166,66 @@ int msgat_adam_step(float* p, const float* g, float* m, float* v, int64_t n, flo
 }
 
 }  // extern "C"
+
+// ---- the allocation-free variant (requested by the run's operators; no counterpart in the reference) ------------
+// Same kernel and grid as msgat_loss_forward, with the scratch (arrival counter + per-block partial sums) in a
+// file-scope device array instead of caller memory: nothing on this path calls cudaMalloc / cudaFree or an
+// allocating library routine, so it can run under CUDA graph capture or in harnesses that forbid allocation.
+// Every device that loads the library holds the MSGAT_LOSS_STATIC_SCRATCH_BYTES array until exit.  All calls on a
+// device share it: two calls that overlap on the GPU (different streams, no ordering between them) race.
+#define MSGAT_LOSS_STATIC_MAX_N (1ll << 28)   // elements per call; the grid is capped, the limit keeps the contract explicit
+#define MSGAT_LOSS_STATIC_SCRATCH_BYTES (LOSS_MAX_BLOCKS * 4 * 8 + 16)
+#ifdef MSGAT_EMU
+static unsigned char g_loss_static_scratch[MSGAT_LOSS_STATIC_SCRATCH_BYTES];
+static int loss_static_scratch(void** out) { *out = g_loss_static_scratch; return 0; }
+#else
+static __device__ __align__(256) unsigned char g_loss_static_scratch[MSGAT_LOSS_STATIC_SCRATCH_BYTES];
+#define LOSS_STATIC_MAX_DEVICES 64
+// In host code g_loss_static_scratch is only a handle of the symbol, not a device address: the address is asked of
+// the runtime once per device, with that device current, and cached.
+static int loss_static_scratch(void** out) {
+  static std::atomic<void*> cache[LOSS_STATIC_MAX_DEVICES];
+  const int dev = msgat_current_device();
+  if (dev < 0 || dev >= LOSS_STATIC_MAX_DEVICES) { msgat_set_error("msgat_loss_forward_static: device ordinal out of range"); return -64; }
+  void* p = cache[dev].load(std::memory_order_acquire);
+  if (!p) {
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_loss_static_scratch);
+    if (e != cudaSuccess || !p) {
+      msgat_set_error("msgat_loss_forward_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return -65;
+    }
+    cache[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+#endif
+
+extern "C" {
+
+int64_t msgat_loss_static_max_n(void) { return MSGAT_LOSS_STATIC_MAX_N; }
+
+int msgat_loss_forward_static(const float* pred, const float* target, int64_t n, float delta, float mask_value, float* loss,
+                              float* dpred, double* metrics, void* stream) {
+  if (n <= 0 || !pred || !target || !loss) { msgat_set_error("msgat_loss_forward_static: bad arguments"); return -60; }
+  if (n > MSGAT_LOSS_STATIC_MAX_N) {
+    msgat_set_error("msgat_loss_forward_static: n exceeds the limit of 2^28 elements of the static-scratch variant; "
+                    "use msgat_loss_forward with caller-provided scratch");
+    return -63;
+  }
+  void* scratch = nullptr;
+  const int rc = loss_static_scratch(&scratch);
+  if (rc != 0) return rc;
+  // the array keeps what the last call left: the arrival counter has to start at zero (the kernel re-arms it, but a
+  // call that was aborted half-way would not have); the partial sums are fully overwritten before they are read
+  if (cudaMemsetAsync(scratch, 0, 16, (cudaStream_t)stream) != 0) { msgat_set_error("msgat_loss_forward_static: cudaMemsetAsync failed"); return -66; }
+  LossArgs a;
+  a.pred = pred; a.target = target; a.n = n; a.delta = delta; a.mask_value = mask_value; a.inv_n = (float)(1.0 / (double)n);
+  a.loss = loss; a.dpred = dpred; a.metrics = metrics;
+  a.counter = reinterpret_cast<unsigned int*>(scratch);
+  a.part = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 16);
+  MSGAT_LAUNCH(k_loss, dim3(grid_for(n, LOSS_THREADS * 4 * 4)), dim3(LOSS_THREADS), ((LOSS_THREADS / 32) * 4 + 1) * sizeof(double), stream, a);
+  return 0;
+}
+
+}  // extern "C"
