@@ -189,6 +189,15 @@ int msgat_loss_backward(const float *dpred, const float *gout, int64_t n, float 
 int msgat_adam_step(float *p, const float *g, float *m, float *v, int64_t n, float lr, float beta1, float beta2,
                     float eps, float weight_decay, float grad_scale, int32_t *step, void *scratch, void *stream);
 
+/* Data feed on the device: the sliding-window sampler of data_loader.py:92-115
+ * (TimeSeriesSlice.__getitem__ + collate) over a time series resident in HBM.  inputs [C,N,L] (normalised series),
+ * target [N,L] (raw channel 0), t [B] device int64 time indices; hours [M] HOST array (windows start at
+ * t - hours[m] * tau); X [B,M,C,N,tau], Y [B,N,q], H/D [B] int64 (hour of day, day of week; may be null).
+ * M <= 16, B <= 256 per call; a window outside [0,L) is written as NaN. */
+int msgat_window_gather(const float *inputs, const float *target, const int64_t *t, int B, int C, int N, int64_t L,
+                        const int32_t *hours, int M, int tau, int q, float *X, int64_t *H, int64_t *D, float *Y,
+                        void *stream);
+
 /* msgat_loss_forward_static: msgat_loss_forward without the scratch argument, for callers that cannot allocate
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in
  * the reference.  Same kernel, grid and result as

@@ -65,7 +65,7 @@ EXPORTS = ["msgat_version", "msgat_last_error", "msgat_device_check", "msgat_lau
            "msgat_head_scratch_floats", "msgat_head_backward", "msgat_tc_probe",
            "msgat_heads_forward", "msgat_heads_scratch_floats", "msgat_heads_backward",
            "msgat_loss_scratch_bytes", "msgat_loss_forward", "msgat_loss_backward", "msgat_adam_step",
-           "msgat_loss_static_max_n", "msgat_loss_forward_static"]
+           "msgat_loss_static_max_n", "msgat_loss_forward_static", "msgat_window_gather"]
 
 _LIB = None
 _DEBUG_BACKEND = False  # set only by tests/emu (kernel-logic debugging on the GPU-less build box)
@@ -82,6 +82,8 @@ def _declare(lib):
     lib.msgat_loss_forward.argtypes = [_fp, _fp, C.c_int64, C.c_float, C.c_float, _fp, _fp, _fp, _fp, _fp]
     lib.msgat_loss_backward.argtypes = [_fp, _fp, C.c_int64, _fp, _fp]
     lib.msgat_loss_static_max_n.restype = C.c_int64
+    lib.msgat_window_gather.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int64, C.POINTER(C.c_int32), C.c_int,
+                                        C.c_int, C.c_int, _fp, _fp, _fp, _fp, _fp]
     lib.msgat_loss_forward_static.argtypes = [_fp, _fp, C.c_int64, C.c_float, C.c_float, _fp, _fp, _fp, _fp]
     lib.msgat_adam_step.argtypes = [_fp, _fp, _fp, _fp, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float,
                                     C.c_float, C.c_float, _fp, _fp, _fp]
