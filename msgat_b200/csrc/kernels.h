@@ -8,6 +8,10 @@
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream);
+// spatial_tc.cu: the same two passes on tcgen05 (MSGAT_PREC_TF32)
+bool score_tc_supported(const Plan& p);
+int launch_sstats_tc(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
+int launch_scol_tc(const Plan& p, const float* saved, const float* delta, float* dq, void* stream);
 int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
                       float* saved, float* scratch, void* stream);
 int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* out,

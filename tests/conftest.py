@@ -18,7 +18,8 @@ def pytest_configure(config):
 
 
 def golden_cases(prefix):
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, prefix + "*.npz")))
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, prefix + "*.npz"))
+                  if not os.path.basename(p).startswith("feed_"))   # feed_*: fixtures of the data feed (tests/feed_cases.py)
 
 
 class Golden:

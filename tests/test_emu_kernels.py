@@ -39,3 +39,36 @@ def test_emulated_head_kernels_ragged_shapes():
         errs = run_head_case(case, torch.device("cpu"))
         bad = {k: v for k, v in errs.items() if not v < 1e-5}
         assert not bad, f"{case}: {bad}"
+
+
+@pytest.mark.parametrize("N", [37, 300])
+def test_emulated_tensor_core_score_passes(N):
+    """csrc/spatial_tc.cu (TF32 mode: the N x N score passes of attention.py:34-36 on tcgen05, forward and backward)
+    through the emulated tcgen05 / TMEM model: one and three column tiles, ragged last tile, against the fp64 oracle
+    at the TF32 bar."""
+    import torch
+    from msgat_b200 import _lib, models, synthetic
+    from oracle import msgat_oracle as O
+    torch.manual_seed(N)
+    adj = synthetic.geometric_graph(N, mean_degree=5.0, seed=1)
+    mod = models.GACN(3, 8, 12)
+    for p in mod.parameters():
+        torch.nn.init.normal_(p, std=0.5) if p.dim() < 2 else torch.nn.init.xavier_normal_(p)
+    mod.precision = mod.gatt.precision = _lib.PREC_TF32
+    g = torch.Generator().manual_seed(N + 1)
+    x = torch.randn(2, 3, N, 12, generator=g)
+    R = torch.randn(2, 8, N, 12, generator=g)
+    xr = x.clone().requires_grad_(True)
+    out = mod(xr, adj)
+    (out * R).sum().backward()
+    p = {k: v.detach().clone().double().requires_grad_(True) for k, v in mod.state_dict().items()}
+    xo = x.clone().double().requires_grad_(True)
+    ref = O.gacn(xo, adj.double(), p, "")
+    (ref * R.double()).sum().backward()
+
+    def rel(a, b):
+        return float((a.double() - b).norm() / b.norm().clamp_min(1e-30))
+    errs = {"out": rel(out.detach(), ref.detach()), "dX": rel(xr.grad, xo.grad)}
+    errs.update({k: rel(v.grad, p[k].grad) for k, v in mod.named_parameters()})
+    assert all(e < 2e-3 for e in errs.values()), errs
+    assert errs["out"] > 2e-6, "the TF32 path was not taken"   # fp32 path: ~1e-7

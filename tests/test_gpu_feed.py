@@ -20,7 +20,8 @@ def test_window_gather_marks_out_of_range_windows():
     series = D.DeviceTimeSeries(torch.randn(2, 5, 100), 60, "cuda")
     X, H, Dd, Y = D.gather_windows(series, torch.tensor([5, 95]), [1], 12, 12)
     torch.cuda.synchronize()
-    assert torch.isnan(X[0]).all() and not torch.isnan(X[1]).any()     # t - 12 < 0
+    assert torch.isnan(X[0, ..., :7]).all() and not torch.isnan(X[0, ..., 7:]).any()     # window starts at t - 12 = -7
+    assert not torch.isnan(X[1]).any()
     assert not torch.isnan(Y[0]).any() and torch.isnan(Y[1, :, 5:]).all() and not torch.isnan(Y[1, :, :5]).any()
     with pytest.raises(ValueError):
         D.WindowLoader(series, (5, 50), [1], 12, 12, 8)

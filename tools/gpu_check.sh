@@ -2,7 +2,7 @@
 set -o pipefail
 mkdir -p gpurun_out
 TAG=${1:-check}
-rm -f gpurun_out/parity_notes.log; timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -40 > gpurun_out/${TAG}_pytest.log
+rm -f gpurun_out/parity_notes.log; timeout 600 python -m pytest tests -m gpu -q --timeout 90 --timeout-method thread 2>&1 | tail -40 > gpurun_out/${TAG}_pytest.log
 cat gpurun_out/${TAG}_pytest.log; cat gpurun_out/parity_notes.log 2>/dev/null | cut -c1-400
 timeout 200 python __graft_entry__.py smoke > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
 timeout 300 python bench.py --no-cpu-baseline > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || tail -5 gpurun_out/${TAG}_bench.err
