@@ -357,7 +357,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
   if (t_lo < t_hi) stage_sample(t_lo / a.ntile, tid, L2_THREADS);
   if (tid == 0) {
     for (int i = 0; i < L2O_NSTG; ++i) { mbar_init(FULL(i), L2_CONV_WARPS); mbar_init(EMPTY(i), 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(TFULL(i), 1); mbar_init(TEMPTY(i), L2_EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(TFULL(i), 1); mbar_init(TEMPTY(i), L2_EPI_WARPS / 2); }
     for (int i = 0; i < L2O_NR; ++i) { mbar_init(RFULL(i), 1); mbar_init(REMPTY(i), L2_CONV_WARPS); }
     mbar_init(WDONE, 1);
     mbar_fence_init();
@@ -540,32 +540,47 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
     }
   } else {
     // ================= epilogue =================
-    const int nj = lane >> 4, t = lane & 15, qtr = warp & 3, par = warp >> 2;
+    // Two groups of four warps (one per TMEM lane quarter) take alternate tiles = alternate accumulator sets: the sparse
+    // aggregation below is a chain of dependent gathers (col_idx -> Z rows) that costs several microseconds per tile,
+    // and with every epilogue warp on every tile it was the pipeline's longest stage (ncu: 60 % of the epilogue's
+    // samples in that chain).  Now the chains of two consecutive tiles run side by side.
+    const int nj = lane >> 4, t = lane & 15, qtr = warp & 3, grp = warp >> 2;
     const uint32_t lane_base = (uint32_t)(qtr * 32) << 16;
-    int it = 0;
-    for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+    for (int tile = t_lo + grp, it = grp; tile < t_hi; tile += 2, it += 2) {
       const int buf = it & 1, ut = it >> 1;
       const int bi = tile / a.ntile, n = (tile - bi * a.ntile) * L2_NT + qtr * 2 + nj;
       const bool live = t < 12 && n < a.N;
       // sparse spatial aggregation of this warp's spatial columns while the tensor core works on the tile
-      float sp[(BW / 8 + 1) / 2][8];
+      float sp[BW / 8][8];
       MSGAT_UNROLL
-      for (int i = 0; i < (BW / 8 + 1) / 2; ++i)
+      for (int i = 0; i < BW / 8; ++i)
         MSGAT_UNROLL
         for (int j = 0; j < 8; ++j) sp[i][j] = 0.f;
       if (live) {
         const float* pwb = a.pw + mo + (int64_t)bi * a.nnz;
         const float* Zb = a.Z + mo + (int64_t)bi * BW * cs + t;
         const int e1 = a.row_ptr[n + 1];
-        for (int e = a.row_ptr[n]; e < e1; ++e) {
+        int e = a.row_ptr[n];
+        for (; e + 1 < e1; e += 2) {   // two edges per step: their index -> row gathers are independent chains
+          const float w0 = pwb[e], w1 = pwb[e + 1];
+          const float* z0 = Zb + (int64_t)a.col_idx[e] * 12;
+          const float* z1 = Zb + (int64_t)a.col_idx[e + 1] * 12;
+          MSGAT_UNROLL
+          for (int g = 0; g < BW / 8; ++g) {
+            float u0[8], u1[8];
+            MSGAT_UNROLL
+            for (int j = 0; j < 8; ++j) { u0[j] = z0[(int64_t)(g * 8 + j) * cs]; u1[j] = z1[(int64_t)(g * 8 + j) * cs]; }
+            MSGAT_UNROLL
+            for (int j = 0; j < 8; ++j) sp[g][j] = fmaf(w1, u1[j], fmaf(w0, u0[j], sp[g][j]));
+          }
+        }
+        if (e < e1) {
           const float w = pwb[e];
           const float* z = Zb + (int64_t)a.col_idx[e] * 12;
           MSGAT_UNROLL
-          for (int g = 0; g < BW / 8; ++g) {
-            if (((8 + g) & 1) != par) continue;   // spatial column groups 8, 9, ... of 8 columns: parity split like below
+          for (int g = 0; g < BW / 8; ++g)
             MSGAT_UNROLL
-            for (int j = 0; j < 8; ++j) sp[g >> 1][j] = fmaf(w, z[(int64_t)(g * 8 + j) * cs], sp[g >> 1][j]);
-          }
+            for (int j = 0; j < 8; ++j) sp[g][j] = fmaf(w, z[(int64_t)(g * 8 + j) * cs], sp[g][j]);
         }
       }
       mbar_wait(TFULL(buf), (uint32_t)(ut & 1));
@@ -574,7 +589,6 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
       float* ob = a.out + (int64_t)m * a.out_sm + (int64_t)bi * 3 * BW * cs + (int64_t)n * 12 + t;
       MSGAT_UNROLL
       for (int g = 0; g < 12; ++g) {
-        if ((g & 1) != par) continue;          // warp-uniform
         if ((g & 3) * 8 >= BW) continue;        // padding columns of a branch (compile-time)
         float v[8];
         if (g < 8) l2_ld8x3(dm + g * 8, dbm + g * 8, dsm + g * 8, a.fp32_grade, v);
@@ -585,7 +599,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
             const int col = g * 8 + j, br = g >> 2, jj = (g & 3) * 8 + j;   // compile-time
             if (jj >= BW) continue;
             float r = v[j] + BIAS[col];
-            if (br == 2) r += sp[(g - 8) >> 1][j];
+            if (br == 2) r += sp[g - 8][j];
             ob[(int64_t)(br * BW + jj) * cs] = fmaxf(r, 0.f);
           }
         }
