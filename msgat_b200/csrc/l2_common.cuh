@@ -36,7 +36,14 @@
                            // of dependent steps per chunk (wait, load, LayerNorm, split, store, fence, arrive: ~2 k cycles
                            // measured); two groups in flight double the chunk rate
 #define L2_PROD_WARP (L2_CONV_WARP0 + L2_CONV_WARPS * L2_CONV_GROUPS)   // one more warp: issues the bulk copies (1-D TMA) of the raw rows
-#define L2_THREADS ((L2_PROD_WARP + 1) * 32)
+#define L2_PROD_WARPS 2    // a bulk copy takes per-lane operands through the uniform datapath, so a warp issues its rows one
+                           // after the other (R2UR loop in the SASS).  In k_l2_mix, whose converters are light, ONE producer
+                           // warp issuing the 24 copies of a chunk was the longest stage (ncu: the producer never idle, every
+                           // other role waiting): 477 us with one producer warp, 350 us with two or three.  k_l2_out is bound
+                           // by its converters and gains nothing (measured 1.12 / 1.15 / 1.19 ms with 1 / 2 / 3); it keeps one
+                           // producer warp and the higher register cap of a 704-thread block.
+#define L2_THREADS_NP(np) ((L2_PROD_WARP + (np)) * 32)
+#define L2_THREADS L2_THREADS_NP(L2_PROD_WARPS)
 #define L2_BAR_BYTES 16    // an mbarrier is 8 bytes; the host-fiber emulation keeps 16
 
 // round to TF32, nearest with ties away from zero in magnitude: two integer instructions (cvt.rna.tf32.f32 is lowered

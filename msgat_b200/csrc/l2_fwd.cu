@@ -10,6 +10,15 @@
 #include <stdlib.h>
 #include "l2_common.cuh"
 
+// threads of a launch: the role layout of l2_common.cuh with np producer warps (test switch: environment variable)
+static int l2_threads(const char* env, int np_default) {
+  const char* e = getenv(env);
+  int np = e ? atoi(e) : np_default;
+  if (np < 1) np = 1;
+  if (np > np_default) np = np_default;   // the launch bounds of the kernels are compiled for their defaults
+  return L2_THREADS_NP(np);
+}
+
 struct L2MixArgs {
   const float* x; int64_t x_sb, x_sc, x_sm, sv_sm, sc_sm;
   int B, C, N, b, ntile, TPC, KC, fp32_grade;
@@ -54,7 +63,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
 
   // ---- one-time staging: B operand [k = input channel][n = output column], n contiguous, hi / lo, zero padded.
   // columns 0..b-1 W1now, b..2b-1 W1past, 2b..3b-1 Ws, 3b alpha_s, 3b+1 alpha_t
-  for (int i = tid; i < C * 96; i += L2_THREADS) {
+  for (int i = tid; i < C * 96; i += (int)blockDim.x) {
     const int k = i / 96, n = i - k * 96;
     float w = 0.f;
     if (n < a.b) w = PM.conv_w[0][(n * C + k) * 2 + 1];
@@ -81,9 +90,11 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
   const int total = a.B * a.ntile, t_lo = blockIdx.x * a.TPC, t_hi = t_lo + a.TPC < total ? t_lo + a.TPC : total;
   const int64_t cs = (int64_t)a.N * 12;
 
-  if (warp == L2_PROD_WARP) {
-    // ================= producer: bulk copies of the raw rows, one chunk = KC channel rows of the tile =================
+  if (warp >= L2_PROD_WARP) {
+    // ================= producers: bulk copies of the raw rows, one chunk = KC channel rows of the tile; producer warp pw
+    // of np issues the rows pw, pw + np, ... =================
     const float* xm = a.x + (int64_t)m * a.x_sm;
+    const int pw = warp - L2_PROD_WARP, prow = pw + ((int)(blockDim.x >> 5) - L2_PROD_WARP) * lane;
     int q = 0;
     for (int tile = t_lo; tile < t_hi; ++tile) {
       const int bi = tile / a.ntile, n0 = (tile - bi * a.ntile) * L2_NT;
@@ -91,10 +102,10 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
       for (int ch = 0; ch < nchunk; ++ch, ++q) {
         const int rs = q % L2M_NR, use = q / L2M_NR;
         if (use > 0) mbar_wait(REMPTY(rs), (uint32_t)((use - 1) & 1));   // every converter warp has read this slot
-        if (lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(KC * nv * 48));
-        if (lane < KC)
-          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)lane * L2_RAW_ROW,
-                   xm + (int64_t)bi * a.x_sb + (int64_t)(ch * KC + lane) * a.x_sc + (int64_t)n0 * 12, (uint32_t)(nv * 48), RFULL(rs));
+        if (pw == 0 && lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(KC * nv * 48));
+        if (prow < KC)
+          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)prow * L2_RAW_ROW,
+                   xm + (int64_t)bi * a.x_sb + (int64_t)(ch * KC + prow) * a.x_sc + (int64_t)n0 * 12, (uint32_t)(nv * 48), RFULL(rs));
       }
     }
   } else if (warp >= L2_CONV_WARP0) {
@@ -249,9 +260,9 @@ int launch_l2_mix(const Plan& p, const msgat_meam_params* prm, const float* x, f
   a.pqc = scratch + p.o_pqc;
   const size_t smem = l2_mix_smem(p.C, a.KC);
   switch (p.Oc) {
-    case 8: MSGAT_LAUNCH(k_l2_mix<8>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
-    case 16: MSGAT_LAUNCH(k_l2_mix<16>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
-    default: MSGAT_LAUNCH(k_l2_mix<24>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    case 8: MSGAT_LAUNCH(k_l2_mix<8>, dim3(G, p.M), dim3(l2_threads("MSGAT_L2_NP_MIX", L2_PROD_WARPS)), smem, stream, a); break;
+    case 16: MSGAT_LAUNCH(k_l2_mix<16>, dim3(G, p.M), dim3(l2_threads("MSGAT_L2_NP_MIX", L2_PROD_WARPS)), smem, stream, a); break;
+    default: MSGAT_LAUNCH(k_l2_mix<24>, dim3(G, p.M), dim3(l2_threads("MSGAT_L2_NP_MIX", L2_PROD_WARPS)), smem, stream, a); break;
   }
   return 0;
 }
@@ -288,7 +299,7 @@ static size_t l2_out_smem(int C, int KC, int b) {
 }
 
 template <int BW>
-MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
+MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(1), 1) k_l2_out(L2OutArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int C = a.C, KC = a.KC, nxc = C / KC, RB = KC > BW ? KC : BW, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
@@ -336,25 +347,25 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
     }
   };
   // ---- one-time staging (component constants)
-  for (int i = tid; i < C * 96; i += L2_THREADS) {
+  for (int i = tid; i < C * 96; i += (int)blockDim.x) {
     const int k = i / 96, n = i - k * 96, br = n >> 5, j = n & 31;
     l2_split1(WRH, WRL, sw128b32_off(k, n, cbW), j < BW ? PM.res_w[(br * BW + j) * C + k] : 0.f);
   }
-  for (int i = tid; i < 2 * BW * 32; i += L2_THREADS) {
+  for (int i = tid; i < 2 * BW * 32; i += (int)blockDim.x) {
     const int k = i >> 5, n = i & 31;
     float w = 0.f;
     if (n < BW) w = k < BW ? PM.conv_w[1][(n * BW + k) * 2 + 1] : PM.conv_w[1][(n * BW + (k - BW)) * 2 + 0];
     l2_split1(W2H, W2L, sw128b32_off(k, n, cbY), w);
   }
-  for (int i = tid; i < 96; i += L2_THREADS) {
+  for (int i = tid; i < 96; i += (int)blockDim.x) {
     const int br = i >> 5, j = i & 31;
     float v = 0.f;
     if (j < BW) v = PM.res_b[br * BW + j] + (br == 0 ? PM.ca_b[j] : (br == 1 ? PM.conv_b[1][j] : 0.f));
     BIAS[i] = v;
   }
-  for (int i = tid; i < 32; i += L2_THREADS) C1B[i] = i < BW ? PM.conv_b[0][i] : 0.f;
+  for (int i = tid; i < 32; i += (int)blockDim.x) C1B[i] = i < BW ? PM.conv_b[0][i] : 0.f;
   if (tid < 12) { LW[tid] = PM.ln_w[tid]; LW[12 + tid] = PM.ln_b[tid]; }
-  if (t_lo < t_hi) stage_sample(t_lo / a.ntile, tid, L2_THREADS);
+  if (t_lo < t_hi) stage_sample(t_lo / a.ntile, tid, (int)blockDim.x);
   if (tid == 0) {
     for (int i = 0; i < L2O_NSTG; ++i) { mbar_init(FULL(i), L2_CONV_WARPS); mbar_init(EMPTY(i), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(TFULL(i), 1); mbar_init(TEMPTY(i), L2_EPI_WARPS / 2); }
@@ -371,7 +382,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
   const int IT = nxc + 1, NRAW = nxc + 2;   // work items and raw chunks per tile
 
   if (warp == L2_PROD_WARP) {
-    // ================= producer =================
+    // ================= producer (one warp: this kernel is bound by its converters, see l2_common.cuh) =================
     const float* xm = a.x + (int64_t)m * a.x_sm;
     int r = 0;
     for (int tile = t_lo; tile < t_hi; ++tile) {
@@ -561,26 +572,19 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_out(L2OutArgs a) {
         const float* Zb = a.Z + mo + (int64_t)bi * BW * cs + t;
         const int e1 = a.row_ptr[n + 1];
         int e = a.row_ptr[n];
-        for (; e + 1 < e1; e += 2) {   // two edges per step: their index -> row gathers are independent chains
-          const float w0 = pwb[e], w1 = pwb[e + 1];
-          const float* z0 = Zb + (int64_t)a.col_idx[e] * 12;
-          const float* z1 = Zb + (int64_t)a.col_idx[e + 1] * 12;
-          MSGAT_UNROLL
-          for (int g = 0; g < BW / 8; ++g) {
-            float u0[8], u1[8];
-            MSGAT_UNROLL
-            for (int j = 0; j < 8; ++j) { u0[j] = z0[(int64_t)(g * 8 + j) * cs]; u1[j] = z1[(int64_t)(g * 8 + j) * cs]; }
-            MSGAT_UNROLL
-            for (int j = 0; j < 8; ++j) sp[g][j] = fmaf(w1, u1[j], fmaf(w0, u0[j], sp[g][j]));
-          }
-        }
-        if (e < e1) {
-          const float w = pwb[e];
-          const float* z = Zb + (int64_t)a.col_idx[e] * 12;
+        float w = e < e1 ? pwb[e] : 0.f;
+        int col = e < e1 ? a.col_idx[e] : 0;
+        while (e < e1) {
+          // index and weight of the NEXT edge are requested before this edge's rows: the index -> row chain of
+          // dependent gathers overlaps with the row loads of the edge before it
+          const float wn = e + 1 < e1 ? pwb[e + 1] : 0.f;
+          const int cn = e + 1 < e1 ? a.col_idx[e + 1] : 0;
+          const float* z = Zb + (int64_t)col * 12;
           MSGAT_UNROLL
           for (int g = 0; g < BW / 8; ++g)
             MSGAT_UNROLL
             for (int j = 0; j < 8; ++j) sp[g][j] = fmaf(w, z[(int64_t)(g * 8 + j) * cs], sp[g][j]);
+          w = wn; col = cn; ++e;
         }
       }
       mbar_wait(TFULL(buf), (uint32_t)(ut & 1));
@@ -627,9 +631,9 @@ int launch_l2_out(const Plan& p, const msgat_meam_params* prm, const msgat_adj* 
   a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out;
   const size_t smem = l2_out_smem(p.C, a.KC, p.Oc);
   switch (p.Oc) {
-    case 8: MSGAT_LAUNCH(k_l2_out<8>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
-    case 16: MSGAT_LAUNCH(k_l2_out<16>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
-    default: MSGAT_LAUNCH(k_l2_out<24>, dim3(G, p.M), dim3(L2_THREADS), smem, stream, a); break;
+    case 8: MSGAT_LAUNCH(k_l2_out<8>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
+    case 16: MSGAT_LAUNCH(k_l2_out<16>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
+    default: MSGAT_LAUNCH(k_l2_out<24>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
   }
   return 0;
 }
