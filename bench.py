@@ -201,6 +201,7 @@ def algorithmic_bytes(kernel: str, S: int, N: int):
         # layer-2 pipelined tcgen05 kernels (csrc/l2_*.cu)
         "k_l2_mix": (C + 3 * b) * A,                   # x in; first-conv taps a_now | a_past and Z out
         "k_l2_out": (C + 2 * b + Cz + O + b) * A,      # x, taps, Z gather; out and Y1
+        "k_l2_gz": 3 * b * A,                          # G_s and Z in (the per-edge gathers hit L2), GZ out
         "k_l2_dy": (2 * b + 2 * b + b + 3 * b) * A,    # G_t, G_s, taps, Z gather; dA_now | dA_past | GZ
         "k_l2_dx": (2 * C + O + 3 * b) * A,            # G, dA/GZ, x; dx
     }

@@ -8,6 +8,9 @@
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream);
+// l2_sparse_bwd.cu: transposed sparse aggregation GZ, dS at the non-zeros and its row sums, all components in one launch
+int launch_l2_gz(const Plan& p, const msgat_adj* adj, const float* G, int64_t g_sm, const float* saved, float* tcA, float* delta,
+                 float* dSnz, void* stream);
 // spatial_tc.cu: the same two passes on tcgen05 (MSGAT_PREC_TF32)
 bool score_tc_supported(const Plan& p);
 int launch_sstats_tc(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);

@@ -1202,6 +1202,21 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     if (rc) return rc;
     return meam_backward_tail(p, L, L.J, prm, adj, x, saved, scratch, dx, g, stream);
   }
+  if (need_mask) {
+    const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
+    int blocks = (int)((n4 + 255) / 256);
+    if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
+    for (int m = 0; m < M; ++m)
+      MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)(dout + m * out_sm), (const float4*)(out + m * out_sm),
+                   (float4*)(scratch + m * sc_sm + L.o_G), n4);
+  }
+#ifndef MSGAT_EMU
+  if (tc_d) {   // the sparse stages of all components in one launch (l2_sparse_bwd.cu): GZ -> tcA rows [2b, 3b), dSnz, delta
+    rc = launch_l2_gz(p, adj, need_mask ? scratch + L.o_G : dout, need_mask ? sc_sm : out_sm, saved, scratch + L.o_tcA,
+                      scratch + L.o_delta, scratch + L.o_dSnz, stream);
+    if (rc) return rc;
+  }
+#endif
   // ---- the passes over the activations: still one launch per component (buffers by pointer offset)
   for (int m = 0; m < M; ++m) {
     const float* xm = x + m * p.x_sm;
@@ -1209,15 +1224,7 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     float* scr = scratch + m * sc_sm;
     float* dxm = dx + m * dx_sm;
     const msgat_meam_params* prmm = prm + m;
-    const float* G = dout + m * out_sm;
-    if (need_mask) {
-      const int64_t n4 = (int64_t)p.B * p.O * p.N * 3;
-      int blocks = (int)((n4 + 255) / 256);
-      if (blocks > msgat_sm_count() * 8) blocks = msgat_sm_count() * 8;
-      MSGAT_LAUNCH(k_relu_mask, dim3(blocks), dim3(256), 0, stream, (const float4*)G, (const float4*)(out + m * out_sm),
-                   (float4*)(scr + L.o_G), n4);
-      G = scr + L.o_G;
-    }
+    const float* G = need_mask ? scr + L.o_G : dout + m * out_sm;
 #ifndef MSGAT_EMU
     if (tc_d) {
       rc = launch_tc_dgrad(p, prmm, adj, xm, G, savedm, scr + L.o_tcA, dxm, scr + L.o_delta, scr + L.o_dSnz, scr + L.o_bias,

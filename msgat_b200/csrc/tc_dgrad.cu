@@ -166,9 +166,6 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
   const float* xb = a.x + bi * a.x_sb;
   const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
-  const float* Gs = Gb + (int64_t)2 * b * a.N * 12;
-  const float* pwb = a.pw + (int64_t)bi * a.nnz;
-  const float* Zb = a.Z + (int64_t)bi * b * a.N * 12;
   const float* A2b = a.A2 + (int64_t)bi * 2 * b * a.N * 12;
   float* tcAb = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
   const int blk = bi * a.J + blockIdx.x;
@@ -221,64 +218,12 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int ks = 0; ks < O / 8; ++ks) td_mma3(Dx, dGH, dGL, dWXH, dWXL, ks, ks, idescC, ks > 0);
       umma_commit(smem_u32(&bar));
     }
-    // ---- while the tensor core runs: GZ[o][i] = sum_n A[n,i] g_s[o][n] through the CSC view (4 channels x
-    // 4 positions per item, kept in registers until the A tile is free), then dS at the adjacency non-zeros
+    // ---- while the tensor core runs: the GZ rows of this tile, computed by k_l2_gz (transposed sparse aggregation
+    // through the CSC view, attention.py:36), come in from the tcA buffer: 4 channels x 4 positions per item
     float4 gz[4] = {f4zero(), f4zero(), f4zero(), f4zero()};
     if (gz_on && n0 + gz_nl < a.N) {
-      const int n = n0 + gz_nl, k1 = a.csc_ptr[n + 1];
-      for (int k = a.csc_ptr[n]; k < k1; ++k) {
-        const float w = pwb[a.csc_eid[k]];
-        const float* gr = Gs + ((int64_t)gz_o0 * a.N + a.csc_row[k]) * 12 + gz_t0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) fma4(gz[j], w, ld4(gr + (int64_t)j * a.N * 12));
-      }
-    }
-    // dS at the adjacency non-zeros and its row sums (attention.py:35-36
-    // transposed): dSnz[e] = A[n,i_e] sum_{o,t} G_s[o,n,t] Z[o,i_e,t]
-    if (warp < TD_NT) {   // one warp per node (the GZ gather above runs on the top warps at the same time)
-      const int n = n0 + warp;
-      float dl = 0.f;
-      if (n < a.N) {
-        const int e0 = a.row_ptr[n], e1 = a.row_ptr[n + 1];
-        // the node's own G_s rows do not depend on the edge: b x 12 values, three float4 per lane at most
-        float4 gs[3];
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-          const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
-          gs[q] = pr < b * 3 ? ld4(Gs + ((int64_t)cz * a.N + n) * 12 + q4) : f4zero();
-        }
-        for (int eb = e0; eb < e1; eb += 32) {
-          const int my = eb + lane < e1 ? a.col_idx[eb + lane] : 0;
-          const float myw = eb + lane < e1 ? pwb[eb + lane] : 0.f;
-          const int cnt = e1 - eb < 32 ? e1 - eb : 32;
-          for (int j = 0; j < cnt; j += 4) {   // four edges in flight: the Z rows are independent gathers
-            float s4[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const float* zr = Zb + (int64_t)__shfl_sync(0xffffffffu, my, (j + u) & 31) * 12;
-              float s = 0.f;
-              if (j + u < cnt) {
-#pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                  const int pr = lane + 32 * q, cz = pr / 3, q4 = (pr - cz * 3) * 4;
-                  if (pr < b * 3) s += dot4(gs[q], ld4(zr + (int64_t)cz * a.N * 12 + q4));
-                }
-              }
-              s4[u] = s;
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const float s = warp_sum(s4[u]);
-              const float dsn = __shfl_sync(0xffffffffu, myw, (j + u) & 31) * s;
-              if (j + u < cnt) {
-                dl += dsn;
-                if (lane == 0) a.dSnz[(int64_t)bi * a.nnz + eb + j + u] = dsn;
-              }
-            }
-          }
-        }
-      }
-      if (lane == 0) DL[warp] = dl;
+      for (int j = 0; j < 4; ++j) gz[j] = ld4(tcAb + ((int64_t)(2 * b + gz_o0 + j) * a.N + n0 + gz_nl) * 12 + gz_t0);
     }
     mbar_wait(smem_u32(&bar), phase); phase ^= 1;
     tc_fence_after_sync();
@@ -296,7 +241,6 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       }
     }
     __syncthreads();
-    if (tid < TD_NT && n0 + tid < a.N) a.delta[(int64_t)bi * a.N + n0 + tid] = DL[tid];
     // ---- 3. rows of 12: dY1, dA_now / dA_past (two threads per row), GZ gather -> the A tile again
     if (tid < 2 * b * TD_NT) {
       const int item = tid >> 1, half = tid & 1, k = item / TD_NT, nl = item - k * TD_NT, n = n0 + nl, pp = nl * 12;
@@ -351,11 +295,9 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       }
     }
     if (gz_on) {
-      const int n = n0 + gz_nl;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         td_split4(GH, GL, sw128b32_off(2 * b + gz_o0 + j, gz_nl * 12 + gz_t0, cbO), gz[j]);
-        if (n < a.N) st4(tcAb + ((int64_t)(2 * b + gz_o0 + j) * a.N + n) * 12 + gz_t0, gz[j]);
       }
     }
     fence_smem_to_async();
