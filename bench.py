@@ -441,10 +441,11 @@ def main():
         sys.stderr.flush()
         if world > 1:
             # orderly: the captured graphs were reset in Run.close(), nothing of NCCL's is in flight any more
-            threading.Timer(30.0, lambda: os._exit(0)).start()   # watchdog only: never hang the driver on a teardown
+            wd = threading.Timer(60.0, lambda: os._exit(3))   # watchdog only (exit code 3 = the teardown hung); daemon: it
+            wd.daemon = True                                   # does not keep a finished process alive
+            wd.start()
             barrier()
             dist.destroy_process_group()
-            os._exit(0)
 
     if rank != 0:
         finish()

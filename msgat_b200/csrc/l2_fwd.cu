@@ -85,7 +85,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tm = *tmem_slot;
+  const uint32_t tm = warp_uniform(*tmem_slot);
   const int ncol = ((b3 + 2) + 15) & ~15;            // accumulator columns (N of the MMA)
   const int total = a.B * a.ntile, t_lo = blockIdx.x * a.TPC, t_hi = t_lo + a.TPC < total ? t_lo + a.TPC : total;
   const int64_t cs = (int64_t)a.N * 12;
@@ -378,7 +378,7 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(1), 1) k_l2_out(L2OutArgs a) {
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tm = *tmem_slot;
+  const uint32_t tm = warp_uniform(*tmem_slot);
   const int IT = nxc + 1, NRAW = nxc + 2;   // work items and raw chunks per tile
 
   if (warp == L2_PROD_WARP) {

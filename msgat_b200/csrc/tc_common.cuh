@@ -71,6 +71,7 @@ TC_DEV void fence_smem_to_async() {}
 TC_DEV void tmem_alloc(uint32_t slot_smem, uint32_t) { *reinterpret_cast<uint32_t*>(emu_smem_at(slot_smem)) = 0u; __syncwarp(); }
 TC_DEV void tmem_dealloc(uint32_t, uint32_t) {}
 TC_DEV uint32_t tmem_addr(uint32_t base, int lane, int col) { return base + ((uint32_t)lane << 16) + (uint32_t)col; }
+TC_DEV uint32_t warp_uniform(uint32_t v) { return v; }
 TC_DEV float* emu_tmem(uint32_t addr) {
   const int lane_base = (int)(addr >> 16), col = (int)(addr & 0xffffu), warp = emu::cur()->lin >> 5, lane = emu::cur()->lin & 31;
   if (lane_base != 32 * (warp & 3)) { fprintf(stderr, "emu: warp %d reads TMEM lanes %d.. (allowed: %d..)\n", warp, lane_base, 32 * (warp & 3)); abort(); }
@@ -131,6 +132,11 @@ TC_DEV void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t 
     }
 }
 TC_DEV void umma_commit(uint32_t bar) { mbar_arrive(bar); }
+// converged-warp variants: the emulated warp's lane 0 is the elected lane
+TC_DEV void umma_tf32_e(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if ((threadIdx.x & 31) == 0) umma_tf32(d_tmem, adesc, bdesc, idesc, accumulate);
+}
+TC_DEV void umma_commit_e(uint32_t bar) { if ((threadIdx.x & 31) == 0) umma_commit(bar); }
 #else
 
 #include <cuda_runtime.h>
@@ -234,6 +240,12 @@ TC_DEV void tmem_ld8_nowait(uint32_t addr, uint32_t (&r)[8]) {
 }
 TC_DEV void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 TC_DEV uint32_t tmem_addr(uint32_t base, int lane, int col) { return base + ((uint32_t)lane << 16) + (uint32_t)col; }
+// A value every lane of the (converged, full) warp holds, handed back through the uniform datapath (REDUX writes a
+// uniform register).  tcgen05.mma takes its TMEM address from a uniform register; for an address the compiler cannot
+// prove uniform (the TMEM base is read from shared memory) it wraps EVERY MMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY
+// loop, ~12 dependent uniform-datapath instructions of ~10 cycles each: the MMA-issuing thread of k_l2_out spent 130
+// cycles per MMA on it and was the pipeline's bottleneck (ncu: 76 % of its samples in the issue code).
+TC_DEV uint32_t warp_uniform(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }
 
 // ---- descriptors -------------------------------------------------------------------------
 // Shared-memory matrix descriptor, 128-byte swizzle (layout type 2), version 1 (sm_100).
@@ -271,6 +283,25 @@ TC_DEV void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t 
 // (implies tcgen05.fence::before_thread_sync).
 TC_DEV void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// The same two instructions for a CONVERGED warp: every lane runs the issue loop (waits, descriptor arithmetic in the
+// uniform datapath) and one elected lane executes the tcgen05 instruction.  Inside an `if (lane == 0)` region the
+// compiler cannot know that a single lane is active and wraps every MMA in an ELECT / BRA.U.ANY loop.
+TC_DEV void umma_tf32_e(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+TC_DEV void umma_commit_e(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
 }
 
 #endif  // MSGAT_EMU
