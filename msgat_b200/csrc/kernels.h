@@ -15,6 +15,10 @@ int launch_l2_gz(const Plan& p, const msgat_adj* adj, const float* G, int64_t g_
 bool score_tc_supported(const Plan& p);
 int launch_sstats_tc(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
 int launch_scol_tc(const Plan& p, const float* saved, const float* delta, float* dq, void* stream);
+// spatial_tc32.cu: the scores on tcgen05 at fp32 grade (three-way operand split), the rest as in spatial.cu (MSGAT_PREC_FP32)
+bool score_tc32_supported(const Plan& p);
+int launch_sstats_tc32(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream);
+int launch_scol_tc32(const Plan& p, const float* saved, const float* delta, float* dq, void* stream);
 int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
                       float* saved, float* scratch, void* stream);
 int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* out,

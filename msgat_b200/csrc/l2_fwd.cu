@@ -41,7 +41,7 @@ static size_t l2_mix_smem(int C, int KC) {
 template <int BW>
 MSGAT_KERNEL MSGAT_LB(L2_THREADS, 1) k_l2_mix(L2MixArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
   const int C = a.C, b3 = 3 * a.b, KC = a.KC, nchunk = C / KC, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
   const msgat_meam_params& PM = a.prm[m];
   const uint32_t cbW = (uint32_t)C * 128u, cbA = (uint32_t)KC * 128u, chunk_bytes = (uint32_t)KC * 128u * 4u;
@@ -301,7 +301,7 @@ static size_t l2_out_smem(int C, int KC, int b) {
 template <int BW>
 MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(1), 1) k_l2_out(L2OutArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
   const int C = a.C, KC = a.KC, nxc = C / KC, RB = KC > BW ? KC : BW, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
   const msgat_meam_params& PM = a.prm[m];
   const uint32_t cbW = (uint32_t)C * 128u, cbY = (uint32_t)(2 * BW) * 128u, cbX = (uint32_t)KC * 128u, cbB = (uint32_t)BW * 128u;

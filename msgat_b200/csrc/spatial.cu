@@ -149,6 +149,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_sstats(SStatsArgs a) {
 
 int launch_sstats(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, float* saved, void* stream) {
   if (score_tc_supported(p)) return launch_sstats_tc(p, prm, adj, saved, stream);
+  if (score_tc32_supported(p)) return launch_sstats_tc32(p, prm, adj, saved, stream);
   SStatsArgs a;
   a.N = p.N; a.nnz = p.nnz;
   a.sv_sm = p.saved_total;
@@ -248,6 +249,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_scol(SColArgs a) {
 
 int launch_scol(const Plan& p, const float* Wg, const float* saved, const float* delta, float* dq, void* stream) {
   if (score_tc_supported(p)) return launch_scol_tc(p, saved, delta, dq, stream);
+  if (score_tc32_supported(p)) return launch_scol_tc32(p, saved, delta, dq, stream);
   SColArgs a;
   a.N = p.N; a.sv_sm = p.saved_total; a.sc_sm = p.scratch_sm;
   a.qs = saved + p.o_qs; a.U = saved + p.o_U; a.m = saved + p.o_m; a.l = saved + p.o_l; a.delta = delta; a.dq = dq;

@@ -57,7 +57,7 @@ static inline size_t score_tc_smem() {
 template <int BWD>
 MSGAT_KERNEL MSGAT_LB(ST_THREADS, 2) k_score_tc(STcArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
   unsigned char* RA = smem;                       // row block  [128][16]   (forward: U, backward: q), TF32
   unsigned char* CB = RA + 8192;                  // column tile [128][16]  (forward: q, backward: U)
   unsigned char* CT = CB + 8192;                  // its transpose [16][128]

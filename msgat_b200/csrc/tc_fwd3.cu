@@ -82,7 +82,7 @@ TC_DEV void tmem_ld8_sum(uint32_t addr, float (&v)[8]) {
 
 __global__ void __launch_bounds__(TF3_THREADS, 1) k_tc_apply3(TcApply3Args a) {
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
   const int C = a.C, b = a.b, O = a.O, tid = threadIdx.x, warp = tid >> 5, bi = blockIdx.y;
   const uint32_t cbX = (uint32_t)C * 128u, cbY = (uint32_t)(2 * b) * 128u;
   unsigned char* AH = smem;

@@ -16,13 +16,14 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("MSGAT_REFERENCE", "/root/reference/src")
 OUT = os.path.join(HERE, "_ref")
 FILES = ["models/__init__.py", "models/attention.py", "models/embeddings.py", "models/msgat.py", "loss.py", "metrics.py"]
+EXTRA = ["engine.py"]   # the reference's train / validate loop: drives the drop-in in tests/test_gpu_engine.py
 
 
 def make(force: bool = False) -> bool:
     """Copies the files; returns True when oracle/_ref is usable afterwards."""
     if not os.path.isdir(REF):
         return available()
-    for f in FILES:
+    for f in FILES + EXTRA:
         src, dst = os.path.join(REF, f), os.path.join(OUT, f)
         os.makedirs(os.path.dirname(dst), exist_ok=True)
         if force or not os.path.exists(dst) or os.path.getmtime(dst) < os.path.getmtime(src):
@@ -49,6 +50,15 @@ def load():
         if not os.path.abspath(mod.__file__).startswith(OUT):
             raise RuntimeError(f"{mod.__name__} was imported from {mod.__file__}, not from oracle/_ref")
     return models, loss, metrics
+
+
+def load_engine():
+    """-> the unmodified reference ``engine`` module (imports ``loss`` / ``metrics`` from oracle/_ref), or None."""
+    if not available() or not os.path.exists(os.path.join(OUT, "engine.py")):
+        return None
+    load()
+    import importlib
+    return importlib.import_module("engine")
 
 
 if __name__ == "__main__":

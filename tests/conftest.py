@@ -65,4 +65,4 @@ def pytest_terminal_summary(terminalreporter):
         return
     terminalreporter.write_line("parity margins (worst over the session): class  n  err/noise  err/tol")
     for cls, r in sorted(parity.RATIOS.items()):
-        terminalreporter.write_line(f"  {cls:12s} {r['n']:5d}  {r['err_over_noise']:9.2f}  {r['err_over_tol']:7.3f}")
+        terminalreporter.write_line(f"  {cls:20s} {r['n']:5d}  {r['err_over_noise']:9.2f}  {r['err_over_tol']:7.3f}")

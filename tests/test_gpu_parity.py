@@ -59,15 +59,18 @@ def compare_with_oracle(model, out, X, ref, ref32, X64, X32, p, p32, floor=FP32_
             rows.append((n, prm.grad, p[n].grad, p32[n].grad))
     noises = [rel_l2(w32, w) for _, _, w, w32 in rows]
     envelope = max(noises)
-    fails = []
+    fails, pending = [], []
     for (label, got, want, _), n in zip(rows, noises):
         scalar = is_attention_scalar(label)
         e, tol = rel_l2(got, want), tolerance(n, envelope, floor, scalar=scalar)
         if cond is not None:
             tol = max(tol, 2.0 * cond.get(label, 0.0))
-        record(tensor_class(label if label in ("out", "dX") else "grad " + label), e, n, tol)
+        pending.append((tensor_class(label if label in ("out", "dX") else "grad " + label) + (" [probe]" if cond is not None else ""), e, n, tol))
         if not e < tol:
             fails.append(f"{label}: {e:.3e} > {tol:.2e} (fp32 oracle noise {n:.2e}, case envelope {envelope:.2e})")
+    if not fails:   # margins of a pass that succeeded; a failing first pass is re-judged with the probe (tests/parity.py)
+        for r in pending:
+            record(*r)
     return fails
 
 

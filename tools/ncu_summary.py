@@ -20,6 +20,11 @@ METRICS = [
     ("FMA pipe active %", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
     ("SM throughput %", "sm__throughput.avg.pct_of_peak_sustained_elapsed"),
     ("DRAM throughput %", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+    ("tensor pipe active % (sm__pipe_tensor_cycles_active)", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
+    ("tensor pipe active %, elapsed", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+    ("tcgen05 instructions % (sm__inst_executed_pipe_tc)", "sm__inst_executed_pipe_tc.sum.pct_of_peak_sustained_active"),
+    ("TMEM instructions % (sm__inst_executed_pipe_tmem)", "sm__inst_executed_pipe_tmem.sum.pct_of_peak_sustained_active"),
+    ("L2 throughput %", "lts__throughput.avg.pct_of_peak_sustained_elapsed"),
     ("L2 hit %", "lts__t_sector_hit_rate.pct"),
     ("warp instructions", "smsp__inst_executed.sum"),
     ("stall long scoreboard (samples)", "smsp__pcsamp_warps_issue_stalled_long_scoreboard"),
@@ -27,6 +32,9 @@ METRICS = [
     ("stall short scoreboard (samples)", "smsp__pcsamp_warps_issue_stalled_short_scoreboard"),
     ("stall wait (samples)", "smsp__pcsamp_warps_issue_stalled_wait"),
     ("stall not selected (samples)", "smsp__pcsamp_warps_issue_stalled_not_selected"),
+    ("stall no instructions (samples)", "smsp__pcsamp_warps_issue_stalled_no_instructions"),
+    ("stall math pipe throttle (samples)", "smsp__pcsamp_warps_issue_stalled_math_pipe_throttle"),
+    ("stall mio throttle (samples)", "smsp__pcsamp_warps_issue_stalled_mio_throttle"),
     ("smem bank conflicts", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"),
 ]
 
