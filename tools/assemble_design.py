@@ -1,0 +1,71 @@
+"""Developer helper: DESIGN.md = tools/design_parts/*.md with the measured tables filled in from profiles/r02_final_*.json.
+
+    python tools/assemble_design.py
+"""
+import glob
+import io
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+P = os.path.join(ROOT, "profiles")
+
+
+def line(path):
+    try:
+        return json.loads([l for l in open(os.path.join(P, path)) if l.startswith("{")][-1])
+    except Exception:
+        return None
+
+
+def row(label, d, key=None):
+    if d is None:
+        return f"| {label} | (not measured) | |"
+    if key:
+        d = d[key]
+    return f"| {label} | {d['value']:.0f} | {d['ms_per_step']:.2f} |"
+
+
+def main():
+    main_run = line("r02_final_bench.json")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "kernel_table.py"), os.path.join(P, "r02_final_bench.json")],
+                         capture_output=True, text=True).stdout
+    ktable = ("**Measured (B200, PEMSD7 B=32, fp32-grade path, `profiles/r02_final_bench.json`; per-kernel CUDA events of the library's "
+              "profiler):** " + out)
+    res = ["* Results on the B200 pool (this round, `profiles/r02_final_*.json`; round 1 for comparison: 2814 samples/s, 11.37 ms/step):", "",
+           "| Run | samples/s | ms/step |", "|---|---|---|"]
+    res.append(row("1 GPU, default (fp32-grade), CUDA graph, inputs resident in HBM", main_run))
+    if main_run:
+        e = main_run["e2e"]
+        res.append(f"| 1 GPU, end to end through the module API, H2D of the batch (8.1 MB) and D2H of the loss inside the timed region | {e['value']:.0f} | {e['ms_per_step']:.2f} |")
+    res.append(row("1 GPU, `--precision tf32` (single-pass TF32 channel mixes in pass 2, score passes fully on tcgen05; 2e-3 bar)", line("r02_final_bench_tf32.json")))
+    for n in (2, 4, 8):
+        d = line(f"r02_final_bench_{n}gpu.json")
+        res.append(row(f"{n} GPUs, weak scaling (batch 32 per GPU)", d))
+        if d and d.get("strong"):
+            res.append(row(f"{n} GPUs, strong scaling (GLOBAL batch 32, {32 // n} per GPU)", d, "strong"))
+    for cfg, desc in (("pemsd8", "PEMSD8 (N=170, C=3, B=64)"), ("pemsd4", "PEMSD4 (N=307, C=3, B=64)"), ("pemsd3", "PEMSD3 (N=358, C=1, M=4, B=64)"),
+                      ("n4096", "N=4096, C=3, B=16")):
+        res.append(row(f"1 GPU, {desc}", line(f"r02_final_bench_cfg_{cfg}.json")))
+    ref = line("r02_final_bench_reference_arm.json")
+    if ref:
+        cb = ref["cpu_baseline"]
+        res.append(f"| reference arm: the unmodified reference modules on the box's {cb['cores']} host cores (`kind: \"{cb['kind']}\"`) | {ref['value']:.1f} | {ref['ms_per_step']:.0f} |")
+    res.append("")
+    res.append("  BASELINE.md holds no published throughput for this metric (`vs_baseline: null`).")
+    text = ""
+    for f in sorted(glob.glob(os.path.join(ROOT, "tools", "design_parts", "*.md"))):
+        text += open(f).read()
+    text = text.replace("KERNEL_TABLE_PLACEHOLDER", ktable).replace("RESULTS_PLACEHOLDER", "\n".join(res))
+    if main_run:
+        text = text.replace("STEP_MS", f"{main_run['ms_per_step']:.2f}")
+    gpu_tests = open(os.path.join(P, "r02_final_pytest_gpu.log")).read().strip().splitlines()[-1] if os.path.exists(os.path.join(P, "r02_final_pytest_gpu.log")) else "see profiles"
+    text = text.replace("GPU_TESTS", "`" + gpu_tests.strip() + "`").replace("CPU_TESTS", "89")
+    open(os.path.join(ROOT, "DESIGN.md"), "w").write(text)
+    print("DESIGN.md written,", len(text), "bytes")
+
+
+if __name__ == "__main__":
+    main()
