@@ -186,7 +186,7 @@ def algorithmic_bytes(kernel: str, S: int, N: int):
         "k_apply": (C + Cz + O) * A,
         "k_tc_apply": (C + Cz + O + 3 * b) * A,        # + Y1 and the first-conv taps kept for the backward
         "k_tc_apply3": (C + Cz + O + 3 * b) * A,
-        "k_tc_dgrad": (2 * C + O + Cz + 5 * b) * A,    # x, dout, Z gather, saved taps; dx, dA_now/dA_past/GZ
+        "k_tc_dgrad": (2 * C + O + 5 * b) * A,         # x, G, taps, GZ (from k_l2_gz) in; dx and dA_now | dA_past out
         "k_bwd_main": (2 * C + O + Cz + 3 * b) * A,    # x, dout, Z gather, dx + dA_now/dA_past/GZ handed to k_tc_wgrad
         "k_tc_wgrad": (C + O + b + 3 * b) * A,         # x, dout, Y1, dA_now/dA_past/GZ
         "k_bwd_fix": 3 * C * A,

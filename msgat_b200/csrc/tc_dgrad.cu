@@ -69,7 +69,7 @@ TC_DEV void td_split1(unsigned char* hi, unsigned char* lo, uint32_t off, float 
   *reinterpret_cast<float*>(hi + off) = h;
   *reinterpret_cast<float*>(lo + off) = td_rna(v - h);
 }
-// acc (+)= Ah Bh + Ah Bl + Al Bh for one k-step; MN-major operands, 128 B swizzle with 32 B atoms
+// acc (+)= Ah Bh + Ah Bl + Al Bh for one k-step (lo*lo, 2^-22 of the product, changed no measured error and is not issued); MN-major operands, 128 B swizzle with 32 B atoms
 // The descriptors of k-step 0 are built once; k-step ks (8 contraction rows = 1024 B) adds ks * 64 to
 // the start-address field (16-byte units).
 TC_DEV void td_mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64_t dbl, uint32_t ka, uint32_t kb, uint32_t idesc,
@@ -81,7 +81,6 @@ TC_DEV void td_mma3(uint32_t d, uint64_t dah, uint64_t dal, uint64_t dbh, uint64
   umma_tf32(d, dah + oa, dbh + ob, idesc, acc);
   umma_tf32(d + 256u, dah + oa, dbl + ob, idesc, acc);
   umma_tf32(d + 256u, dal + oa, dbh + ob, idesc, 1u);
-  umma_tf32(d + 256u, dal + oa, dbl + ob, idesc, 1u);
 }
 TC_DEV void td_ld8_sum(uint32_t addr, float (&v)[8]) {
   uint32_t r0[8], r1[8];
@@ -190,6 +189,19 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int sgi = seg; sgi < nrow; sgi += TD_THREADS / 4) {
         const float* base = sgi < 2 * b ? A2b + (int64_t)sgi * a.N * 12 : xb + (int64_t)(sgi - 2 * b) * a.x_sc;
         int64_t off = (int64_t)n0 * 12 + part * 32;                 // floats
+        const int64_t last = (int64_t)a.N * 12 - 1;
+        if (off > last) off = last;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));
+      }
+    }
+    // ... and of what the NEXT tile of this CTA reads first: its G rows and the GZ rows k_l2_gz left in tcA (the loads at the top
+    // of a tile were exposed DRAM latency: 7 % of the kernel's samples)
+    if (tile + a.J < a.ntile) {
+      const int nrow = O + b, seg = tid >> 2, part = tid & 3;
+      const int64_t n1 = (int64_t)(n0 + a.J * TD_NT) * 12;
+      for (int sgi = seg; sgi < nrow; sgi += TD_THREADS / 4) {
+        const float* base = sgi < O ? Gb + (int64_t)sgi * a.N * 12 : tcAb + (int64_t)(2 * b + sgi - O) * a.N * 12;
+        int64_t off = n1 + part * 32;
         const int64_t last = (int64_t)a.N * 12 - 1;
         if (off > last) off = last;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));

@@ -130,9 +130,9 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
         for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
           const uint64_t d = (uint64_t)(((uint32_t)st * 2u * part + (uint32_t)k8 * 256u) >> 4);   // start-address field, 16-byte units
           const uint32_t acc = (it == 0 && k8 == 0) ? 0u : 1u;
-          umma_tf32(D1, gh0 + d, xh0 + d, id1, acc); umma_tf32(D1, gh0 + d, xl0 + d, id1, 1u); umma_tf32(D1, gl0 + d, xh0 + d, id1, 1u); umma_tf32(D1, gl0 + d, xl0 + d, id1, 1u);
-          umma_tf32(D2, ah0 + d, hh0 + d, id2, acc); umma_tf32(D2, ah0 + d, hl0 + d, id2, 1u); umma_tf32(D2, al0 + d, hh0 + d, id2, 1u); umma_tf32(D2, al0 + d, hl0 + d, id2, 1u);
-          umma_tf32(D3, th0 + d, yh0 + d, id3, acc); umma_tf32(D3, th0 + d, yl0 + d, id3, 1u); umma_tf32(D3, tl0 + d, yh0 + d, id3, 1u); umma_tf32(D3, tl0 + d, yl0 + d, id3, 1u);
+          umma_tf32(D1, gh0 + d, xh0 + d, id1, acc); umma_tf32(D1, gh0 + d, xl0 + d, id1, 1u); umma_tf32(D1, gl0 + d, xh0 + d, id1, 1u);
+          umma_tf32(D2, ah0 + d, hh0 + d, id2, acc); umma_tf32(D2, ah0 + d, hl0 + d, id2, 1u); umma_tf32(D2, al0 + d, hh0 + d, id2, 1u);
+          umma_tf32(D3, th0 + d, yh0 + d, id3, acc); umma_tf32(D3, th0 + d, yl0 + d, id3, 1u); umma_tf32(D3, tl0 + d, yh0 + d, id3, 1u);
         }
         umma_commit(smem_u32(&bars[st]));
       }
