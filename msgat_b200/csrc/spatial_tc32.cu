@@ -200,12 +200,12 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
           for (int i = 0; i < 8; ++i)   // static register indices (a dynamic pick turns s[] into a local-memory array)
             if (nc == cbase + i) { pwb[e] = s[i]; ++e; nc = e < e1 ? a.col_idx[e] : 0x7fffffff; }
         }
-        float mg = -INFINITY;
+        if (cbase + 8 > a.N) {   // warp-uniform: only the last chunk of a row has columns beyond N
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (cbase + i >= a.N) s[i] = -INFINITY;
-          mg = fmaxf(mg, s[i]);
+          for (int i = 0; i < 8; ++i)
+            if (cbase + i >= a.N) s[i] = -INFINITY;
         }
+        const float mg = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), fmaxf(fmaxf(s[4], s[5]), fmaxf(s[6], s[7])));
         if (mg > m) {
           const double c = (double)expf(m - mg);
           l *= c;
