@@ -63,8 +63,9 @@ int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream);
 bool tc_dgrad_supported(const Plan& p);
 int tc_dgrad_blocks_per_sample(const Plan& p);
-int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
-                    const float* saved, float* tcA, float* dx, float* delta, float* dSnz, float* bias_part, int nbias,
-                    float* ln_part, double* dPt_part, void* stream);
+// grouped: all p.M components in one launch (inputs x_sm / g_sm apart, saved / scratch slices, dx dx_sm apart)
+int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G, int64_t g_sm,
+                    const float* saved, float* tcA, float* dx, int64_t dx_sm, float* bias_part, int nbias, float* ln_part,
+                    double* dPt_part, void* stream);
 int launch_tc_apply(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, float* out,
                     float* saved, void* stream);

@@ -1215,9 +1215,13 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     rc = launch_l2_gz(p, adj, need_mask ? scratch + L.o_G : dout, need_mask ? sc_sm : out_sm, saved, scratch + L.o_tcA,
                       scratch + L.o_delta, scratch + L.o_dSnz, stream);
     if (rc) return rc;
+    // ... and the node-local data gradients of all components in one persistent launch (tc_dgrad.cu)
+    rc = launch_tc_dgrad(p, prm, adj, x, need_mask ? scratch + L.o_G : dout, need_mask ? sc_sm : out_sm, saved, scratch + L.o_tcA, dx,
+                         dx_sm, scratch + L.o_bias, L.nbias, scratch + L.o_ln, reinterpret_cast<double*>(scratch + L.o_dPt), stream);
+    if (rc) return rc;
   }
 #endif
-  // ---- the passes over the activations: still one launch per component (buffers by pointer offset)
+  // ---- the remaining passes over the activations: one launch per component (buffers by pointer offset)
   for (int m = 0; m < M; ++m) {
     const float* xm = x + m * p.x_sm;
     const float* savedm = saved + m * sv_sm;
@@ -1225,13 +1229,6 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
     float* dxm = dx + m * dx_sm;
     const msgat_meam_params* prmm = prm + m;
     const float* G = need_mask ? scr + L.o_G : dout + m * out_sm;
-#ifndef MSGAT_EMU
-    if (tc_d) {
-      rc = launch_tc_dgrad(p, prmm, adj, xm, G, savedm, scr + L.o_tcA, dxm, scr + L.o_delta, scr + L.o_dSnz, scr + L.o_bias,
-                           L.nbias, scr + L.o_ln, reinterpret_cast<double*>(scr + L.o_dPt), stream);
-      if (rc) return rc;
-    }
-#endif
     if (!tc_d) {
       BwdArgs a;
       a.x = xm; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;

@@ -29,11 +29,12 @@
 #define TD_NGR 32      // 9-thread groups of the dPt contraction
 #define TD_ISSUER 320  // MMA-issuing thread: warp 10 has no work inside the two MMA windows, so nothing waits for the issue
 
-struct TcDgradArgs {
-  const float* x; int64_t x_sb, x_sc;
+struct TcDgradArgs {   // grouped: blockIdx.y = component; inputs x_sm / g_sm apart, saved slices sv_sm, scratch slices sc_sm, dx dx_sm apart
+  const float* x; int64_t x_sb, x_sc, x_sm, g_sm, sv_sm, sc_sm, dx_sm;
   const float* G;
-  int C, N, O, b, ntile, J, d1, d2, nnz, x_is_relu, nbias;
-  const float *ln_w, *ln_b, *res_w, *c1_w, *c2_w, *sa_W;
+  int C, N, O, b, ntile, J, B, d1, d2, nnz, x_is_relu, nbias;
+  const float *ln_w[MSGAT_MAX_GROUP], *ln_b[MSGAT_MAX_GROUP], *res_w[MSGAT_MAX_GROUP], *c1_w[MSGAT_MAX_GROUP], *c2_w[MSGAT_MAX_GROUP],
+      *sa_W[MSGAT_MAX_GROUP];
   const float *Mc, *Pt, *Z, *pw, *A2;
   const int32_t *row_ptr, *col_idx, *csc_ptr, *csc_row, *csc_eid;
   float *dx, *tcA, *delta, *dSnz, *bias_part, *ln_part;
@@ -94,7 +95,8 @@ TC_DEV void td_ld8_sum(uint32_t addr, float (&v)[8]) {
 __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
-  const int C = a.C, b = a.b, O = a.O, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, bi = blockIdx.y;
+  const int C = a.C, b = a.b, O = a.O, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
+  const int64_t svo = (int64_t)m * a.sv_sm, sco = (int64_t)m * a.sc_sm;
   const uint32_t cbO = (uint32_t)O * 128u, cbM = (uint32_t)b * 128u;
   unsigned char* GH = smem;
   unsigned char* GL = GH + 3 * cbO;
@@ -121,32 +123,23 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   for (int i = tid; i < O * 96; i += TD_THREADS) {
     const int k = i / 96, n = i - k * 96;
     const uint32_t off = sw128b32_off(k, n, cbO);
-    td_split1(WXH, WXL, off, n < C ? a.res_w[k * C + n] : 0.f);
+    td_split1(WXH, WXL, off, n < C ? a.res_w[m][k * C + n] : 0.f);
     float w = 0.f;
     if (n < C) {
-      if (k < b) w = a.c1_w[(k * C + n) * 2 + 1];
-      else if (k < 2 * b) w = a.c1_w[((k - b) * C + n) * 2 + 0];
-      else w = a.sa_W[(k - 2 * b) * C + n];
+      if (k < b) w = a.c1_w[m][(k * C + n) * 2 + 1];
+      else if (k < 2 * b) w = a.c1_w[m][((k - b) * C + n) * 2 + 0];
+      else w = a.sa_W[m][(k - 2 * b) * C + n];
     }
     td_split1(W3H, W3L, off, w);
-  }
-  for (int i = tid; i < b * 96; i += TD_THREADS) {
-    const int k = i / 96, n = i - k * 96;
-    td_split1(WMH, WML, sw128b32_off(k, n, cbM), n < C ? a.Mc[((int64_t)bi * b + k) * C + n] : 0.f);
   }
   for (int i = tid; i < b * 64; i += TD_THREADS) {
     const int k = i / 64, n = i - k * 64;   // k = output channel o of the second conv (contraction), n = its input channel (+ b: past tap)
     float w = 0.f;
-    if (n < b) w = a.c2_w[(k * b + n) * 2 + 1];
-    else if (n < 2 * b) w = a.c2_w[(k * b + (n - b)) * 2 + 0];
+    if (n < b) w = a.c2_w[m][(k * b + n) * 2 + 1];
+    else if (n < 2 * b) w = a.c2_w[m][(k * b + (n - b)) * 2 + 0];
     td_split1(W2H, W2L, sw128b32_off(k, n, cbM), w);
   }
-  for (int i = tid; i < 144; i += TD_THREADS) {
-    const int t = i / 12, j = i - t * 12;
-    Pt[i] = a.Pt[(int64_t)bi * 144 + i];
-    Ptd[i] = t >= a.d1 ? a.Pt[(int64_t)bi * 144 + (t - a.d1) * 12 + j] : 0.f;
-  }
-  if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  if (tid < 12) { LW[tid] = a.ln_w[m][tid]; LW[12 + tid] = a.ln_b[m][tid]; }
   if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
   tc_fence_before_sync();
@@ -163,11 +156,6 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   uint32_t phase = 0;
   const int l = tid & 127, quarter = warp >> 2;   // l = TMEM lane = position; the 4 warpgroups split the column groups
   const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-  const float* xb = a.x + bi * a.x_sb;
-  const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
-  const float* A2b = a.A2 + (int64_t)bi * 2 * b * a.N * 12;
-  float* tcAb = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
-  const int blk = bi * a.J + blockIdx.x;
 
   // GZ gather items on the top threads: 4 channels x 4 positions each
   const int gz_i = tid - (TD_THREADS - (b / 4) * TD_NT * 3);
@@ -175,12 +163,34 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   const int gz_ch = gz_i / (TD_NT * 3), gz_pq = gz_i - gz_ch * (TD_NT * 3), gz_nl = gz_pq / 3, gz_t0 = (gz_pq - gz_nl * 3) * 4, gz_o0 = gz_ch * 4;
   uint32_t* MSK = reinterpret_cast<uint32_t*>(DY);   // [C][8] x > 0 bits of a row, over the dY1 rows once dPt has read them
 
+  // A CTA serves one component (its weights are staged once) and walks the logical blocks (sample bi, slot j) lb = bi * J + j
+  // with lb = blockIdx.x, blockIdx.x + gridDim.x, ...: block (bi, j) owns the tiles j, j + J, ... of its sample and its own
+  // slice of the per-block partial sums, exactly as when every logical block was a CTA of its own launch.
+  for (int blk = blockIdx.x; blk < a.J * a.B; blk += gridDim.x) {
+  const int bi = blk / a.J, jslot = blk - bi * a.J;
+  // per-sample operands: Mc as a B operand, the temporal attention matrix and its d1-shifted copy (the MMAs of the previous
+  // block have completed: every tile ends with a wait on its second MMA group)
+  for (int i = tid; i < b * 96; i += TD_THREADS) {
+    const int k = i / 96, n = i - k * 96;
+    td_split1(WMH, WML, sw128b32_off(k, n, cbM), n < C ? a.Mc[svo + ((int64_t)bi * b + k) * C + n] : 0.f);
+  }
+  for (int i = tid; i < 144; i += TD_THREADS) {
+    const int t = i / 12, j = i - t * 12;
+    Pt[i] = a.Pt[svo + (int64_t)bi * 144 + i];
+    Ptd[i] = t >= a.d1 ? a.Pt[svo + (int64_t)bi * 144 + (t - a.d1) * 12 + j] : 0.f;
+  }
+  __syncthreads();
+  const float* xb = a.x + (int64_t)m * a.x_sm + bi * a.x_sb;
+  const float* Gb = a.G + (int64_t)m * a.g_sm + (int64_t)bi * O * a.N * 12;
+  const float* A2b = a.A2 + svo + (int64_t)bi * 2 * b * a.N * 12;
+  float* tcAb = a.tcA + sco + (int64_t)bi * 3 * b * a.N * 12;
+  float* dxb = a.dx + (int64_t)m * a.dx_sm;
   float bsG[2] = {0.f, 0.f}, bsY = 0.f, lnw_acc[12], lnb_acc[12];
   double pt_acc = 0.0;
 #pragma unroll
   for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
 
-  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J) {
+  for (int tile = jslot; tile < a.ntile; tile += a.J) {
     const int n0 = tile * TD_NT;
     // L2 prefetch of what this tile reads late and latency-bound: the saved first-conv taps (dPt, inside
     // the second MMA window) and the x rows of the LayerNorm backward.  One 128-byte line per thread.
@@ -430,7 +440,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       const int nl = l / 12, n = n0 + nl, t = l - nl * 12;
       const bool live = l < TD_P && n < a.N;
       const int64_t cs = (int64_t)a.N * 12;
-      float* ob = a.dx + (int64_t)bi * C * cs + (int64_t)n * 12 + t;
+      float* ob = dxb + (int64_t)bi * C * cs + (int64_t)n * 12 + t;
       int g = 0;
       for (int c0 = 0; c0 < C; c0 += 8, ++g) {
         if ((g & 3) != quarter) continue;
@@ -455,14 +465,14 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     float s = bsG[q];
     s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4);
     const int r = tid + q * TD_THREADS;
-    if (r < O * TD_NT && (r & 7) == 0) a.bias_part[(int64_t)blk * a.nbias + r / TD_NT] = s;
+    if (r < O * TD_NT && (r & 7) == 0) a.bias_part[sco + (int64_t)blk * a.nbias + r / TD_NT] = s;
   }
   {
     float s = bsY;   // rows k on the even threads tid = 2 (k * 8 + nl)
     s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4); s += __shfl_xor_sync(0xffffffffu, s, 8);
-    if (tid < 2 * b * TD_NT && (tid & 15) == 0) a.bias_part[(int64_t)blk * a.nbias + O + (tid >> 4)] = s;
+    if (tid < 2 * b * TD_NT && (tid & 15) == 0) a.bias_part[sco + (int64_t)blk * a.nbias + O + (tid >> 4)] = s;
   }
-  if (tid < 144) a.dPt_part[(int64_t)blk * 144 + tid] = pt_acc;
+  if (tid < 144) reinterpret_cast<double*>(reinterpret_cast<float*>(a.dPt_part) + sco)[(int64_t)blk * 144 + tid] = pt_acc;
 #pragma unroll
   for (int t = 0; t < 12; ++t) {
     const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
@@ -472,7 +482,9 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   if (tid < 24) {
     float s = 0.f;
     for (int w = 0; w < TD_THREADS / 32; ++w) s += RED[w * 24 + tid];
-    a.ln_part[(int64_t)blk * 24 + tid] = s;
+    a.ln_part[sco + (int64_t)blk * 24 + tid] = s;
+  }
+  __syncthreads();   // RED, the per-sample operands and the accumulators are reused by the next logical block
   }
   if (warp == 0) tmem_dealloc(tm, 512);
 }
@@ -489,17 +501,25 @@ int tc_dgrad_blocks_per_sample(const Plan& p) {
   return tc_ctas_per_sample(p.B, ntile, 2, "MSGAT_TD_WAVES");
 }
 
-int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
-                    const float* saved, float* tcA, float* dx, float* delta, float* dSnz, float* bias_part, int nbias,
-                    float* ln_part, double* dPt_part, void* stream) {
+int launch_tc_dgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G, int64_t g_sm,
+                    const float* saved, float* tcA, float* dx, int64_t dx_sm, float* bias_part, int nbias, float* ln_part,
+                    double* dPt_part, void* stream) {
   TcDgradArgs a;
-  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
-  a.C = p.C; a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TD_NT - 1) / TD_NT; a.J = tc_dgrad_blocks_per_sample(p);
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.g_sm = g_sm; a.sv_sm = p.saved_total; a.sc_sm = p.scratch_sm; a.dx_sm = dx_sm;
+  a.G = G;
+  a.C = p.C; a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TD_NT - 1) / TD_NT; a.J = tc_dgrad_blocks_per_sample(p); a.B = p.B;
   a.d1 = p.dil[0]; a.d2 = p.dil[1]; a.nnz = p.nnz; a.x_is_relu = (p.flags & MSGAT_F_X_IS_RELU) ? 1 : 0; a.nbias = nbias;
-  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.res_w = prm->res_w; a.c1_w = prm->conv_w[0]; a.c2_w = prm->conv_w[1]; a.sa_W = prm->sa_W;
+  for (int m = 0; m < MSGAT_MAX_GROUP; ++m) {
+    const msgat_meam_params* q = prm + (m < p.M ? m : 0);
+    a.ln_w[m] = q->ln_w; a.ln_b[m] = q->ln_b; a.res_w[m] = q->res_w; a.c1_w[m] = q->conv_w[0]; a.c2_w[m] = q->conv_w[1]; a.sa_W[m] = q->sa_W;
+  }
   a.Mc = saved + p.o_Mc; a.Pt = saved + p.o_Pt; a.Z = saved + p.o_Z; a.pw = saved + p.o_pw; a.A2 = saved + p.o_A2;
   a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
-  a.dx = dx; a.tcA = tcA; a.delta = delta; a.dSnz = dSnz; a.bias_part = bias_part; a.ln_part = ln_part; a.dPt_part = dPt_part;
-  MSGAT_LAUNCH(k_tc_dgrad, dim3(a.J, p.B), dim3(TD_THREADS), tc_dgrad_smem(p.O, p.Oc), stream, a);
+  a.dx = dx; a.tcA = tcA; a.delta = nullptr; a.dSnz = nullptr; a.bias_part = bias_part; a.ln_part = ln_part; a.dPt_part = dPt_part;
+  // one CTA per SM, every CTA on ONE component: sm_count / M CTAs per component walk its J * B logical blocks
+  int G1 = msgat_sm_count() / p.M;
+  if (G1 < 1) G1 = 1;
+  if (G1 > a.J * p.B) G1 = a.J * p.B;
+  MSGAT_LAUNCH(k_tc_dgrad, dim3(G1, p.M), dim3(TD_THREADS), tc_dgrad_smem(p.O, p.Oc), stream, a);
   return 0;
 }
