@@ -16,6 +16,7 @@
 #define MSGAT_LAUNCH(kern, grid, block, smem, stream, ...) \
   emu::launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
 #define MSGAT_UNROLL
+#define MSGAT_UNROLL_N(n)
 #define MSGAT_PIN(x)
 static inline void msgat_prof_tag(const char*, int, int) {}
 static inline int msgat_current_device() { return 0; }
@@ -49,6 +50,8 @@ int msgat_sm_count();         // multiprocessors of the current device (148 on a
     if (_slot >= 0) msgat_prof_end(_slot, (cudaStream_t)(stream));                                \
   } while (0)
 #define MSGAT_UNROLL _Pragma("unroll")
+#define MSGAT_STR_(x) #x
+#define MSGAT_UNROLL_N(n) _Pragma(MSGAT_STR_(unroll n))
 // keep a kernel-parameter value (e.g. dil[i], an indexed constant-bank load) in a register instead of
 // letting the compiler reload it inside the inner loops
 #define MSGAT_PIN(x) asm volatile("" : "+r"(x))

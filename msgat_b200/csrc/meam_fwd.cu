@@ -142,7 +142,11 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
     const float* pqf = a.pqc + m * a.sc_sm;
     for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
       double s = 0.0;
-      if (a.l2) for (int tl = 0; tl < a.ntile; ++tl) s += (double)pqf[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      if (a.l2) {
+        // independent loads, serial fp64 adds in tile order: eight loads in flight instead of one L2 round trip per tile
+        MSGAT_UNROLL_N(8)
+        for (int tl = 0; tl < a.ntile; ++tl) s += (double)pqf[((int64_t)b * a.ntile + tl) * C * 12 + i];
+      }
       else for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
       qc[i] = s;
       qc_o[(int64_t)b * C * 12 + i] = (float)s;
@@ -167,6 +171,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
     if (part < parts) {
       const float* W = (r < 10) ? a.prm[m].ta_Wt1 + (int64_t)r * a.N : a.prm[m].ta_Wt2 + (int64_t)(r - 10) * a.N;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+      MSGAT_UNROLL_N(4)
       for (int n = part; n < a.N; n += parts) {
         const double w = (double)__ldg(W + n);
         const float4 qv = ld4(qtb + (int64_t)n * 12 + t4);
