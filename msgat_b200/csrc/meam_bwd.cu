@@ -811,6 +811,15 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
     for (int r = tid; r < C * NT; r += T) {
       const int c = r / NT, nl = r - c * NT, n = n0 + nl;
       double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+#ifndef MSGAT_EMU
+      {   // the rows of the thread's NEXT item on their way into L1 while this one is computed
+        const int r2 = r + T, c2 = r2 / NT, n2 = n0 + r2 - c2 * NT;
+        if (r2 < C * NT && n2 < a.N) {
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(xm + b * a.x_sb + c2 * a.x_sc + (int64_t)n2 * 12));
+          if (!g_DH) asm volatile("prefetch.global.L1 [%0];" ::"l"(dxm + (((int64_t)b * C + c2) * a.N + n2) * 12));
+        }
+      }
+#endif
       if (n < a.N) {
         const float* src = xm + b * a.x_sb + c * a.x_sc + (int64_t)n * 12;
         float xv[12], xh[12], h[12], dh[12];
