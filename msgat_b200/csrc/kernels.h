@@ -58,7 +58,8 @@ int launch_tc_apply3(const Plan& p, const msgat_meam_params* prm, const msgat_ad
                      float* saved, void* stream);
 bool tc_wgrad_supported(const Plan& p);
 int tc_wgrad_blocks_per_sample(const Plan& p);
-int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
+// grouped: all p.M components in one launch (inputs x_sm / g_sm apart, saved / scratch slices)
+int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G, int64_t g_sm,
                     const float* saved, const float* tcA, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream);
 bool tc_dgrad_supported(const Plan& p);

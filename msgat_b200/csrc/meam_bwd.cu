@@ -1270,14 +1270,14 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
       }
 #undef BWD_CASE
     }
-#ifndef MSGAT_EMU
-    if (tc_w) {
-      float* wg = scr + L.o_wg;
-      launch_tc_wgrad(p, prmm, adj, xm, G, savedm, scr + L.o_tcA, wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0],
-                      wg + L.off_job[JOB_CONV + 1], wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT,
-                      scr + L.o_dMc, (int64_t)p.Oc * p.C, stream);
-    }
-#endif
   }
+#ifndef MSGAT_EMU
+  if (tc_w) {   // every weight gradient of all components in one persistent launch (tc_wgrad.cu); dA / GZ come from the passes above
+    float* wg = scratch + L.o_wg;
+    launch_tc_wgrad(p, prm, adj, x, need_mask ? scratch + L.o_G : dout, need_mask ? sc_sm : out_sm, saved, scratch + L.o_tcA,
+                    wg + L.off_job[JOB_RES], wg + L.off_job[JOB_WS], wg + L.off_job[JOB_CONV + 0], wg + L.off_job[JOB_CONV + 1],
+                    wg + L.off_job[JOB_CONV + 2], wg + L.off_job[JOB_CONV + 3], L.WGT, scratch + L.o_dMc, (int64_t)p.Oc * p.C, stream);
+  }
+#endif
   return meam_backward_tail(p, L, Jw, prm, adj, x, saved, scratch, dx, g, stream);
 }

@@ -35,11 +35,12 @@
 #define TCW_STAGES 2         // operand tiles are double-buffered: staging tile i+1 overlaps the MMAs of tile i
 #define TCW_SLACK (16 * TCW_GS)  // an M=128 operand descriptor reads 16 row groups from its base
 
-struct TcWgradArgs {
-  const float* x; int64_t x_sb, x_sc;
+struct TcWgradArgs {   // grouped: blockIdx.y = component; inputs x_sm / g_sm apart, saved slices sv_sm, scratch slices sc_sm apart
+  const float* x; int64_t x_sb, x_sc, x_sm, g_sm, sv_sm, sc_sm;
   const float* G;   // masked dout [B,O,N,12]
-  int C, Cp, N, O, b, ntile, J, d2, has_ln;
-  const float *ln_w, *ln_b, *Y1, *tcA;
+  int C, Cp, N, O, b, ntile, J, B, d2, has_ln;
+  const float *ln_w[MSGAT_MAX_GROUP], *ln_b[MSGAT_MAX_GROUP];
+  const float *Y1, *tcA;
   float *p_res, *p_ws, *p_c1past, *p_c1now, *p_c2past, *p_c2now;  // partial bases (block 0), row-major
   int64_t wg_stride;                                             // floats between consecutive blocks
   float* p_mc; int64_t mc_stride;
@@ -74,7 +75,8 @@ TC_DEV void st_split(unsigned char* hi, unsigned char* lo, uint32_t off, float4 
 __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
-  const int C = a.C, Cp = a.Cp, O = a.O, b = a.b, tid = threadIdx.x, warp = tid >> 5, bi = blockIdx.y;
+  const int C = a.C, Cp = a.Cp, O = a.O, b = a.b, tid = threadIdx.x, warp = tid >> 5, m = blockIdx.y;
+  const int64_t svo = (int64_t)m * a.sv_sm, sco = (int64_t)m * a.sc_sm;
   const int Op = (O + 7) & ~7;
   const uint32_t GS = TCW_GS;
   const uint32_t szG = (uint32_t)(Op / 8) * GS, szX = (uint32_t)(2 * Cp / 8) * GS, szA = (uint32_t)(3 * b / 8) * GS,
@@ -90,7 +92,7 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
   // zero all operand tiles once: pad rows (C..Cp) and the slack must be finite
   for (int i = tid; i < (int)((TCW_STAGES * 2 * part + TCW_SLACK) / 16); i += TCW_ALL)
     reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (tid < 12) { LW[tid] = a.has_ln ? a.ln_w[tid] : 1.f; LW[12 + tid] = a.has_ln ? a.ln_b[tid] : 0.f; }
+  if (tid < 12) { LW[tid] = a.has_ln ? a.ln_w[m][tid] : 1.f; LW[12 + tid] = a.has_ln ? a.ln_b[m][tid] : 0.f; }
   if (tid == 0) {
     mbar_init(smem_u32(&bars[0]), 1); mbar_init(smem_u32(&bars[1]), 1);
     mbar_init(smem_u32(&full[0]), TCW_THREADS / 32); mbar_init(smem_u32(&full[1]), TCW_THREADS / 32);
@@ -104,11 +106,10 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
   const int N1 = (2 * Cp + 15) & ~15, N2 = (Cp + 15) & ~15, N3 = 2 * b;
   const uint32_t D1 = tm, D2 = tm + 160, D3 = tm + 256;
   const uint32_t id1 = umma_idesc_tf32(128, N1, 0, 0), id2 = umma_idesc_tf32(128, N2, 0, 0), id3 = umma_idesc_tf32(128, N3, 0, 0);
-  const float* xb = a.x + bi * a.x_sb;
-  const float* Gb = a.G + (int64_t)bi * O * a.N * 12;
-  const float* Yb = a.Y1 + (int64_t)bi * b * a.N * 12;
-  const float* Ab = a.tcA + (int64_t)bi * 3 * b * a.N * 12;
-  const int ntl = (a.ntile - (int)blockIdx.x + a.J - 1) / a.J;   // tiles of this CTA (>= 1)
+  // A CTA serves one component and walks the logical blocks (sample bi, slot j), lb = bi * J + j = blockIdx.x, + gridDim.x, ...:
+  // block (bi, j) owns the tiles j, j + J, ... of its sample, accumulates them in TMEM and flushes its own slice of partials,
+  // exactly as when every logical block was a CTA.  The stage / barrier sequence (itg) runs on across the blocks.
+  const int nlb = a.J * a.B;
 
   if (warp == TCW_THREADS / 32) {
     // ---- MMA warp: one thread waits for a staged tile, issues its 27 MMAs and commits them to the
@@ -123,9 +124,12 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
       const uint64_t hh0 = umma_desc(s0 + szG + offH, 128u, GS, 0), hl0 = umma_desc(s0 + part + szG + offH, 128u, GS, 0);
       const uint64_t th0 = umma_desc(s0 + offT, 128u, GS, 0), tl0 = umma_desc(s0 + part + offT, 128u, GS, 0);
       const uint64_t yh0 = umma_desc(s0 + szG + szX + szA, 128u, GS, 0), yl0 = umma_desc(s0 + part + szG + szX + szA, 128u, GS, 0);
-      for (int it = 0; it < ntl; ++it) {
-        const int st = it & 1;
-        mbar_wait(smem_u32(&full[st]), (uint32_t)((it >> 1) & 1));
+      int itg = 0;
+      for (int lb = blockIdx.x; lb < nlb; lb += gridDim.x) {
+      const int ntl = (a.ntile - (lb % a.J) + a.J - 1) / a.J;
+      for (int it = 0; it < ntl; ++it, ++itg) {
+        const int st = itg & 1;
+        mbar_wait(smem_u32(&full[st]), (uint32_t)((itg >> 1) & 1));
         tc_fence_after_sync();
         for (int k8 = 0; k8 < TCW_P / 8; ++k8) {
           const uint64_t d = (uint64_t)(((uint32_t)st * 2u * part + (uint32_t)k8 * 256u) >> 4);   // start-address field, 16-byte units
@@ -136,9 +140,19 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
         }
         umma_commit(smem_u32(&bars[st]));
       }
+      }
     }
-  } else {
-  int it = 0;
+  }
+  int it = 0;   // tiles staged so far by this CTA (all logical blocks)
+  if (warp < TCW_THREADS / 32)
+  for (int lb = blockIdx.x; lb < nlb; lb += gridDim.x) {
+  const int bi = lb / a.J, jslot = lb - bi * a.J;
+  const int ntl = (a.ntile - jslot + a.J - 1) / a.J;   // tiles of this logical block (>= 1)
+  const float* xb = a.x + (int64_t)m * a.x_sm + bi * a.x_sb;
+  const float* Gb = a.G + (int64_t)m * a.g_sm + (int64_t)bi * O * a.N * 12;
+  const float* Yb = a.Y1 + svo + (int64_t)bi * b * a.N * 12;
+  const float* Ab = a.tcA + sco + (int64_t)bi * 3 * b * a.N * 12;
+  {
 
   // Work assignment, fixed for the whole kernel, every item one float4 (4 positions of one row):
   //  * G and dA rows: flat items on warps 8..15 (row-within-group in the low 3 bits, so 8
@@ -180,8 +194,8 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
       }
     }
   }
-  const float4 lw4 = a.has_ln && ql < 3 ? ld4(a.ln_w + 4 * ql) : make_float4(1.f, 1.f, 1.f, 1.f);
-  const float4 lb4 = a.has_ln && ql < 3 ? ld4(a.ln_b + 4 * ql) : f4zero();
+  const float4 lw4 = a.has_ln && ql < 3 ? ld4(a.ln_w[m] + 4 * ql) : make_float4(1.f, 1.f, 1.f, 1.f);
+  const float4 lb4 = a.has_ln && ql < 3 ? ld4(a.ln_b[m] + 4 * ql) : f4zero();
   const int qd = a.d2 >> 2, rd = a.d2 & 3;   // causal shift = qd whole quads + rd positions
   // The global loads of tile i+1 are issued before tile i is staged (register prefetch): their
   // latency hides behind the staging arithmetic and the wait for the stage to drain.
@@ -198,8 +212,8 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
       if (w_kind[k] && in && n0 + w_nl[k] < a.N) pw[k] = ld4((w_kind[k] == 1 ? xb : Yb) + w_go[k] + (int64_t)n0 * 12);
     }
   };
-  prefetch(blockIdx.x);
-  for (int tile = blockIdx.x; tile < a.ntile; tile += a.J, ++it) {
+  prefetch(jslot);
+  for (int tile = jslot; tile < a.ntile; tile += a.J, ++it) {
     const int n0 = tile * TCW_NT, st = it & 1;
     unsigned char* SB = smem + (size_t)st * 2 * part;   // stage base: G | X,H | dA,GZ | Y1,shift
     unsigned char* TG = SB;
@@ -254,17 +268,17 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
     if (lane == 0) mbar_arrive(smem_u32(&full[st]));
   }
   }
-  // the last commit covers every MMA issued before it
-  mbar_wait(smem_u32(&bars[(ntl - 1) & 1]), (uint32_t)(((ntl - 1) >> 1) & 1));
+  // the last commit of the block covers every MMA issued before it
+  mbar_wait(smem_u32(&bars[(it - 1) & 1]), (uint32_t)(((it - 1) >> 1) & 1));
   tc_fence_after_sync();
   // ---- flush: TMEM lane = output row, columns = input channel
-  if (warp < TCW_THREADS / 32) {
-    const int blk = bi * a.J + blockIdx.x;
+  {
+    const int blk = lb;
     const int row = (warp & 3) * 32 + (tid & 31);
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const int quarter = warp >> 2;  // the four warpgroups split the column groups
-    float* wres = a.p_res + (int64_t)blk * a.wg_stride;
-    float* wmc = a.p_mc + (int64_t)blk * a.mc_stride;
+    float* wres = a.p_res + sco + (int64_t)blk * a.wg_stride;
+    float* wmc = a.p_mc + sco + (int64_t)blk * a.mc_stride;
     int cg = 0;
     for (int c0 = 0; c0 < N1; c0 += 8, ++cg) {
       float v[8];
@@ -277,9 +291,9 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
         if (c >= Cp && c < Cp + C && row < b) wmc[row * C + c - Cp] = v[j];
       }
     }
-    float* w1n = a.p_c1now + (int64_t)blk * a.wg_stride;
-    float* w1p = a.p_c1past + (int64_t)blk * a.wg_stride;
-    float* wws = a.p_ws + (int64_t)blk * a.wg_stride;
+    float* w1n = a.p_c1now + sco + (int64_t)blk * a.wg_stride;
+    float* w1p = a.p_c1past + sco + (int64_t)blk * a.wg_stride;
+    float* wws = a.p_ws + sco + (int64_t)blk * a.wg_stride;
     cg = 0;
     for (int c0 = 0; c0 < N2; c0 += 8, ++cg) {
       float v[8];
@@ -294,8 +308,8 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
         else if (row < 3 * b) wws[(row - 2 * b) * C + c] = v[j];
       }
     }
-    float* w2n = a.p_c2now + (int64_t)blk * a.wg_stride;
-    float* w2p = a.p_c2past + (int64_t)blk * a.wg_stride;
+    float* w2n = a.p_c2now + sco + (int64_t)blk * a.wg_stride;
+    float* w2p = a.p_c2past + sco + (int64_t)blk * a.wg_stride;
     cg = 0;
     for (int c0 = 0; c0 < N3; c0 += 8, ++cg) {
       float v[8];
@@ -309,6 +323,9 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
         else w2p[row * b + c - b] = v[j];
       }
     }
+  }
+  tc_fence_before_sync();   // the flush's TMEM reads are ordered before this warp's next arrival on a `full` barrier, after
+                            // which the MMA thread overwrites the accumulators with the next block's first product
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -330,17 +347,22 @@ int tc_wgrad_blocks_per_sample(const Plan& p) {
   return tc_ctas_per_sample(p.B, ntile, 2, "MSGAT_TW_WAVES");
 }
 
-int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G,
+int launch_tc_wgrad(const Plan& p, const msgat_meam_params* prm, const msgat_adj* adj, const float* x, const float* G, int64_t g_sm,
                     const float* saved, const float* tcA, float* p_res, float* p_ws, float* p_c1past, float* p_c1now, float* p_c2past,
                     float* p_c2now, int64_t wg_stride, float* p_mc, int64_t mc_stride, void* stream) {
   TcWgradArgs a;
-  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.G = G;
+  a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.g_sm = g_sm; a.sv_sm = p.saved_total; a.sc_sm = p.scratch_sm; a.G = G;
   a.C = p.C; a.Cp = rup8(p.C); a.N = p.N; a.O = p.O; a.b = p.Oc; a.ntile = (p.N + TCW_NT - 1) / TCW_NT;
-  a.J = tc_wgrad_blocks_per_sample(p);
+  a.J = tc_wgrad_blocks_per_sample(p); a.B = p.B;
   a.d2 = p.dil[1]; a.has_ln = (p.flags & MSGAT_F_LN) ? 1 : 0;
-  a.ln_w = prm->ln_w; a.ln_b = prm->ln_b; a.Y1 = saved + p.o_Y1; a.tcA = tcA;
+  for (int m = 0; m < MSGAT_MAX_GROUP; ++m) { a.ln_w[m] = prm[m < p.M ? m : 0].ln_w; a.ln_b[m] = prm[m < p.M ? m : 0].ln_b; }
+  a.Y1 = saved + p.o_Y1; a.tcA = tcA;
   a.p_res = p_res; a.p_ws = p_ws; a.p_c1past = p_c1past; a.p_c1now = p_c1now; a.p_c2past = p_c2past; a.p_c2now = p_c2now;
   a.wg_stride = wg_stride; a.p_mc = p_mc; a.mc_stride = mc_stride;
-  MSGAT_LAUNCH(k_tc_wgrad, dim3(a.J, p.B), dim3(TCW_ALL), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
+  // one CTA per SM, every CTA on ONE component: sm_count / M CTAs per component walk its J * B logical blocks
+  int G1 = msgat_sm_count() / p.M;
+  if (G1 < 1) G1 = 1;
+  if (G1 > a.J * p.B) G1 = a.J * p.B;
+  MSGAT_LAUNCH(k_tc_wgrad, dim3(G1, p.M), dim3(TCW_ALL), tc_wgrad_smem(p.C, p.O, p.Oc), stream, a);
   return 0;
 }

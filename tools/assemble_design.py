@@ -64,6 +64,24 @@ def main():
     gpu_tests = open(os.path.join(P, "r02_final_pytest_gpu.log")).read().strip().splitlines()[-1] if os.path.exists(os.path.join(P, "r02_final_pytest_gpu.log")) else "see profiles"
     text = text.replace("GPU_TESTS", "`" + gpu_tests.strip() + "`").replace("CPU_TESTS", "89")
     open(os.path.join(ROOT, "DESIGN.md"), "w").write(text)
+    # README: the headline numbers between its <!-- numbers --> markers
+    rp = os.path.join(ROOT, "README.md")
+    r = open(rp).read()
+    if main_run and "<!-- numbers -->" in r:
+        g8, tf = line("r02_final_bench_8gpu.json"), line("r02_final_bench_tf32.json")
+        msg = (f"{main_run['value']:.0f} samples/s on one GPU ({main_run['ms_per_step']:.2f} ms/step; round 1: 2814 / 11.37), "
+               f"{main_run['e2e']['value']:.0f} samples/s end to end with the batch copied from pinned host memory every step")
+        if tf:
+            msg += f", {tf['value']:.0f} samples/s in TF32 mode"
+        if g8:
+            msg += f"; {g8['value']:.0f} samples/s on eight GPUs (weak scaling, {g8['ms_per_step']:.2f} ms/step)"
+            if g8.get("strong"):
+                msg += f", {g8['strong']['value']:.0f} samples/s with the GLOBAL batch of 32 sharded over them ({g8['strong']['ms_per_step']:.2f} ms/step)"
+        if ref:
+            msg += f". The unmodified reference modules on the box's {ref['cpu_baseline']['cores']} host cores: {ref['value']:.1f} samples/s."
+        a, b = r.index("<!-- numbers -->"), r.index("<!-- /numbers -->")
+        r = r[:a] + "<!-- numbers -->\n" + msg + "\n" + r[b:]
+        open(rp, "w").write(r)
     print("DESIGN.md written,", len(text), "bytes")
 
 
