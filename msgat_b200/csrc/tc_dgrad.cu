@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tm = tmem_slot;
+  const uint32_t tm = warp_uniform(tmem_slot);   // uniform register: no per-MMA R2UR loop in the issue thread (tc_common.cuh)
   const uint32_t Dx = tm, Dh = tm + 96, Dy = tm + 192;
   const uint64_t dGH = umma_desc(smem_u32(GH), cbO, 512u, 1), dGL = umma_desc(smem_u32(GL), cbO, 512u, 1);
   const uint64_t dWXH = umma_desc(smem_u32(WXH), cbO, 512u, 1), dWXL = umma_desc(smem_u32(WXL), cbO, 512u, 1);

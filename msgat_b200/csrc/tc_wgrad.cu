@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(TCW_ALL, 1) k_tc_wgrad(TcWgradArgs a) {
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tm = tmem_slot;
+  const uint32_t tm = warp_uniform(tmem_slot);   // uniform register: no per-MMA R2UR loop in the issue thread (tc_common.cuh)
   const int N1 = (2 * Cp + 15) & ~15, N2 = (Cp + 15) & ~15, N3 = 2 * b;
   const uint32_t D1 = tm, D2 = tm + 160, D3 = tm + 256;
   const uint32_t id1 = umma_idesc_tf32(128, N1, 0, 0), id2 = umma_idesc_tf32(128, N2, 0, 0), id3 = umma_idesc_tf32(128, N3, 0, 0);
