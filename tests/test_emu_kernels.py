@@ -72,3 +72,33 @@ def test_emulated_tensor_core_score_passes(N):
     errs.update({k: rel(v.grad, p[k].grad) for k, v in mod.named_parameters()})
     assert all(e < 2e-3 for e in errs.values()), errs
     assert errs["out"] > 2e-6, "the TF32 path was not taken"   # fp32 path: ~1e-7
+
+
+def test_adjacency_view_follows_the_tensor_not_its_address():
+    """ADVICE (round 1): a model that is freed and rebuilt with ANOTHER adjacency of the same size, and an adjacency edited
+    in place, must not be served the old graph's CSR / CSC (ops.sparse_adjacency caches per tensor object + version)."""
+    import gc
+    import torch
+    from msgat_b200 import models, synthetic
+    from oracle import msgat_oracle as O
+    torch.manual_seed(3)
+    N = 31
+    mod = models.GACN(3, 8, 12)
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, 3, N, 12, generator=g)
+    p = {k: v.detach().double() for k, v in mod.state_dict().items()}
+
+    def check(adj):
+        out = mod(x, adj)
+        ref = O.gacn(x.double(), adj.double(), p, "")
+        assert float((out.double() - ref).norm() / ref.norm()) < 1e-5
+
+    adj1 = synthetic.geometric_graph(N, mean_degree=4.0, seed=1)
+    check(adj1)
+    del adj1
+    gc.collect()
+    adj2 = synthetic.geometric_graph(N, mean_degree=4.0, seed=2)   # may land on the freed tensor's storage
+    check(adj2)
+    with torch.no_grad():                                          # in-place edit: same object, new version
+        adj2[0, N - 1] = adj2[N - 1, 0] = 0.37
+    check(adj2)
