@@ -10,7 +10,7 @@
 #define HPS (HNT * 12 + 4)
 
 struct HeadArgs {
-  const float* x; int C, N, Tout, ntile, J, accumulate, x_is_relu;
+  const float* x; int C, N, Tout, ntile, J, accumulate, x_is_relu, Bn;   // Bn: samples (the streaming kernels walk (sample, node tile) blocks)
   const float *ln_w, *ln_b, *fc_w, *fc_b, *gate; int64_t gate_sb;
   float *head_out, *out;
   // backward
@@ -267,26 +267,31 @@ MSGAT_DEV void row_normalise(const Row12& x, float (&xh)[12], float& rs_out) {
 MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a0, HeadGrp grp) {
   const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
-  const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int C = a.C, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
   float* RED = Wh + C * HS_WP;                       // [HS_WARPS][HS_NODES][12] (after the channel loop)
   float* LW = RED + 2 * HS_WARPS * HS_NODES * 12;   // [24]
   float* XS = RED;                                  // [HS_WARPS][2 stages][HS_NODES][12] rows in flight (RED reuses it after the loop)
-  const int n0 = blockIdx.x * HS_NODES, nA = n0 + lane, nB = nA + 32;
-  const bool liveA = nA < a.N, liveB = nB < a.N;
-  const float* xb = a.x + (int64_t)b * C * a.N * 12;
   float* ring = XS + warp * 2 * HS_NODES * 12;
-  // two channels ahead of the one being consumed: issued before the weights are staged
-  if (warp < C) rows_fetch(ring, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
-  cp_async_commit();
-  if (warp + HS_WARPS < C) rows_fetch(ring + HS_NODES * 12, xb + (int64_t)(warp + HS_WARPS) * a.N * 12, nA, liveA, liveB, lane);
-  cp_async_commit();
+  // The 41 KB of fc weights are staged ONCE per block; the block then walks the logical blocks (sample b, node tile)
+  // lb = blockIdx.x, + gridDim.x, ... of its component (staging them per 64-node tile was 11 % of the kernel's samples).
   stage_fc12(Wh, a.fc_w, C);
   if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
   __syncthreads();
   float lw[12], lb[12];
   MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) { lw[t] = LW[t]; lb[t] = LW[12 + t]; }
+  const int ntn = (a.N + HS_NODES - 1) / HS_NODES;
+  for (int lbk = blockIdx.x; lbk < ntn * a.Bn; lbk += gridDim.x) {
+  const int b = lbk / ntn;
+  const int n0 = (lbk - b * ntn) * HS_NODES, nA = n0 + lane, nB = nA + 32;
+  const bool liveA = nA < a.N, liveB = nB < a.N;
+  const float* xb = a.x + (int64_t)b * C * a.N * 12;
+  // two channels ahead of the one being consumed
+  if (warp < C) rows_fetch(ring, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
+  if (warp + HS_WARPS < C) rows_fetch(ring + HS_NODES * 12, xb + (int64_t)(warp + HS_WARPS) * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
   float accA[12], accB[12];
   MSGAT_UNROLL
   for (int o = 0; o < 12; ++o) { accA[o] = 0.f; accB[o] = 0.f; }
@@ -339,6 +344,8 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a0, HeadGrp grp) {
     const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
     if (a.out) a.out[g] = a.accumulate ? a.out[g] + s * gt : s * gt;
   }
+  __syncthreads();   // RED is the next logical block's ring
+  }
 }
 
 // LayerNorm([12]) backward of one row: dh -> dx (masked by x > 0 when x is a ReLU output), affine gradient
@@ -378,7 +385,7 @@ MSGAT_DEV void head_ln_bwd_row(const float (&dh)[12], const Row12& xr, const flo
 MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   const HeadArgs a = head_component(a0, grp);
   MSGAT_DYN_SMEM(smem_raw);
-  const int C = a.C, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int C = a.C, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float* Wh = reinterpret_cast<float*>(smem_raw);   // [C][12 o][12 t]
   float* HB = Wh + C * HS_WP;                        // [HS_WARPS][HS_NODES][12]  normalised rows of the warp's channel
   float* DY = HB + HS_WARPS * HS_NODES * 12;        // [HS_NODES][12]   dy = dout * gate
@@ -387,15 +394,20 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   float* BS = LW + 24;                              // [12] column sums of DY (fc bias gradient of the block)
   float* RED = BS + 12;                             // [HS_WARPS][24]
   float* XS = RED + HS_WARPS * 24;                  // [HS_WARPS][HS_NODES][12]  next channel's rows in flight
-  const int n0 = blockIdx.x * HS_NODES, nA = n0 + lane, nB = nA + 32;
-  const bool liveA = nA < a.N, liveB = nB < a.N;
-  const float* xb = a.x + (int64_t)b * C * a.N * 12;
-  // the first channel's rows are in flight while the block stages the weights and dy
   float* stage = XS + warp * HS_NODES * 12;
-  if (warp < C) rows_fetch(stage, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
-  cp_async_commit();
+  // fc weights staged once per block; the block walks the logical blocks (sample b, node tile) of its component, each with its
+  // own slice of partial sums (same layout as when every logical block was a CTA)
   stage_fc12(Wh, a.fc_w, C);
   if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  const int ntn = (a.N + HS_NODES - 1) / HS_NODES;
+  for (int lbk = blockIdx.x; lbk < ntn * a.Bn; lbk += gridDim.x) {
+  const int b = lbk / ntn;
+  const int n0 = (lbk - b * ntn) * HS_NODES, nA = n0 + lane, nB = nA + 32;
+  const bool liveA = nA < a.N, liveB = nB < a.N;
+  const float* xb = a.x + (int64_t)b * C * a.N * 12;
+  // the first channel's rows are in flight while the block stages dy
+  if (warp < C) rows_fetch(stage, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
+  cp_async_commit();
   for (int it = tid; it < HS_NODES * 12; it += 256) {
     const int nl = it / 12, o = it - nl * 12, n = n0 + nl;
     float dy = 0.f;
@@ -416,7 +428,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
     BS[tid] = s;
   }
   __syncthreads();
-  float* part = a.part + (int64_t)(b * gridDim.x + blockIdx.x) * a.pstride;
+  float* part = a.part + (int64_t)lbk * a.pstride;
   float* hb = HB + warp * HS_NODES * 12;
   float lnw_acc[12], lnb_acc[12];
   MSGAT_UNROLL
@@ -500,8 +512,17 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
     for (int w = 0; w < HS_WARPS; ++w) s += RED[w * 24 + tid];
     part[144 * C + 12 + tid] = s;
   }
+  __syncthreads();   // DY, BS, RED and the row buffers are the next logical block's
+  }
 }
 
+// blocks of a streaming launch per component: two per SM over all components, at most one per (sample, node tile)
+static int head_stream_grid(int N, int B, int M) {
+  const int lb = ((N + HS_NODES - 1) / HS_NODES) * B;
+  int g = (2 * msgat_sm_count()) / (M < 1 ? 1 : M);
+  if (g < 1) g = 1;
+  return g > lb ? lb : g;
+}
 static bool head_streaming(const msgat_head_desc* d) {
   return d->Tout == 12 && ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4 <= 110 * 1024;
 }
@@ -545,7 +566,8 @@ int msgat_head_forward(const msgat_head_desc* d, const float* x, const float* ln
   a.gate_sb = d->gate_sb; a.head_out = head_out; a.out = out;
   if (head_streaming(d)) {
     size_t smem = ((size_t)d->C * HS_WP + 2 * HS_WARPS * HS_NODES * 12 + 24) * 4;
-    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B), dim3(256), smem, stream, a, HeadGrp{});
+    a.Bn = d->B;
+    MSGAT_LAUNCH(k_head_fwd12, dim3(head_stream_grid(d->N, d->B, 1)), dim3(256), smem, stream, a, HeadGrp{});
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
     MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B), dim3(256), smem, stream, a, HeadGrp{});
@@ -577,7 +599,8 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   if (head_streaming(d)) {
     nblk = (d->N + HS_NODES - 1) / HS_NODES;
     size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
-    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B), dim3(256), smem, stream, a, HeadGrp{});
+    a.Bn = d->B;
+    MSGAT_LAUNCH(k_head_bwd12, dim3(head_stream_grid(d->N, d->B, 1)), dim3(256), smem, stream, a, HeadGrp{});
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
     MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B), dim3(256), smem, stream, a, HeadGrp{});
@@ -620,7 +643,8 @@ int msgat_heads_forward(const msgat_heads_desc* d, const float* x, const float* 
   for (int m = 0; m < d->M; ++m) { g.ln_w[m] = ln_w[m]; g.ln_b[m] = ln_b[m]; g.fc_w[m] = fc_w[m]; g.fc_b[m] = fc_b[m]; }
   if (head_streaming(&d1)) {
     size_t smem = ((size_t)d->C * HS_WP + 2 * HS_WARPS * HS_NODES * 12 + 24) * 4;
-    MSGAT_LAUNCH(k_head_fwd12, dim3((d->N + HS_NODES - 1) / HS_NODES, d->B, d->M), dim3(256), smem, stream, a, g);
+    a.Bn = d->B;
+    MSGAT_LAUNCH(k_head_fwd12, dim3(head_stream_grid(d->N, d->B, d->M), 1, d->M), dim3(256), smem, stream, a, g);
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24) * 4;
     MSGAT_LAUNCH(k_head_fwd, dim3(a.J, d->B, d->M), dim3(256), smem, stream, a, g);
@@ -663,7 +687,8 @@ int msgat_heads_backward(const msgat_heads_desc* d, const float* x, const float*
   if (head_streaming(&d1)) {
     nblk = (d->N + HS_NODES - 1) / HS_NODES;
     size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
-    MSGAT_LAUNCH(k_head_bwd12, dim3(nblk, d->B, d->M), dim3(256), smem, stream, a, g);
+    a.Bn = d->B;
+    MSGAT_LAUNCH(k_head_bwd12, dim3(head_stream_grid(d->N, d->B, d->M), 1, d->M), dim3(256), smem, stream, a, g);
   } else {
     size_t smem = ((size_t)d->C * HPS + (size_t)d->C * d->Tout * 12 + 24 + (size_t)d->C * HNT * 2 + HNT * d->Tout + 8 * 24) * 4;
     MSGAT_LAUNCH(k_head_bwd, dim3(a.J, d->B, d->M), dim3(256), smem, stream, a, g);
