@@ -60,7 +60,7 @@ def main():
         text += open(f).read()
     text = text.replace("KERNEL_TABLE_PLACEHOLDER", ktable).replace("RESULTS_PLACEHOLDER", "\n".join(res))
     if main_run:
-        text = text.replace("STEP_MS", f"{main_run['ms_per_step']:.2f}")
+        text = text.replace("STEP_FRAC", f"{0.75 / main_run['ms_per_step'] * 100:.0f}").replace("STEP_MS", f"{main_run['ms_per_step']:.2f}")
     gpu_tests = open(os.path.join(P, "r02_final_pytest_gpu.log")).read().strip().splitlines()[-1] if os.path.exists(os.path.join(P, "r02_final_pytest_gpu.log")) else "see profiles"
     text = text.replace("GPU_TESTS", "`" + gpu_tests.strip() + "`").replace("CPU_TESTS", "89")
     open(os.path.join(ROOT, "DESIGN.md"), "w").write(text)
