@@ -84,6 +84,8 @@ def test_adjacency_view_follows_the_tensor_not_its_address():
     torch.manual_seed(3)
     N = 31
     mod = models.GACN(3, 8, 12)
+    for q in mod.parameters():   # the bare layers leave their parameters uninitialised, as the reference's do (msgat.py:206 is MSGAT's)
+        torch.nn.init.normal_(q, std=0.5) if q.dim() < 2 else torch.nn.init.xavier_normal_(q)
     g = torch.Generator().manual_seed(4)
     x = torch.randn(2, 3, N, 12, generator=g)
     p = {k: v.detach().double() for k, v in mod.state_dict().items()}
