@@ -59,11 +59,9 @@ size_t tc_wgrad_smem(int C, int O, int b) {
   return s + 1024;
 }
 
-TC_DEV float tf32_rna(float x) {
-  uint32_t u;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-  return __uint_as_float(u);
-}
+// round to TF32, nearest with ties away from zero: the add-and-mask cvt.rna.tf32.f32 is lowered to, without its Inf / NaN guard
+// (two integer instructions instead of four; bit-identical for finite values)
+TC_DEV float tf32_rna(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
 // v -> hi tile and lo tile at the same offset
 TC_DEV void st_split(unsigned char* hi, unsigned char* lo, uint32_t off, float4 v) {
   float4 h = make_float4(tf32_rna(v.x), tf32_rna(v.y), tf32_rna(v.z), tf32_rna(v.w));
