@@ -487,14 +487,17 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
       gv[i] = (gv[i] + v1) + v2;
     }
     if (lane < 9) {
+      // 16 stores C floats apart: the offsets are rebuilt from an opaque base every channel (as loop invariants the compiler kept
+      // 16 64-bit addresses alive across the channel loop and spilled them: 19 % of the kernel's samples sat on their reloads)
+      int off = (oq * 48 + tq * 4) * C + c;
+      MSGAT_PIN(off);
       MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) {
-        const int o = oq * 4 + i;
-        const float bs = BS[o];
+        const float bs = BS[oq * 4 + i];
         MSGAT_UNROLL
         for (int j = 0; j < 4; ++j) {
           const int t = tq * 4 + j;
-          part[((int64_t)o * 12 + t) * C + c] = fmaf(LW[t], gv[i * 4 + j], LW[12 + t] * bs);
+          part[off + (i * 12 + j) * C] = fmaf(LW[t], gv[i * 4 + j], LW[12 + t] * bs);
         }
       }
     }
