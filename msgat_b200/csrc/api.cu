@@ -62,6 +62,42 @@ void msgat_prof_end(int slot, cudaStream_t s) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   cudaEventRecord(g_recs[slot].e1, s);
 }
+
+// ---- a side stream per device: independent small kernels of one operator run next to its big ones (fork / join with events, so
+// the pattern is legal under CUDA graph capture: the side stream joins the capture at the fork and leaves it at the join).  All
+// side work is joined back into the caller's stream before the operator returns: callers see one stream, as the C ABI says.
+struct SideCtx { cudaStream_t s; cudaEvent_t fork, join; bool ok; };
+static SideCtx g_side[64];
+static std::mutex g_side_mu;
+static SideCtx* side_ctx() {
+  static const bool off = getenv("MSGAT_NO_FORK") != nullptr;   // measurement switch: everything on the caller's stream
+  if (off) return nullptr;
+  const int dev = msgat_current_device() & 63;
+  std::lock_guard<std::mutex> lk(g_side_mu);
+  SideCtx& c = g_side[dev];
+  if (!c.ok) {
+    if (cudaStreamCreateWithFlags(&c.s, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c.join, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    c.ok = true;
+  }
+  return &c;
+}
+void* msgat_fork(void* stream) {
+  SideCtx* c = side_ctx();
+  if (!c) return stream;
+  if (cudaEventRecord(c->fork, (cudaStream_t)stream) != cudaSuccess || cudaStreamWaitEvent(c->s, c->fork, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return stream;
+  }
+  return (void*)c->s;
+}
+void msgat_join(void* stream, void* side) {
+  if (side == stream) return;
+  SideCtx* c = side_ctx();
+  cudaEventRecord(c->join, (cudaStream_t)side);
+  cudaStreamWaitEvent((cudaStream_t)stream, c->join, 0);
+}
 #endif
 
 static int check_launch(const char* what) {

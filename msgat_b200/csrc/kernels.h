@@ -26,6 +26,15 @@ int meam_backward_impl(Plan& p, const msgat_meam_params* prm, const msgat_adj* a
                        void* stream);
 int64_t meam_backward_scratch(Plan& p);
 void msgat_set_error(const char* fmt, ...);
+// api.cu: side = msgat_fork(stream) makes the device's side stream wait for everything queued on `stream` and returns it (or
+// `stream` itself when forking is off); msgat_join(stream, side) makes `stream` wait for the side work.  Capture-safe.
+#ifdef MSGAT_EMU
+static inline void* msgat_fork(void* stream) { return stream; }
+static inline void msgat_join(void*, void*) {}
+#else
+void* msgat_fork(void* stream);
+void msgat_join(void* stream, void* side);
+#endif
 // CTAs per sample of a one-CTA-per-SM tcgen05 kernel whose CTAs stay inside a sample (per-sample weights):
 // `waves` rounds of 148 CTAs; more waves waste fewer SMs (148 is not a multiple of B) but repeat the set-up.
 static inline int tc_ctas_per_sample(int B, int ntile, int waves, const char* env) {

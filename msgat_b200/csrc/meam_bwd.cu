@@ -1070,6 +1070,9 @@ static int meam_backward_tail(Plan& p, BwdLayout& L, int Jw, const msgat_meam_pa
                               const float* saved, float* scratch, float* dx, const msgat_meam_grads* g, void* stream) {
   const int M = p.M;
   const int64_t sv_sm = p.saved_total, sc_sm = p.scratch_sm, dx_sm = (int64_t)p.B * p.C * p.N * 12;
+  // the softmax backward of the channel / temporal attention and dWt (per-sample, latency-bound) run on the side stream next to
+  // the dense column pass of the spatial attention; both chains meet again in front of k_bwd_fix
+  void* side = (p.Os && (p.Oc || p.Ot)) ? msgat_fork(stream) : stream;
   if (p.Os) {
     launch_scol(p, prm->sa_Wg, saved, scratch + L.o_delta, scratch + L.o_dqd, stream);
     SFinArgs a;
@@ -1090,14 +1093,15 @@ static int meam_backward_tail(Plan& p, BwdLayout& L, int Jw, const msgat_meam_pa
     a.caw_part = scratch + L.o_caw; a.Wc_part = scratch + L.o_Wc; a.dqc = scratch + L.o_dqc; a.dK = scratch + L.o_dK;
     size_t smem = ((size_t)p.C * 48 + 2 * (size_t)p.C * p.C + (size_t)p.Oc * p.C + 528) * 4;
     const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
-    MSGAT_LAUNCH(k_bwd_small, dim3(p.B, M), dim3(smT), smem, stream, a);
+    MSGAT_LAUNCH(k_bwd_small, dim3(p.B, M), dim3(smT), smem, side, a);
   }
   if (p.Ot && (g->ta_Wt1 || g->ta_Wt2)) {
     DwtArgs a;
     a.dK = scratch + L.o_dK; a.qt = saved + p.o_qt; a.sv_sm = sv_sm; a.sc_sm = sc_sm; a.B = p.B; a.N = p.N;
     for (int m = 0; m < M; ++m) { a.dWt1[m] = g[m].ta_Wt1; a.dWt2[m] = g[m].ta_Wt2; }
-    MSGAT_LAUNCH(k_dwt, dim3((p.N * 20 + 255) / 256, M), dim3(256), 0, stream, a);
+    MSGAT_LAUNCH(k_dwt, dim3((p.N * 20 + 255) / 256, M), dim3(256), 0, side, a);
   }
+  msgat_join(stream, side);
   {
     FixArgs a;
     a.x = x; a.x_sb = p.x_sb; a.x_sc = p.x_sc; a.x_sm = p.x_sm; a.dx_sm = dx_sm; a.sc_sm = sc_sm;

@@ -507,6 +507,8 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
     MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
   }
+  // the per-sample softmaxes (latency-bound, one block per sample) run on the side stream next to the dense score pass
+  void* side = (p.Os && (p.Oc || p.Ot)) ? msgat_fork(stream) : stream;
   if (p.Oc || p.Ot) {
     SmallArgs a;
     a.C = p.C; a.Oc = p.Oc; a.Ot = p.Ot; a.cmix = (p.flags & MSGAT_F_CMIX) ? 1 : 0; a.ntile = l2 ? (p.N + 7) / 8 : p.ntile_p;
@@ -517,9 +519,10 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.qc = saved + p.o_qc; a.Pc = saved + p.o_Pc; a.Mc = saved + p.o_Mc; a.K = saved + p.o_K; a.Pt = saved + p.o_Pt;
     size_t smem = ((size_t)p.C * 24 + (size_t)p.C * p.C + 240 + 144 + (l2 ? 8 * 240 : 0)) * 8;
     const int smT = p.C >= 16 ? 512 : 256;   // one block per sample: the C x C phases of a wide operator use 512 threads (81 -> 69 us, 57 -> 46 us at C = 72)
-    MSGAT_LAUNCH(k_small, dim3(p.B, M), dim3(smT), smem, stream, a);
+    MSGAT_LAUNCH(k_small, dim3(p.B, M), dim3(smT), smem, side, a);
   }
   if (p.Os) launch_sstats(p, prm, adj, saved, stream);
+  msgat_join(stream, side);
   if (l1_fwd_supported(p)) return launch_l1_fwd(p, prm, adj, x, out, saved, stream);   // first layer: one grouped launch
   if (l2 && !getenv("MSGAT_L2_OLD_APPLY")) return launch_l2_out(p, prm, adj, x, out, saved, stream);   // layer 2: one grouped launch
   // the apply pass: still one launch per component (the component's buffers by pointer offset)
