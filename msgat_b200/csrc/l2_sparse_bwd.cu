@@ -40,11 +40,21 @@ MSGAT_KERNEL MSGAT_LB(GZ_WARPS * 32, 4) k_l2_gz(GzArgs a) {
     ion[u] = it < b * 3;
     ioff[u] = ion[u] ? (int64_t)o * cs + q4 : 0;
   }
+  // Both stages are chains of dependent gathers (pointer -> index -> weight -> rows).  The heads of the second chain (the row's
+  // range, its first 32 edges, the node's own G rows) are requested here, in front of the first stage's loop, so that the two
+  // chains run side by side instead of one after the other (the stores of GZ in between keep the compiler from doing it).
+  const int k_lo = a.csc_ptr[n], k1 = a.csc_ptr[n + 1];
+  const int e_lo = a.row_ptr[n], e1 = a.row_ptr[n + 1];
+  const int cnt0 = e1 - e_lo < 32 ? e1 - e_lo : 32;
+  const int myc0 = lane < cnt0 ? a.col_idx[e_lo + lane] : 0;
+  const float myw0 = lane < cnt0 ? pwb[e_lo + lane] : 0.f;
+  float4 gs[3];
+#pragma unroll
+  for (int u = 0; u < 3; ++u) gs[u] = ion[u] ? ld4(Gs + (int64_t)n * 12 + ioff[u]) : f4zero();
   // ---- GZ: the node's column of A
   float4 gz[3] = {f4zero(), f4zero(), f4zero()};
   {
-    const int k1 = a.csc_ptr[n + 1];
-    for (int k0 = a.csc_ptr[n]; k0 < k1; k0 += 32) {
+    for (int k0 = k_lo; k0 < k1; k0 += 32) {
       const int cnt = k1 - k0 < 32 ? k1 - k0 : 32;
       const int myr = lane < cnt ? a.csc_row[k0 + lane] : 0;
       const float myw = lane < cnt ? pwb[a.csc_eid[k0 + lane]] : 0.f;
@@ -62,15 +72,11 @@ MSGAT_KERNEL MSGAT_LB(GZ_WARPS * 32, 4) k_l2_gz(GzArgs a) {
   for (int u = 0; u < 3; ++u)
     if (ion[u]) st4(gzo + ioff[u], gz[u]);
   // ---- dS at the non-zeros of the node's row, and their sum
-  float4 gs[3];
-#pragma unroll
-  for (int u = 0; u < 3; ++u) gs[u] = ion[u] ? ld4(Gs + (int64_t)n * 12 + ioff[u]) : f4zero();
   float dl = 0.f;
-  const int e1 = a.row_ptr[n + 1];
-  for (int e0 = a.row_ptr[n]; e0 < e1; e0 += 32) {
+  for (int e0 = e_lo; e0 < e1; e0 += 32) {
     const int cnt = e1 - e0 < 32 ? e1 - e0 : 32;
-    const int myc = lane < cnt ? a.col_idx[e0 + lane] : 0;
-    const float myw = lane < cnt ? pwb[e0 + lane] : 0.f;
+    const int myc = e0 == e_lo ? myc0 : (lane < cnt ? a.col_idx[e0 + lane] : 0);
+    const float myw = e0 == e_lo ? myw0 : (lane < cnt ? pwb[e0 + lane] : 0.f);
     float mine = 0.f;
 #pragma unroll 4
     for (int j = 0; j < cnt; ++j) {

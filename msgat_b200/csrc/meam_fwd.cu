@@ -503,9 +503,10 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     for (int m = 0; m < M; ++m) a.prm[m] = prm[m];
     a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
     a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
-    constexpr int NT = 16;
+    const int NT = p.NTp;
     size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
-    MSGAT_LAUNCH(k_prep<NT>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
+    if (NT == 64) MSGAT_LAUNCH(k_prep<64>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
+    else MSGAT_LAUNCH(k_prep<16>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
   }
   // the per-sample softmaxes (latency-bound, one block per sample) run on the side stream next to the dense score pass
   void* side = (p.Os && (p.Oc || p.Ot)) ? msgat_fork(stream) : stream;

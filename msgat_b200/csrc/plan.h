@@ -60,7 +60,7 @@ static inline int make_plan(const msgat_meam_desc* d, int nnz, Plan* p) {
   p->s_pre = (d->Os && (d->flags & MSGAT_F_SMIX) && d->C > d->Os) ? 1 : 0;
   p->Cz = d->Os ? (p->s_pre ? d->Os : d->C) : 0;
   // tiles
-  p->NTp = 16;
+  p->NTp = d->C <= 4 ? 64 : 16;   // narrow (first-layer) inputs: 16-node tiles leave most of a block idle (C * 16 rows on 256 threads)
   p->ntile_p = (d->N + p->NTp - 1) / p->NTp;
   int NT = 16;
   while (NT > 2 && apply_smem_floats(*p, NT) * 4 > MSGAT_SMEM_BUDGET) NT >>= 1;
