@@ -10,7 +10,8 @@ top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, capture_output=True)
 cubin = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
-dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
+outer = os.environ.get("OUTER") == "1"   # attribute to the outermost call site (the kernel's own line) instead of the inlined helper
+dis = subprocess.run(["nvdisasm", "-gi" if outer else "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 lines, cur, infn, stack = [], None, False, None
 for l in dis.splitlines():
     if l.startswith("\t.section\t.text."):
@@ -20,7 +21,7 @@ for l in dis.splitlines():
         continue
     m = re.match(r'\s*//## File "([^"]+)", line (\d+)(.*)', l)
     if m:
-        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+        cur = (os.path.basename(m.group(1)), int(m.group(2)))   # with -gi the last marker of a group is the outermost frame
         continue
     if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s", l):
         lines.append(cur)
