@@ -292,9 +292,6 @@ struct L2OutArgs {
 
 #define L2O_NSTG 2   // operand stages (two chunks each)
 #define L2O_NR 4     // raw chunks in flight
-#ifndef L2O_NP
-#define L2O_NP 1     // producer warps (rows np apart, as in k_l2_mix); measured again after the epilogue and converter changes: 966 us with one, 1042 us with two
-#endif
 static size_t l2_out_smem(int C, int KC, int b) {
   const int RB = KC > b ? KC : b;
   return (size_t)2 * C * 96 * 4 + (size_t)2 * C * 32 * 4 + (size_t)2 * 2 * b * 32 * 4 + (size_t)L2O_NSTG * 4 * RB * 128 * 4 +
@@ -302,7 +299,7 @@ static size_t l2_out_smem(int C, int KC, int b) {
 }
 
 template <int BW>
-MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(L2O_NP), 1) k_l2_out(L2OutArgs a) {
+MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(1), 1) k_l2_out(L2OutArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // aligned inside the shared window: the pointer stays a shared-memory pointer (LDS / STS, not generic LD / ST)
   const int C = a.C, KC = a.KC, nxc = C / KC, RB = KC > BW ? KC : BW, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, m = blockIdx.y;
@@ -384,10 +381,9 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(L2O_NP), 1) k_l2_out(L2OutArgs a) {
   const uint32_t tm = warp_uniform(*tmem_slot);
   const int IT = nxc + 1, NRAW = nxc + 2;   // work items and raw chunks per tile
 
-  if (warp >= L2_PROD_WARP) {
-    // ================= producers: warp pw of L2O_NP issues the rows pw, pw + L2O_NP, ... of every chunk =================
+  if (warp == L2_PROD_WARP) {
+    // ================= producer (one warp: this kernel is bound by its converters, see l2_common.cuh) =================
     const float* xm = a.x + (int64_t)m * a.x_sm;
-    const int pw = warp - L2_PROD_WARP, prow = pw + L2O_NP * lane;
     int r = 0;
     for (int tile = t_lo; tile < t_hi; ++tile) {
       const int bi = tile / a.ntile, n0 = (tile - bi * a.ntile) * L2_NT;
@@ -396,11 +392,11 @@ MSGAT_KERNEL MSGAT_LB(L2_THREADS_NP(L2O_NP), 1) k_l2_out(L2OutArgs a) {
       for (int j = 0; j < NRAW; ++j, ++r) {
         const int rs = r % L2O_NR, use = r / L2O_NR, rows = j < nxc ? KC : BW;
         if (use > 0) mbar_wait(REMPTY(rs), (uint32_t)((use - 1) & 1));
-        if (pw == 0 && lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(rows * nv * 48));
-        if (prow < rows) {
-          const float* src = j < nxc ? xm + (int64_t)bi * a.x_sb + (int64_t)(j * KC + prow) * a.x_sc + (int64_t)n0 * 12
-                                     : A2b + (int64_t)((j - nxc) * BW + prow) * cs + (int64_t)n0 * 12;
-          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)prow * L2_RAW_ROW, src, (uint32_t)(nv * 48), RFULL(rs));
+        if (lane == 0) mbar_arrive_expect_tx(RFULL(rs), (uint32_t)(rows * nv * 48));
+        if (lane < rows) {
+          const float* src = j < nxc ? xm + (int64_t)bi * a.x_sb + (int64_t)(j * KC + lane) * a.x_sc + (int64_t)n0 * 12
+                                     : A2b + (int64_t)((j - nxc) * BW + lane) * cs + (int64_t)n0 * 12;
+          bulk_g2s(RAW + (size_t)rs * raw_bytes + (size_t)lane * L2_RAW_ROW, src, (uint32_t)(nv * 48), RFULL(rs));
         }
       }
     }
@@ -635,9 +631,9 @@ int launch_l2_out(const Plan& p, const msgat_meam_params* prm, const msgat_adj* 
   a.row_ptr = adj->row_ptr; a.col_idx = adj->col_idx; a.out = out;
   const size_t smem = l2_out_smem(p.C, a.KC, p.Oc);
   switch (p.Oc) {
-    case 8: MSGAT_LAUNCH(k_l2_out<8>, dim3(G, p.M), dim3(L2_THREADS_NP(L2O_NP)), smem, stream, a); break;
-    case 16: MSGAT_LAUNCH(k_l2_out<16>, dim3(G, p.M), dim3(L2_THREADS_NP(L2O_NP)), smem, stream, a); break;
-    default: MSGAT_LAUNCH(k_l2_out<24>, dim3(G, p.M), dim3(L2_THREADS_NP(L2O_NP)), smem, stream, a); break;
+    case 8: MSGAT_LAUNCH(k_l2_out<8>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
+    case 16: MSGAT_LAUNCH(k_l2_out<16>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
+    default: MSGAT_LAUNCH(k_l2_out<24>, dim3(G, p.M), dim3(L2_THREADS_NP(1)), smem, stream, a); break;
   }
   return 0;
 }

@@ -377,6 +377,17 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       for (int g2 = 0; g2 < TD_NGR; ++g2) s += (double)PRE[g2 * 144 + tid];
       pt_acc += s;
     }
+    // the x rows of the LayerNorm backward (phase 5) are requested here: their L2 latency runs under phase 4
+    float4 xq[2][3];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int r = tid + q * TD_THREADS, c = r / TD_NT, nl = r - c * TD_NT, n = n0 + nl;
+      xq[q][0] = xq[q][1] = xq[q][2] = f4zero();
+      if (r < C * TD_NT && n < a.N) {
+        const float* src = xb + c * a.x_sc + (int64_t)n * 12;
+        xq[q][0] = ld4(src); xq[q][1] = ld4(src + 4); xq[q][2] = ld4(src + 8);
+      }
+    }
     // ---- 4. D_h -> staging rows STG[C][.] (over the A tile, which the tensor core has finished reading)
     {
       int g = 0;
@@ -398,8 +409,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       if (r < C * TD_NT) {
         const int c = r / TD_NT, nl = r - c * TD_NT, n = n0 + nl;
         if (n < a.N) {
-          const float* src = xb + c * a.x_sc + (int64_t)n * 12;
-          const float4 u = ld4(src), v = ld4(src + 4), w = ld4(src + 8);
+          const float4 u = xq[q][0], v = xq[q][1], w = xq[q][2];
           float xh[12] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w, w.x, w.y, w.z, w.w};
           uint32_t mb = 0;
 #pragma unroll
