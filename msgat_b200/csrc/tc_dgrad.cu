@@ -322,6 +322,14 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
         td_split4(GH, GL, sw128b32_off(2 * b + gz_o0 + j, gz_nl * 12 + gz_t0, cbO), gz[j]);
       }
     }
+    // the saved first-conv taps of the dPt contraction below: the first tap's rows are requested in front of the barrier, the
+    // second tap's while the first is contracted (their L2 latency was exposed inside the short second MMA window)
+    const int p_blk9 = tid % 9, p_grp = tid / 9, p_ib = (p_blk9 % 3) * 4, p_n = n0 + (p_grp & 7), p_kb = p_grp >> 3;
+    const bool p_on = tid < TD_NGR * 9 && p_n < a.N;
+    float4 hq[2][6];
+#pragma unroll
+    for (int m = 0; m < 6; ++m)
+      hq[0][m] = p_on && p_kb + 4 * m < b ? ld4(A2b + ((int64_t)(p_kb + 4 * m) * a.N + p_n) * 12 + p_ib) : f4zero();
     fence_smem_to_async();
     __syncthreads();
     if (tid == TD_ISSUER) {
@@ -338,12 +346,13 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) o16[i] = 0.f;
       if (n < a.N) {
+#pragma unroll
+        for (int m = 0; m < 6; ++m)
+          hq[1][m] = p_kb + 4 * m < b ? ld4(A2b + ((int64_t)(b + p_kb + 4 * m) * a.N + n) * 12 + ib) : f4zero();
+#pragma unroll
         for (int tap = 0; tap < 2; ++tap) {
           const int sh = tap ? a.d1 : 0, kb = grp >> 3, sr = sh & 3, q0 = tb + (sh & ~3);
-          float4 h[6];   // all loads of a tap in flight before the first use (b <= 24: at most 6 rows)
-#pragma unroll
-          for (int m = 0; m < 6; ++m)
-            h[m] = kb + 4 * m < b ? ld4(A2b + ((int64_t)(tap * b + kb + 4 * m) * a.N + n) * 12 + ib) : f4zero();
+          const float4 (&h)[6] = hq[tap];
 #pragma unroll
           for (int m = 0; m < 6; ++m) {
             if (kb + 4 * m < b) {
