@@ -193,10 +193,13 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   for (int tile = jslot; tile < a.ntile; tile += a.J) {
     const int n0 = tile * TD_NT;
     // the thread's first G row is requested before the prefetch instructions below queue up in front of it
-    float4 g0a = f4zero(), g0b = f4zero(), g0c = f4zero();
+    float4 g0a = f4zero(), g0b = f4zero(), g0c = f4zero(), g1a = f4zero(), g1b = f4zero(), g1c = f4zero();
     {
-      const int o = tid / TD_NT, nl = tid - o * TD_NT, n = n0 + nl;
-      if (n < a.N) { const float* s = Gb + ((int64_t)o * a.N + n) * 12; g0a = ld4(s); g0b = ld4(s + 4); g0c = ld4(s + 8); }
+      const int o = tid / TD_NT, nl = tid - o * TD_NT, n = n0 + nl, o1 = o + TD_THREADS / TD_NT;
+      if (n < a.N) {
+        const float* s = Gb + ((int64_t)o * a.N + n) * 12; g0a = ld4(s); g0b = ld4(s + 4); g0c = ld4(s + 8);
+        if (o1 < O) { const float* s1 = Gb + ((int64_t)o1 * a.N + n) * 12; g1a = ld4(s1); g1b = ld4(s1 + 4); g1c = ld4(s1 + 8); }
+      }
     }
     // L2 prefetch of what this tile reads late and latency-bound: the saved first-conv taps (dPt, inside
     // the second MMA window) and the x rows of the LayerNorm backward.  One 128-byte line per thread.
@@ -229,11 +232,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       const int r = tid + q * TD_THREADS;
       if (r < O * TD_NT) {
         const int o = r / TD_NT, nl = r - o * TD_NT, n = n0 + nl, pp = nl * 12;
-        float4 u = g0a, v = g0b, w = g0c;
-        if (q == 1) {
-          u = v = w = f4zero();
-          if (n < a.N) { const float* s = Gb + ((int64_t)o * a.N + n) * 12; u = ld4(s); v = ld4(s + 4); w = ld4(s + 8); }
-        }
+        const float4 u = q ? g1a : g0a, v = q ? g1b : g0b, w = q ? g1c : g0c;
         bsG[q] += ((u.x + u.y) + (u.z + u.w)) + ((v.x + v.y) + (v.z + v.w)) + ((w.x + w.y) + (w.z + w.w));
         td_split4(GH, GL, sw128b32_off(o, pp, cbO), u);
         td_split4(GH, GL, sw128b32_off(o, pp + 4, cbO), v);
