@@ -176,6 +176,12 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
     const int cbase0 = j * S3_COLS + half * 64;
     const float* qf = QF + (j & 1) * S3_COLS * 12 + half * 64 * 12;
     const float2* mw = MW + (j & 1) * S3_COLS + half * 64;
+    // fp32 partial sums of TWO chunks (16 columns) go to the fp64 accumulators at once: the fp32 -> fp64 conversions run on the
+    // quarter-rate conversion pipe, 13 per chunk next to its 8 exponentials
+    float lc = 0.f;
+    float2 Ec2[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Ec2[k] = make_float2(0.f, 0.f);
 #pragma unroll 1
     for (int c0 = 0; c0 < 64; c0 += 8) {
       if (cbase0 + c0 >= a.N) break;   // warp-uniform: the chunk lies beyond the last column (every chunk that is processed has a live
@@ -188,10 +194,6 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) s[i] = __uint_as_float(v0[i]) + __uint_as_float(v1[i]);
       const int cbase = cbase0 + c0;
-      float lc = 0.f;
-      float2 Ec2[6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) Ec2[k] = make_float2(0.f, 0.f);
       if (!BWD) {
         // raw scores of the row's adjacency entries in this chunk (normalised once m and l are final)
         if (nc < cbase + 8) {   // rare: ~3 entries per row of N columns
@@ -207,10 +209,14 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
         }
         const float mg = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), fmaxf(fmaxf(s[4], s[5]), fmaxf(s[6], s[7])));
         if (mg > m) {
-          const double c = (double)expf(m - mg);
+          const float cf = expf(m - mg);
+          const double c = (double)cf;
           l *= c;
 #pragma unroll
           for (int t = 0; t < 12; ++t) E[t] *= c;
+          lc *= cf;   // the pending fp32 partials of the chunk before
+#pragma unroll
+          for (int k = 0; k < 6; ++k) Ec2[k] = fmul2(Ec2[k], make_float2(cf, cf));
           m = mg;
         }
 #pragma unroll
@@ -224,7 +230,6 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
           Ec2[2] = ffma2(p2, lo2(q1), Ec2[2]); Ec2[3] = ffma2(p2, hi2(q1), Ec2[3]);
           Ec2[4] = ffma2(p2, lo2(q2), Ec2[4]); Ec2[5] = ffma2(p2, hi2(q2), Ec2[5]);
         }
-        l += (double)lc;
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -238,9 +243,16 @@ MSGAT_KERNEL MSGAT_LB(S3_THREADS, 2) k_score_tc32(S3Args a) {
           Ec2[4] = ffma2(p2, lo2(u2), Ec2[4]); Ec2[5] = ffma2(p2, hi2(u2), Ec2[5]);
         }
       }
+      if (c0 & 8) {   // every second chunk (the last chunk of a tile's half is an odd one: 64 columns = 8 chunks)
+        if (!BWD) { l += (double)lc; lc = 0.f; }
 #pragma unroll
-      for (int k = 0; k < 6; ++k) { E[2 * k] += (double)Ec2[k].x; E[2 * k + 1] += (double)Ec2[k].y; }
+        for (int k = 0; k < 6; ++k) { E[2 * k] += (double)Ec2[k].x; E[2 * k + 1] += (double)Ec2[k].y; Ec2[k] = make_float2(0.f, 0.f); }
+      }
     }
+    // a tile that ended on an even chunk (ragged last tile) leaves partials behind
+    if (!BWD) { l += (double)lc; lc = 0.f; }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { E[2 * k] += (double)Ec2[k].x; E[2 * k + 1] += (double)Ec2[k].y; Ec2[k] = make_float2(0.f, 0.f); }
     if (j + 1 < ntile) store_tile(j + 1);
     fence_smem_to_async();
     tc_fence_before_sync();
