@@ -140,16 +140,28 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
   double* St = K + 240;                              // [144]
   if (a.Oc) {
     const float* pqf = a.pqc + m * a.sc_sm;
-    for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
-      double s = 0.0;
-      if (a.l2) {
-        // independent loads, serial fp64 adds in tile order: eight loads in flight instead of one L2 round trip per tile
+    if (a.l2) {
+      // independent loads, serial fp64 adds in tile order; a thread walks its (up to) two outputs together: sixteen loads in flight
+      // instead of one L2 round trip per tile and output
+      for (int i = threadIdx.x; i < C * 12; i += 2 * blockDim.x) {
+        const int i1 = i + blockDim.x;
+        const bool two = i1 < C * 12;
+        const float* p0 = pqf + (int64_t)b * a.ntile * C * 12 + i;
+        const float* p1 = p0 + (two ? blockDim.x : 0);
+        double s0 = 0.0, s1 = 0.0;
         MSGAT_UNROLL_N(8)
-        for (int tl = 0; tl < a.ntile; ++tl) s += (double)pqf[((int64_t)b * a.ntile + tl) * C * 12 + i];
+        for (int tl = 0; tl < a.ntile; ++tl) { s0 += (double)p0[(int64_t)tl * C * 12]; s1 += (double)p1[(int64_t)tl * C * 12]; }
+        qc[i] = s0;
+        qc_o[(int64_t)b * C * 12 + i] = (float)s0;
+        if (two) { qc[i1] = s1; qc_o[(int64_t)b * C * 12 + i1] = (float)s1; }
       }
-      else for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
-      qc[i] = s;
-      qc_o[(int64_t)b * C * 12 + i] = (float)s;
+    } else {
+      for (int i = threadIdx.x; i < C * 12; i += blockDim.x) {
+        double s = 0.0;
+        for (int tl = 0; tl < a.ntile; ++tl) s += pqc_m[((int64_t)b * a.ntile + tl) * C * 12 + i];
+        qc[i] = s;
+        qc_o[(int64_t)b * C * 12 + i] = (float)s;
+      }
     }
   }
   if (a.Ot && !a.l2) {
@@ -164,28 +176,51 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
     // temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T over all N nodes (attention.py:65) from the saved query, fp64;
     // two halves of the nodes per output, combined through St (free until the scores are formed)
     const float* qtb = a.qt + m * a.sv_sm + (int64_t)b * a.N * 12;
-    // thread = (node group, rank index r, quad of t): one 128-bit read of q_t and one weight per node, 4 fp64 FMAs
-    const int parts = (int)blockDim.x / 60;
-    const int part = threadIdx.x / 60, rq = threadIdx.x - part * 60, r = rq / 3, t4 = (rq - r * 3) * 4;
-    double* KP = St + 144;   // [parts][240], behind the score matrix (the launch adds the room in l2 mode)
-    if (part < parts) {
-      const float* W = (r < 10) ? a.prm[m].ta_Wt1 + (int64_t)r * a.N : a.prm[m].ta_Wt2 + (int64_t)(r - 10) * a.N;
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-      MSGAT_UNROLL_N(4)
-      for (int n = part; n < a.N; n += parts) {
-        const double w = (double)__ldg(W + n);
-        const float4 qv = ld4(qtb + (int64_t)n * 12 + t4);
-        s0 += w * (double)qv.x; s1 += w * (double)qv.y; s2 += w * (double)qv.z; s3 += w * (double)qv.w;
+    // The sample's q_t rows are staged in shared memory AS DOUBLES (converted once; the score matrix S, K, St and the partial
+    // area behind them are free until the scores are formed), in chunks of as many nodes as fit.  Thread = (rank index r,
+    // node group g): per node one weight W[r][n] (consecutive lanes read consecutive n) and the node's 12 staged values,
+    // 12 fp64 FMAs.  The per-group sums meet in the same area.
+    const int Rn = C * C + 240 + 144 + 8 * 240;             // doubles behind S (see the launch)
+    double* R = S;
+    int NG = (int)blockDim.x / 20;
+    if (NG > Rn / 240) NG = Rn / 240;
+    const int capn = Rn / 12;
+    const int r = threadIdx.x / NG, g = threadIdx.x - r * NG;
+    const bool on = threadIdx.x < 20 * NG;
+    const float* W = on ? ((r < 10) ? a.prm[m].ta_Wt1 + (int64_t)r * a.N : a.prm[m].ta_Wt2 + (int64_t)(r - 10) * a.N) : nullptr;
+    double acc[12];
+    MSGAT_UNROLL
+    for (int t = 0; t < 12; ++t) acc[t] = 0.0;
+    for (int base = 0; base < a.N; base += capn) {
+      const int cn = a.N - base < capn ? a.N - base : capn;
+      __syncthreads();   // the chunk before has been consumed (first trip: qc is written, nobody reads R yet)
+      for (int i = threadIdx.x; i < cn * 3; i += blockDim.x) {
+        const float4 v = ld4(qtb + (int64_t)base * 12 + i * 4);
+        R[i * 4 + 0] = (double)v.x; R[i * 4 + 1] = (double)v.y; R[i * 4 + 2] = (double)v.z; R[i * 4 + 3] = (double)v.w;
       }
-      double* kp = KP + part * 240;
-      kp[(t4 + 0) * 20 + r] = s0; kp[(t4 + 1) * 20 + r] = s1; kp[(t4 + 2) * 20 + r] = s2; kp[(t4 + 3) * 20 + r] = s3;
+      __syncthreads();
+      if (on) {
+        MSGAT_UNROLL_N(4)
+        for (int n = g; n < cn; n += NG) {
+          const double w = (double)__ldg(W + base + n);
+          const double* q = R + n * 12;
+          MSGAT_UNROLL
+          for (int t = 0; t < 12; ++t) acc[t] += w * q[t];
+        }
+      }
     }
     __syncthreads();
+    if (on) {
+      MSGAT_UNROLL
+      for (int t = 0; t < 12; ++t) R[g * 240 + t * 20 + r] = acc[t];
+    }
+    __syncthreads();
+    double ksum = 0.0;
+    if (threadIdx.x < 240) for (int k = 0; k < NG; ++k) ksum += R[k * 240 + threadIdx.x];
+    __syncthreads();   // K lies inside R
     if (threadIdx.x < 240) {
-      double s = 0.0;
-      for (int k = 0; k < parts; ++k) s += KP[k * 240 + threadIdx.x];
-      K[threadIdx.x] = s;
-      K_o[(int64_t)b * 240 + threadIdx.x] = (float)s;
+      K[threadIdx.x] = ksum;
+      K_o[(int64_t)b * 240 + threadIdx.x] = (float)ksum;
     }
   }
   __syncthreads();
@@ -207,13 +242,21 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_small(SmallArgs a) {
       S[i] = s;
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-      double m = -INFINITY;
-      for (int j = 0; j < C; ++j) m = fmax(m, S[c * C + j]);
+    // four threads per row (columns part, part + 4, ...), combined with two shuffles: the rows of a wide operator were 72
+    // serial fp64 exponentials on 72 of the block's threads
+    for (int base = 0; base < 4 * C; base += blockDim.x) {   // every thread takes every trip: the shuffles are warp-wide
+      const int c4 = base + threadIdx.x, c = c4 >> 2, part = c4 & 3;
+      const bool live = c4 < 4 * C;
+      double mx = -INFINITY;
+      if (live) for (int j = part; j < C; j += 4) mx = fmax(mx, S[c * C + j]);
+      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
       double l = 0.0;
-      for (int j = 0; j < C; ++j) { double e = exp(S[c * C + j] - m); S[c * C + j] = e; l += e; }
+      if (live) for (int j = part; j < C; j += 4) { const double e = exp(S[c * C + j] - mx); S[c * C + j] = e; l += e; }
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
       const double inv = 1.0 / l;
-      for (int j = 0; j < C; ++j) S[c * C + j] *= inv;
+      if (live) for (int j = part; j < C; j += 4) S[c * C + j] *= inv;
     }
     __syncthreads();
     for (int i = threadIdx.x; i < C * C; i += blockDim.x) Pc_o[(int64_t)b * C * C + i] = (float)S[i];
