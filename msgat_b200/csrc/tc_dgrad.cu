@@ -28,6 +28,7 @@
 #define TD_PITCH 100
 #define TD_NGR 32      // 9-thread groups of the dPt contraction
 #define TD_ISSUER 320  // MMA-issuing thread: warp 10 has no work inside the two MMA windows, so nothing waits for the issue
+#define TD_ISSUER2 352 // second issuing thread (warp 11) of the first window: D_x (27 of its 45 MMAs) on its own barrier
 
 struct TcDgradArgs {   // grouped: blockIdx.y = component; inputs x_sm / g_sm apart, saved slices sv_sm, scratch slices sc_sm, dx dx_sm apart
   const float* x; int64_t x_sb, x_sc, x_sm, g_sm, sv_sm, sc_sm, dx_sm;
@@ -117,6 +118,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   float* RED = DL + 16;                                   // [16][24] final LayerNorm-affine reduction
   uint64_t& bar = *reinterpret_cast<uint64_t*>(RED + 16 * 24);
   uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(RED + 16 * 24 + 2);
+  uint64_t& bar2 = *reinterpret_cast<uint64_t*>(RED + 16 * 24 + 4);
   float* STG = reinterpret_cast<float*>(GH);              // [C][TD_PITCH] D_h rows, aliases the A tile once it is consumed
 
   // ---- one-time staging: weights as B operands [K][N] (N contiguous), hi / lo, zero padded
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     td_split1(W2H, W2L, sw128b32_off(k, n, cbM), w);
   }
   if (tid < 12) { LW[tid] = a.ln_w[m][tid]; LW[12 + tid] = a.ln_b[m][tid]; }
-  if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_fence_init(); }
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); mbar_init(smem_u32(&bar2), 1); mbar_fence_init(); }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_slot), 512);
   tc_fence_before_sync();
   __syncthreads();
@@ -153,7 +155,7 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
   const uint64_t dWMH = umma_desc(smem_u32(WMH), cbM, 512u, 1), dWML = umma_desc(smem_u32(WML), cbM, 512u, 1);
   const uint64_t dW2H = umma_desc(smem_u32(W2H), cbM, 512u, 1), dW2L = umma_desc(smem_u32(W2L), cbM, 512u, 1);
   const uint32_t idescC = umma_idesc_tf32(128, (C + 15) & ~15, 1, 1), idescY = umma_idesc_tf32(128, 2 * b, 1, 1);
-  uint32_t phase = 0;
+  uint32_t phase = 0, phase2 = 0;
   const int l = tid & 127, quarter = warp >> 2;   // l = TMEM lane = position; the 4 warpgroups split the column groups
   const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
 
@@ -244,9 +246,13 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
     if (tid == TD_ISSUER) {
       tc_fence_after_sync();
       for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dy, dGH, dGL, dW2H, dW2L, b / 8 + ks, ks, idescY, ks > 0);
+      umma_commit(smem_u32(&bar));
+    }
+    if (tid == TD_ISSUER2) {   // the issue of an MMA costs ~40 cycles of dependent uniform-datapath work: two threads halve the window
+      tc_fence_after_sync();
       for (int ks = 0; ks < b / 8; ++ks) td_mma3(Dh, dGH, dGL, dWMH, dWML, ks, ks, idescC, ks > 0);
       for (int ks = 0; ks < O / 8; ++ks) td_mma3(Dx, dGH, dGL, dWXH, dWXL, ks, ks, idescC, ks > 0);
-      umma_commit(smem_u32(&bar));
+      umma_commit(smem_u32(&bar2));
     }
     // ---- while the tensor core runs: the GZ rows of this tile, computed by k_l2_gz (transposed sparse aggregation
     // through the CSC view, attention.py:36), come in from the tcA buffer: 4 channels x 4 positions per item
@@ -271,6 +277,8 @@ __global__ void __launch_bounds__(TD_THREADS, 1) k_tc_dgrad(TcDgradArgs a) {
       }
     }
     __syncthreads();
+    mbar_wait(smem_u32(&bar2), phase2); phase2 ^= 1;   // the D_x products read the G tile that phase 3 overwrites
+    tc_fence_after_sync();
     // ---- 3. rows of 12: dY1, dA_now / dA_past (two threads per row), GZ gather -> the A tile again
     if (tid < 2 * b * TD_NT) {
       const int item = tid >> 1, half = tid & 1, k = item / TD_NT, nl = item - k * TD_NT, n = n0 + nl, pp = nl * 12;
