@@ -13,8 +13,11 @@
  *     the (n, t) plane must be contiguous, batch and channel strides are explicit;
  *   - the library never allocates caller-visible memory: outputs, saved statistics and
  *     scratch are caller-owned buffers whose sizes msgat_meam_sizes() reports;
- *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), nothing
- *     synchronises the device;
+ *   - all work is ordered on `stream` (a cudaStream_t passed as void*), nothing
+ *     synchronises the device; msgat_meam_forward / _backward run their per-sample
+ *     kernels on a side stream of the library that is forked from and joined back
+ *     into `stream` with events inside the call (legal under stream capture;
+ *     MSGAT_NO_FORK=1 in the environment disables it);
  *   - return value 0 on success, negative on error; msgat_last_error() gives the text.
  *     No CPU fallback exists: without an sm_100 device msgat_device_check() fails.
  */
