@@ -810,7 +810,10 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
     __syncthreads();
     for (int r = tid; r < C * NT; r += T) {
       const int c = r / NT, nl = r - c * NT, n = n0 + nl;
-      double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+      // the three alpha-gradient dot products of a row: 12 terms each in fp32 FMAs, the ROW sums then go to the fp64 accumulation
+      // over rows, tiles and samples (per-term fp64 products cost four fp32 -> fp64 conversions per element on the quarter-rate
+      // conversion pipe: 17 % of this kernel's samples; the error of a 12-term fp32 dot is random per row and averages out)
+      float v1 = 0.f, v2 = 0.f, v3 = 0.f;
 #ifndef MSGAT_EMU
       {   // the rows of the thread's NEXT item on their way into L1 while this one is computed
         const int r2 = r + T, c2 = r2 / NT, n2 = n0 + r2 - c2 * NT;
@@ -853,7 +856,7 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_bwd_fix(FixArgs a) {
         for (int t = 0; t < 12; ++t) {
           const float dqc = a.Oc ? DQC[c * 12 + t] : 0.f, dqt = DQT[nl * 12 + t], dqs = DQS[nl * 12 + t];
           dh[t] = an * dqc + att * dqt + as * dqs;
-          v1 += (double)dqc * h[t]; v2 += (double)dqt * h[t]; v3 += (double)dqs * h[t];
+          v1 = fmaf(dqc, h[t], v1); v2 = fmaf(dqt, h[t], v2); v3 = fmaf(dqs, h[t], v3);
         }
         const int64_t rowo = (((int64_t)b * C + c) * a.N + n) * 12;
         if (g_DH) {
