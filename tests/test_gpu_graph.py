@@ -52,3 +52,47 @@ def test_gradient_sinks_equal_autograd_accumulation():
         torch.cuda.synchronize()
         outs.append(fg.flat.clone())
     assert torch.equal(outs[0], outs[1])
+
+
+_FORK_PROBE = r"""
+import hashlib, sys, torch
+sys.path.insert(0, {root!r})
+from msgat_b200 import models, synthetic
+from msgat_b200.loss import huber_loss
+torch.manual_seed(5)
+N, C, M, B = 170, 3, 3, 4
+adj = synthetic.road_graph(N, 200, seed=2)
+model = models.msgat72(n_components=M, in_channels=C, in_timesteps=12, out_timesteps=12, use_te=True, adj=adj.clone()).cuda()
+b = synthetic.make_batch(B, M, C, N, seed=11)
+h = hashlib.sha256()
+for _ in range(3):
+    model.zero_grad(set_to_none=True)
+    out = model(b.X.cuda(), b.H.cuda(), b.D.cuda())
+    huber_loss(out, b.Y.cuda(), 50.0).backward()
+    torch.cuda.synchronize()
+    h.update(out.detach().cpu().numpy().tobytes())
+    for p in model.parameters():
+        if p.grad is not None:
+            h.update(p.grad.cpu().numpy().tobytes())
+print("DIGEST", h.hexdigest())
+"""
+
+
+def test_side_stream_changes_no_bit():
+    """The library forks a side stream for the per-sample kernels of a MEAM (api.cu: msgat_fork / msgat_join).  With
+    MSGAT_NO_FORK=1 everything runs on the caller's stream: outputs and every parameter gradient of three training steps
+    must be bit-identical either way (a missed dependency between the two branches would show here as a difference)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for no_fork in (False, True):
+        env = dict(os.environ)
+        env.pop("MSGAT_NO_FORK", None)
+        if no_fork:
+            env["MSGAT_NO_FORK"] = "1"
+        r = subprocess.run([sys.executable, "-c", _FORK_PROBE.format(root=root)], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        digests.append([l for l in r.stdout.splitlines() if l.startswith("DIGEST")][-1])
+    assert digests[0] == digests[1]
