@@ -1023,7 +1023,12 @@ static int bwd_layout(Plan& p, BwdLayout& L) {
   L.l1 = l1_bwd_supported(p) ? 1 : 0;
   if (L.l1) { L.J = l1_bwd_blocks_per_sample(p); L.S = 1; }
   L.nblk = L.J * p.B;
-  L.NT4 = 16; L.ntile4 = (p.N + 15) / 16;
+  // nodes per tile of k_bwd_fix: a tile is C x NT4 rows for 128 threads; a narrow (first-layer) input gets wider tiles so that
+  // at least 64 rows are in flight per block (C = 1 with 16-node tiles kept 16 of 128 threads busy: 118 us for 17 MB)
+  L.NT4 = 16;
+  while (L.NT4 < 64 && p.C * L.NT4 < 64) L.NT4 <<= 1;
+  { const char* e = getenv("MSGAT_FIX_NT"); if (e && (atoi(e) == 16 || atoi(e) == 32 || atoi(e) == 64)) L.NT4 = atoi(e); }
+  L.ntile4 = (p.N + L.NT4 - 1) / L.NT4;
   L.J4 = pick_J(p.B, L.ntile4, msgat_sm_count() * 4); L.nblk4 = L.J4 * p.B;
   L.nfin = (p.N + 127) / 128;
   int64_t o = 0;
@@ -1119,11 +1124,13 @@ static int meam_backward_tail(Plan& p, BwdLayout& L, int Jw, const msgat_meam_pa
       a.csc_ptr = adj->csc_ptr; a.csc_row = adj->csc_row; a.csc_eid = adj->csc_eid;
     }
     a.ln_part = scratch + L.o_ln + (int64_t)L.nblk * 24;
-    size_t smem = ((size_t)p.C * 12 + 2 * 192 + 5 * (size_t)p.C * 16 + 240 + 24 + 8 * 24) * 4;
+    size_t smem = ((size_t)p.C * 12 + 2 * 12 * (size_t)L.NT4 + 5 * (size_t)p.C * L.NT4 + 240 + 24 + 8 * 24) * 4;
     // 128-thread blocks, four per SM (a thread owns channel tid across the tiles: at least C threads): more
     // independent blocks hide the barriers between the phases of a tile (C = 1: 35 -> 25 us, C = 72: 118 -> 114 us)
     const int fixT = p.C > 128 ? ((p.C + 31) & ~31) : 128;
-    MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B, M), dim3(fixT), smem, stream, a);
+    if (L.NT4 == 64) MSGAT_LAUNCH(k_bwd_fix<64>, dim3(L.J4, p.B, M), dim3(fixT), smem, stream, a);
+    else if (L.NT4 == 32) MSGAT_LAUNCH(k_bwd_fix<32>, dim3(L.J4, p.B, M), dim3(fixT), smem, stream, a);
+    else MSGAT_LAUNCH(k_bwd_fix<16>, dim3(L.J4, p.B, M), dim3(fixT), smem, stream, a);
   }
   {
     ReduceArgs r;
