@@ -351,14 +351,14 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_fwd12(HeadArgs a0, HeadGrp grp) {
 // LayerNorm([12]) backward of one row: dh -> dx (masked by x > 0 when x is a ReLU output), affine gradient
 // partials.  The normalised row comes back from the warp buffer the thread wrote it to.
 MSGAT_DEV void head_ln_bwd_row(const float (&dh)[12], const Row12& xr, const float* hrow, float rs, const float* LW,
-                               float (&lnw_acc)[12], float (&lnb_acc)[12], int x_is_relu, float* dst) {
+                               float (&lnw_acc)[12], int x_is_relu, float* dst) {
   const float4 h0 = ld4(hrow), h1 = ld4(hrow + 4), h2 = ld4(hrow + 8);
   const float xh[12] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w, h2.x, h2.y, h2.z, h2.w};
   const float xv[12] = {xr.a.x, xr.a.y, xr.a.z, xr.a.w, xr.b.x, xr.b.y, xr.b.z, xr.b.w, xr.c.x, xr.c.y, xr.c.z, xr.c.w};
   float m1 = 0.f, m2 = 0.f;
   MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) {
-    lnw_acc[t] += dh[t] * xh[t]; lnb_acc[t] += dh[t];
+    lnw_acc[t] += dh[t] * xh[t];
     const float gg = dh[t] * LW[t];
     m1 += gg; m2 += gg * xh[t];
   }
@@ -394,11 +394,21 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   float* BS = LW + 24;                              // [12] column sums of DY (fc bias gradient of the block)
   float* RED = BS + 12;                             // [HS_WARPS][24]
   float* XS = RED + HS_WARPS * 24;                  // [HS_WARPS][HS_NODES][12]  next channel's rows in flight
+  float* WS = XS + HS_WARPS * HS_NODES * 12;        // [12 o][12 t] fc weights summed over the channels
   float* stage = XS + warp * HS_NODES * 12;
   // fc weights staged once per block; the block walks the logical blocks (sample b, node tile) of its component, each with its
   // own slice of partial sums (same layout as when every logical block was a CTA)
   stage_fc12(Wh, a.fc_w, C);
   if (tid < 12) { LW[tid] = a.ln_w[tid]; LW[12 + tid] = a.ln_b[tid]; }
+  __syncthreads();
+  // The LayerNorm bias gradient of a logical block, sum over its rows of dh[t] = sum_o fc_w[o][t][c] dy[n][o], is
+  // sum_o (sum_n dy[n][o]) (sum_c fc_w[o][t][c]) = sum_o BS[o] WS[o][t]: no per-row accumulation (12 registers of every thread
+  // across the channel loop, 24 additions per channel)
+  if (tid < 144) {
+    float sw = 0.f;
+    for (int c = 0; c < C; ++c) sw += Wh[c * HS_WP + tid];
+    WS[tid] = sw;
+  }
   const int ntn = (a.N + HS_NODES - 1) / HS_NODES;
   for (int lbk = blockIdx.x; lbk < ntn * a.Bn; lbk += gridDim.x) {
   const int b = lbk / ntn;
@@ -430,9 +440,9 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   __syncthreads();
   float* part = a.part + (int64_t)lbk * a.pstride;
   float* hb = HB + warp * HS_NODES * 12;
-  float lnw_acc[12], lnb_acc[12];
+  float lnw_acc[12];
   MSGAT_UNROLL
-  for (int t = 0; t < 12; ++t) { lnw_acc[t] = 0.f; lnb_acc[t] = 0.f; }
+  for (int t = 0; t < 12; ++t) lnw_acc[t] = 0.f;
   const int third = lane / 9, item = lane - third * 9, oq = item / 3, tq = item - oq * 3;
   for (int c = warp; c < C; c += HS_WARPS) {
     cp_async_wait<0>();   // each thread reads back only the rows it fetched itself
@@ -467,16 +477,25 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
       dB[8] = fmaf(yb, w2.x, dB[8]); dB[9] = fmaf(yb, w2.y, dB[9]); dB[10] = fmaf(yb, w2.z, dB[10]); dB[11] = fmaf(yb, w2.w, dB[11]);
     }
     // LayerNorm backward, masked by the ReLU that produced x, one row per (thread, node)
-    head_ln_bwd_row(dA, xa, hb + lane * 12, rsA, LW, lnw_acc, lnb_acc, a.x_is_relu,
+    head_ln_bwd_row(dA, xa, hb + lane * 12, rsA, LW, lnw_acc, a.x_is_relu,
                     liveA ? a.dx + (((int64_t)b * C + c) * a.N + nA) * 12 : nullptr);
-    head_ln_bwd_row(dB, xc, hb + (lane + 32) * 12, rsB, LW, lnw_acc, lnb_acc, a.x_is_relu,
+    head_ln_bwd_row(dB, xc, hb + (lane + 32) * 12, rsB, LW, lnw_acc, a.x_is_relu,
                     liveB ? a.dx + (((int64_t)b * C + c) * a.N + nB) * 12 : nullptr);
     __syncwarp();
     // fc weight gradient of channel c over the block's nodes
     float4 g0 = f4zero(), g1 = f4zero(), g2 = f4zero(), g3 = f4zero();
     if (lane < 27) {
-      for (int nl = third; nl < HS_NODES; nl += 3) {
-        const float4 d4 = ld4(DY + nl * 12 + oq * 4), h4 = ld4(hb + nl * 12 + tq * 4);
+      // a uniform trip count (node 64, which only the first third would reach, does not exist: 22, 21, 21 nodes) lets the compiler
+      // keep the loads of the next step in flight under the 16 FMAs of this one
+      const float* dyp = DY + third * 12 + oq * 4;
+      const float* hp = hb + third * 12 + tq * 4;
+      MSGAT_UNROLL_N(3)
+      for (int k = 0; k < 21; ++k) {
+        const float4 d4 = ld4(dyp + k * 36), h4 = ld4(hp + k * 36);
+        fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
+      }
+      if (third == 0) {
+        const float4 d4 = ld4(DY + 63 * 12 + oq * 4), h4 = ld4(hb + 63 * 12 + tq * 4);
         fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
       }
     }
@@ -487,18 +506,16 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
       gv[i] = (gv[i] + v1) + v2;
     }
     if (lane < 9) {
-      // 16 stores C floats apart: the offsets are rebuilt from an opaque base every channel (as loop invariants the compiler kept
-      // 16 64-bit addresses alive across the channel loop and spilled them: 19 % of the kernel's samples sat on their reloads)
-      int off = (oq * 48 + tq * 4) * C + c;
-      MSGAT_PIN(off);
+      // the partials of a logical block are CHANNEL-major, [c][o][t]: a lane's 4 x 4 block is four 16-byte stores into the 576
+      // contiguous bytes of its channel (as [o][t][c], the gradient's own layout, it was 16 four-byte stores C floats apart: 12 %
+      // of the kernel's samples); k_reduce transposes while it sums (RJob::tr)
+      float* pc = part + c * 144 + oq * 48 + tq * 4;
+      const float4 lw = ld4(LW + tq * 4), lb = ld4(LW + 12 + tq * 4);
       MSGAT_UNROLL
       for (int i = 0; i < 4; ++i) {
         const float bs = BS[oq * 4 + i];
-        MSGAT_UNROLL
-        for (int j = 0; j < 4; ++j) {
-          const int t = tq * 4 + j;
-          part[off + (i * 12 + j) * C] = fmaf(LW[t], gv[i * 4 + j], LW[12 + t] * bs);
-        }
+        st4(pc + i * 12, make_float4(fmaf(lw.x, gv[i * 4], lb.x * bs), fmaf(lw.y, gv[i * 4 + 1], lb.y * bs),
+                                     fmaf(lw.z, gv[i * 4 + 2], lb.z * bs), fmaf(lw.w, gv[i * 4 + 3], lb.w * bs)));
       }
     }
     __syncwarp();
@@ -506,13 +523,17 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   if (tid < 12) part[144 * C + tid] = BS[tid];
   MSGAT_UNROLL
   for (int t = 0; t < 12; ++t) {
-    const float w = warp_sum(lnw_acc[t]), bb = warp_sum(lnb_acc[t]);
-    if (lane == 0) { RED[warp * 24 + t] = w; RED[warp * 24 + 12 + t] = bb; }
+    const float w = warp_sum(lnw_acc[t]);
+    if (lane == 0) RED[warp * 24 + t] = w;
   }
   __syncthreads();
-  if (tid < 24) {
+  if (tid < 12) {
     float s = 0.f;
     for (int w = 0; w < HS_WARPS; ++w) s += RED[w * 24 + tid];
+    part[144 * C + 12 + tid] = s;
+  } else if (tid < 24) {
+    float s = 0.f;
+    for (int o = 0; o < 12; ++o) s = fmaf(BS[o], WS[o * 12 + tid - 12], s);
     part[144 * C + 12 + tid] = s;
   }
   __syncthreads();   // DY, BS, RED and the row buffers are the next logical block's
@@ -527,7 +548,7 @@ static int head_stream_grid(int N, int B, int M) {
   return g > lb ? lb : g;
 }
 static bool head_streaming(const msgat_head_desc* d) {
-  return d->Tout == 12 && ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4 <= 110 * 1024;
+  return d->Tout == 12 && ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12 + 144) * 4 <= 110 * 1024;
 }
 
 static int head_J(const msgat_head_desc* d, int ntile) {
@@ -601,7 +622,7 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   int nblk = a.J;
   if (head_streaming(d)) {
     nblk = (d->N + HS_NODES - 1) / HS_NODES;
-    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
+    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12 + 144) * 4;
     a.Bn = d->B;
     MSGAT_LAUNCH(k_head_bwd12, dim3(head_stream_grid(d->N, d->B, 1)), dim3(256), smem, stream, a, HeadGrp{});
   } else {
@@ -611,14 +632,15 @@ int msgat_head_backward(const msgat_head_desc* d, const float* x, const float* l
   ReduceArgs r;
   int nj = 0, tot = 0;
   const int nparts = nblk * d->B;
-  auto add = [&](float* dst, const float* src, int n) {
+  auto add = [&](float* dst, const float* src, int n, int tr = 0) {
     if (!dst) return;
     RJob jb = {};
     jb.dst[0] = dst; jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = 1; jb.doff = 0; jb.pstride = (int64_t)a.pstride; jb.f64 = 0;
+    jb.tr = tr;
     r.j[nj] = jb;
     r.starts[nj] = tot; tot += n; ++nj;
   };
-  add(d_fc_w, scratch, nW);
+  add(d_fc_w, scratch, nW, head_streaming(d) ? 144 : 0);   // k_head_bwd12 writes channel-major partials
   add(d_fc_b, scratch + nW, d->Tout);
   add(d_ln_w, scratch + nW + d->Tout, 12);
   add(d_ln_b, scratch + nW + d->Tout + 12, 12);
@@ -689,7 +711,7 @@ int msgat_heads_backward(const msgat_heads_desc* d, const float* x, const float*
   int nblk = a.J;
   if (head_streaming(&d1)) {
     nblk = (d->N + HS_NODES - 1) / HS_NODES;
-    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12) * 4;
+    size_t smem = ((size_t)d->C * HS_WP + HS_WARPS * HS_NODES * 12 + 2 * HS_NODES * 12 + 24 + 12 + HS_WARPS * 24 + HS_WARPS * HS_NODES * 12 + 144) * 4;
     a.Bn = d->B;
     MSGAT_LAUNCH(k_head_bwd12, dim3(head_stream_grid(d->N, d->B, d->M), 1, d->M), dim3(256), smem, stream, a, g);
   } else {
@@ -699,15 +721,16 @@ int msgat_heads_backward(const msgat_heads_desc* d, const float* x, const float*
   ReduceArgs r;
   int nj = 0, tot = 0;
   const int nparts = nblk * d->B;
-  auto add = [&](float* const* dst, const float* src, int n) {
+  auto add = [&](float* const* dst, const float* src, int n, int tr = 0) {
     if (!dst || !dst[0]) return;
     RJob jb = {};
     for (int m = 0; m < d->M; ++m) jb.dst[m] = dst[m];
     jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = 1; jb.doff = 0; jb.pstride = (int64_t)a.pstride; jb.f64 = 0;
+    jb.tr = tr;
     r.j[nj] = jb;
     r.starts[nj] = tot; tot += n; ++nj;
   };
-  add(d_fc_w, scratch, nW);
+  add(d_fc_w, scratch, nW, head_streaming(&d1) ? 144 : 0);   // k_head_bwd12 writes channel-major partials
   add(d_fc_b, scratch + nW, d->Tout);
   add(d_ln_w, scratch + nW + d->Tout, 12);
   add(d_ln_b, scratch + nW + d->Tout + 12, 12);

@@ -1146,7 +1146,7 @@ static int meam_backward_tail(Plan& p, BwdLayout& L, int Jw, const msgat_meam_pa
       if (!get(0) || n <= 0 || nj >= MAX_RJOBS) return;
       RJob jb;
       for (int m = 0; m < MSGAT_MAX_GROUP; ++m) jb.dst[m] = m < M ? get(m) : nullptr;
-      jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = dmul; jb.doff = doff; jb.pstride = pstride; jb.f64 = f64;
+      jb.src = src; jb.n = n; jb.nparts = nparts; jb.dmul = dmul; jb.doff = doff; jb.pstride = pstride; jb.f64 = f64; jb.tr = 0;
       r.j[nj] = jb;
       r.starts[nj] = tot; tot += n; ++nj;
     };

@@ -10,7 +10,9 @@
 #define MAX_RJOBS 28
 #define RED_WARPS 8
 // Grouped: blockIdx.y = component m writes dst[m] from src + m * sc_sm (floats).
-struct RJob { float* dst[MSGAT_MAX_GROUP]; const float* src; int n, nparts, dmul, doff; int64_t pstride; int f64; };  // f64: src holds doubles (pstride in doubles)
+// f64: src holds doubles (pstride in doubles).  tr > 0: the partials are [n / tr][tr] (e.g. channel-major fc weight gradients, written
+// by their producer as contiguous 16-byte quads) and the destination is the transposed [tr][n / tr] tensor.
+struct RJob { float* dst[MSGAT_MAX_GROUP]; const float* src; int n, nparts, dmul, doff; int64_t pstride; int f64; int tr; };
 struct ReduceArgs { RJob j[MAX_RJOBS]; int starts[MAX_RJOBS + 1]; int njobs; int64_t sc_sm; };
 #define LAUNCH_REDUCE(tot, M, stream, r) \
   MSGAT_LAUNCH(k_reduce, dim3(((tot) + 31) / 32, (M)), dim3(32 * RED_WARPS), RED_WARPS * 32 * sizeof(double), stream, r)
@@ -50,6 +52,7 @@ MSGAT_KERNEL MSGAT_LB(32 * RED_WARPS, 4) k_reduce(ReduceArgs a) {
     double t = 0.0;
     for (int k = 0; k < RED_WARPS; ++k) t += part[k][lane];
     const RJob& jb = a.j[q];
-    jb.dst[blockIdx.y][(int64_t)e * jb.dmul + jb.doff] = (float)t;
+    const int de = jb.tr > 0 ? (e % jb.tr) * (jb.n / jb.tr) + e / jb.tr : e;
+    jb.dst[blockIdx.y][(int64_t)de * jb.dmul + jb.doff] = (float)t;
   }
 }
