@@ -418,18 +418,28 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
   // the first channel's rows are in flight while the block stages dy
   if (warp < C) rows_fetch(stage, xb + (int64_t)warp * a.N * 12, nA, liveA, liveB, lane);
   cp_async_commit();
-  for (int it = tid; it < HS_NODES * 12; it += 256) {
-    const int nl = it / 12, o = it - nl * 12, n = n0 + nl;
-    float dy = 0.f;
-    if (n < a.N) {
-      const int64_t g = ((int64_t)b * a.N + n) * 12 + o;
-      const float d = a.dout[g];
-      const float gt = a.gate ? a.gate[b * a.gate_sb + (int64_t)n * 12 + o] : 1.f;
-      dy = d * gt;
-      if (a.d_gate) a.d_gate[g + (int64_t)b * (a.dgate_sb - (int64_t)a.N * a.Tout)] = d * a.head_out[g];
+  {
+    // the tile's 64 x 12 gradients are contiguous in dout / gate / head_out: three items per thread, all nine loads requested
+    // before the first use (one exposed round trip per logical block instead of three)
+    float dv[3], gv3[3], hv[3];
+    MSGAT_UNROLL
+    for (int u = 0; u < 3; ++u) {
+      const int it = tid + u * 256;
+      const bool ok = n0 + it / 12 < a.N;
+      const int64_t g = ((int64_t)b * a.N + n0) * 12 + it;
+      dv[u] = ok ? a.dout[g] : 0.f;
+      gv3[u] = (ok && a.gate) ? a.gate[b * a.gate_sb + (int64_t)n0 * 12 + it] : 1.f;
+      hv[u] = (ok && a.d_gate) ? a.head_out[g] : 0.f;
     }
-    DY[it] = dy;
-    DYT[o * HS_NODES + nl] = dy;
+    MSGAT_UNROLL
+    for (int u = 0; u < 3; ++u) {
+      const int it = tid + u * 256, nl = it / 12, o = it - nl * 12;
+      const float dy = dv[u] * gv3[u];
+      if (a.d_gate && n0 + nl < a.N)
+        a.d_gate[((int64_t)b * a.N + n0) * 12 + it + (int64_t)b * (a.dgate_sb - (int64_t)a.N * a.Tout)] = dv[u] * hv[u];
+      DY[it] = dy;
+      DYT[o * HS_NODES + nl] = dy;
+    }
   }
   __syncthreads();
   if (tid < 12) {
@@ -489,11 +499,16 @@ MSGAT_KERNEL MSGAT_LB(256, 2) k_head_bwd12(HeadArgs a0, HeadGrp grp) {
       // keep the loads of the next step in flight under the 16 FMAs of this one
       const float* dyp = DY + third * 12 + oq * 4;
       const float* hp = hb + third * 12 + tq * 4;
-      MSGAT_UNROLL_N(3)
-      for (int k = 0; k < 21; ++k) {
-        const float4 d4 = ld4(dyp + k * 36), h4 = ld4(hp + k * 36);
+      // software-pipelined by hand: the operands of step k + 1 are requested before the 16 FMAs of step k (with the loads at the
+      // top of each unrolled body 60 % of this loop's samples waited for shared memory)
+      float4 d4 = ld4(dyp), h4 = ld4(hp);
+      MSGAT_UNROLL_N(4)
+      for (int k = 1; k < 21; ++k) {
+        const float4 dn = ld4(dyp + k * 36), hn = ld4(hp + k * 36);
         fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
+        d4 = dn; h4 = hn;
       }
+      fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
       if (third == 0) {
         const float4 d4 = ld4(DY + 63 * 12 + oq * 4), h4 = ld4(hb + 63 * 12 + tq * 4);
         fma4(g0, d4.x, h4); fma4(g1, d4.y, h4); fma4(g2, d4.z, h4); fma4(g3, d4.w, h4);
