@@ -301,36 +301,69 @@ MSGAT_KERNEL MSGAT_LB(L1B_THREADS, (C >= 3 ? 2 : 3)) k_l1_bwd(L1BwdArgs a) {
       cp_async16(GT + o * PS + r * 4, Gb + ((int64_t)o * a.N + (nn < a.N ? nn : 0)) * 12 + (r % 3) * 4, nn < a.N);
     }
     cp_async_commit();
-    cp_async_wait<0>();
-    __syncthreads();
     const int n = n0 + nl;
     const bool live = rowthr && n < a.N;
+    // the node's x rows and its edge range are requested while the G tile is in flight (requested behind the barrier they were
+    // a second exposed round trip per tile: 14 % of the kernel's samples), and the next tile's G rows are pulled into L2
+    float4 xr[C][3];
+    int e_lo = 0, e_hi = 0;
+    MSGAT_UNROLL
+    for (int c = 0; c < C; ++c) {
+      xr[c][0] = xr[c][1] = xr[c][2] = f4zero();
+      if (live) {
+        const float* src = xb + c * a.x_sc + (int64_t)n * 12;
+        xr[c][0] = ld4(src); xr[c][1] = ld4(src + 4); xr[c][2] = ld4(src + 8);
+      }
+    }
+    if (live) { e_lo = a.row_ptr[n]; e_hi = a.row_ptr[n + 1]; }
+    // ... and so is the node's aggregated row (edge range -> column / weight -> Z rows: three dependent round trips that need
+    // nothing from the G tile)
+    float4 ag[C];
+    MSGAT_UNROLL
+    for (int c = 0; c < C; ++c) ag[c] = f4zero();
+    constexpr bool AGG_EARLY = C <= 2;   // measured: C = 1 273 -> 261 us; C = 3 327 -> 351 us (its 12 more live registers spill)
+    if (AGG_EARLY)
+      for (int e = e_lo; e < e_hi; ++e) {
+        const float w = pwb[e];
+        const float* zr = Zb + (int64_t)a.col_idx[e] * 12 + t0;
+        MSGAT_UNROLL
+        for (int c = 0; c < C; ++c) fma4(ag[c], w, ld4(zr + c * cs));
+      }
+#ifndef MSGAT_EMU
+    if (tile + a.J < a.ntile) {   // O rows of NT * 48 contiguous bytes: one prefetch per 128-byte line
+      const int n1 = (tile + a.J) * NT;
+      constexpr int LPR = (NT * 48 + 127) / 128 + 1;   // lines a row's run can touch
+      for (int i = tid; i < O * LPR; i += T) {
+        const int o = i / LPR, l = i - o * LPR;
+        const float* pa = Gb + ((int64_t)o * a.N + n1) * 12 + l * 32;
+        if (n1 + (l * 32) / 12 < a.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(pa));
+      }
+    }
+#endif
+    cp_async_wait<0>();
+    __syncthreads();
     float4 h4[C], dhc[C];
     if (rowthr) {
-      float4 x4[C], ot[C][4], ag[C];
+      float4 x4[C], ot[C][4];
       MSGAT_UNROLL
       for (int c = 0; c < C; ++c) {
-        float4 ra = f4zero(), rb = f4zero(), rd = f4zero();
-        x4[c] = h4[c] = ag[c] = f4zero();
+        float4 ra = xr[c][0], rb = xr[c][1], rd = xr[c][2];
+        x4[c] = h4[c] = f4zero();
         ot[c][0] = ot[c][1] = ot[c][2] = ot[c][3] = f4zero();
         if (live) {
-          const float* src = xb + c * a.x_sc + (int64_t)n * 12;
-          ra = ld4(src); rb = ld4(src + 4); rd = ld4(src + 8);
           x4[c] = l1_pick(ra, rb, rd, q);
           l1_row_ln(ra, rb, rd, LW, LW + 12);
           h4[c] = l1_pick(ra, rb, rd, q);
           l1_taps(ot[c], PtP, t0, a.d1, a.d2, ra, rb, rd);
         }
       }
-      if (live) {
-        const int e1 = a.row_ptr[n + 1];
-        for (int e = a.row_ptr[n]; e < e1; ++e) {
+      if (!AGG_EARLY)
+        for (int e = e_lo; e < e_hi; ++e) {
           const float w = pwb[e];
           const float* zr = Zb + (int64_t)a.col_idx[e] * 12 + t0;
           MSGAT_UNROLL
           for (int c = 0; c < C; ++c) fma4(ag[c], w, ld4(zr + c * cs));
         }
-      }
       const int po = nl * 12 + t0;
       MSGAT_UNROLL
       for (int c = 0; c < C; ++c) {
@@ -405,8 +438,8 @@ MSGAT_KERNEL MSGAT_LB(L1B_THREADS, (C >= 3 ? 2 : 3)) k_l1_bwd(L1BwdArgs a) {
         st4(a.DH + rowb + ((int64_t)c * a.N + n) * 12 + t0, dh);
       }
       // dS at the adjacency non-zeros of this row, edges e = q, q + 3, ... of the row
-      const int e1 = a.row_ptr[n + 1];
-      for (int e = a.row_ptr[n] + q; e < e1; e += 3) {
+      const int e1 = e_hi;
+      for (int e = e_lo + q; e < e1; e += 3) {
         const float* zr = Zb + (int64_t)a.col_idx[e] * 12;
         float s = 0.f;
         MSGAT_UNROLL
