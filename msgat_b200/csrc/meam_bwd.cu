@@ -529,7 +529,7 @@ struct SFinArgs {   // grouped: blockIdx.z = component (saved buffers sv_sm apar
   float *dqs, *Wg_part;
 };
 
-MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
+MSGAT_KERNEL MSGAT_LB(128, 4) k_sfin(SFinArgs a) {
   MSGAT_DYN_SMEM(smem_raw);
   float* WG = reinterpret_cast<float*>(smem_raw);  // [144]
   float* QD = WG + 144;                            // [128][24]: q, dU of every node of the block
@@ -547,25 +547,70 @@ MSGAT_KERNEL MSGAT_LB(128, 1) k_sfin(SFinArgs a) {
   for (int t = 0; t < 12; ++t) { q[t] = 0.f; dU[t] = 0.0; dq[t] = 0.f; }
   if (n < a.N) {
     const int64_t g = (int64_t)b * a.N + n;
+    // the edge ranges first: both edge loops below are chains of dependent gathers (range -> index / weight -> row)
+    const int e_lo = a.row_ptr[n], e_hi = a.row_ptr[n + 1], k_lo = a.csc_ptr[n], k_hi = a.csc_ptr[n + 1];
     const double dl = (double)a.delta[so + g];
-    MSGAT_UNROLL
-    for (int t = 0; t < 12; ++t) { q[t] = qb[(int64_t)n * 12 + t]; dU[t] = -dl * Eb[g * 12 + t]; dq[t] = a.dq_dense[so + g * 12 + t]; }
-    for (int e = a.row_ptr[n]; e < a.row_ptr[n + 1]; ++e) {
-      const double w = (double)ds[e];
-      const float* qi = qb + (int64_t)a.col_idx[e] * 12;
+    {
+      const float* qn = qb + (int64_t)n * 12;
+      const float* dn = a.dq_dense + so + g * 12;
+      const double* En = Eb + g * 12;
+      const float4 q0 = ld4(qn), q1 = ld4(qn + 4), q2 = ld4(qn + 8), d0 = ld4(dn), d1 = ld4(dn + 4), d2 = ld4(dn + 8);
+      q[0] = q0.x; q[1] = q0.y; q[2] = q0.z; q[3] = q0.w; q[4] = q1.x; q[5] = q1.y; q[6] = q1.z; q[7] = q1.w;
+      q[8] = q2.x; q[9] = q2.y; q[10] = q2.z; q[11] = q2.w;
+      dq[0] = d0.x; dq[1] = d0.y; dq[2] = d0.z; dq[3] = d0.w; dq[4] = d1.x; dq[5] = d1.y; dq[6] = d1.z; dq[7] = d1.w;
+      dq[8] = d2.x; dq[9] = d2.y; dq[10] = d2.z; dq[11] = d2.w;
       MSGAT_UNROLL
-      for (int t = 0; t < 12; ++t) dU[t] = fma(w, (double)qi[t], dU[t]);
+      for (int t = 0; t < 12; ++t) dU[t] = -dl * En[t];
     }
-    for (int k = a.csc_ptr[n]; k < a.csc_ptr[n + 1]; ++k) {
-      const float w = ds[a.csc_eid[k]];
-      const float* qr = qb + (int64_t)a.csc_row[k] * 12;
+    // four edges per step: their indices and weights, then their rows, are requested together (one pair of round trips per
+    // four edges instead of per edge); a step's dead slots carry weight 0 and the node's own row
+    for (int e = e_lo; e < e_hi; e += 4) {
+      float w[4];
+      float4 r[4][3];
       MSGAT_UNROLL
-      for (int t = 0; t < 12; ++t) {
-        float u = 0.f;
-        MSGAT_UNROLL
-        for (int t1 = 0; t1 < 12; ++t1) u = fmaf(qr[t1], WG[t1 * 12 + t], u);
-        dq[t] = fmaf(w, u, dq[t]);
+      for (int j = 0; j < 4; ++j) {
+        const bool ok = e + j < e_hi;
+        w[j] = ok ? ds[e + j] : 0.f;
+        const float* qi = qb + (int64_t)(ok ? a.col_idx[e + j] : n) * 12;
+        r[j][0] = ld4(qi); r[j][1] = ld4(qi + 4); r[j][2] = ld4(qi + 8);
       }
+      MSGAT_UNROLL
+      for (int j = 0; j < 4; ++j) {
+        const double wd = (double)w[j];
+        const float qi[12] = {r[j][0].x, r[j][0].y, r[j][0].z, r[j][0].w, r[j][1].x, r[j][1].y, r[j][1].z, r[j][1].w,
+                              r[j][2].x, r[j][2].y, r[j][2].z, r[j][2].w};
+        MSGAT_UNROLL
+        for (int t = 0; t < 12; ++t) dU[t] = fma(wd, (double)qi[t], dU[t]);
+      }
+    }
+    // sum_k dSnz[eid_k] U[row_k,:] with U = q Wg: the weighted rows are summed first, Wg is applied once
+    float v[12];
+    MSGAT_UNROLL
+    for (int t = 0; t < 12; ++t) v[t] = 0.f;
+    for (int k = k_lo; k < k_hi; k += 4) {
+      float w[4];
+      float4 r[4][3];
+      MSGAT_UNROLL
+      for (int j = 0; j < 4; ++j) {
+        const bool ok = k + j < k_hi;
+        w[j] = ok ? ds[a.csc_eid[k + j]] : 0.f;
+        const float* qr = qb + (int64_t)(ok ? a.csc_row[k + j] : n) * 12;
+        r[j][0] = ld4(qr); r[j][1] = ld4(qr + 4); r[j][2] = ld4(qr + 8);
+      }
+      MSGAT_UNROLL
+      for (int j = 0; j < 4; ++j) {
+        const float qr[12] = {r[j][0].x, r[j][0].y, r[j][0].z, r[j][0].w, r[j][1].x, r[j][1].y, r[j][1].z, r[j][1].w,
+                              r[j][2].x, r[j][2].y, r[j][2].z, r[j][2].w};
+        MSGAT_UNROLL
+        for (int t = 0; t < 12; ++t) v[t] = fmaf(w[j], qr[t], v[t]);
+      }
+    }
+    MSGAT_UNROLL
+    for (int t = 0; t < 12; ++t) {
+      float u = 0.f;
+      MSGAT_UNROLL
+      for (int t1 = 0; t1 < 12; ++t1) u = fmaf(v[t1], WG[t1 * 12 + t], u);
+      dq[t] += u;
     }
     MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) {
