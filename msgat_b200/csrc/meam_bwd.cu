@@ -672,6 +672,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
     for (int i = tid; i < C * C; i += T) Pc[i] = g_Pc[(int64_t)b * C * C + i];
     for (int i = tid; i < a.Oc * C; i += T) {
       double s = 0.0;
+      MSGAT_UNROLL_N(8)   // the partials of eight blocks requested together (same order of additions)
       for (int j = 0; j < a.Jm; ++j) s += g_dMc[((int64_t)b * a.Jm + j) * a.Oc * C + i];
       dMc[i] = s;
     }
@@ -734,6 +735,7 @@ MSGAT_KERNEL MSGAT_LB(1024, 1) k_bwd_small(BSmallArgs a) {
     for (int i = tid; i < 144; i += T) {
       Pt[i] = g_Pt[(int64_t)b * 144 + i];
       double s = 0.0;
+      MSGAT_UNROLL_N(8)
       for (int j = 0; j < a.J; ++j) s += g_dPt[((int64_t)b * a.J + j) * 144 + i];
       dSt[i] = s;
     }
@@ -775,6 +777,7 @@ MSGAT_KERNEL k_dwt(DwtArgs a) {
   if (i >= N * 20) return;
   const int n = i / 20, r = i - n * 20;
   float s = 0.f;
+  MSGAT_UNROLL_N(4)   // the rows of four samples requested together (same order of additions)
   for (int b = 0; b < B; ++b)
     MSGAT_UNROLL
     for (int t = 0; t < 12; ++t) s = fmaf(dK[(int64_t)b * 240 + t * 20 + r], qt[((int64_t)b * N + n) * 12 + t], s);
