@@ -33,6 +33,9 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
   float* QT = H + a.C * PS;                       // [P]
   float* LW = QT + P;                             // ln w,b [24]
   float* WsT = LW + 24;                           // [C][rup4(Os)] when s_pre
+  const int WS = (a.Os + 3) & ~3;
+  double* Wd = reinterpret_cast<double*>(WsT + (a.s_pre ? a.C * WS : 0));   // [20][NT + 1] Wt1 | Wt2 columns of the tile, as doubles
+  double* QTd = Wd + 20 * (NT + 1);               // [P] the temporal query, as doubles
   const int tile = blockIdx.x, b = blockIdx.y, m = blockIdx.z, n0 = tile * NT;
   const msgat_meam_params& PM = a.prm[m];
   float* const qs_m = a.qs + m * a.sv_sm;
@@ -40,12 +43,19 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
   float* const Z_m = a.Z + m * a.sv_sm;
   double* const pqc_m = reinterpret_cast<double*>(a.pqc + m * a.sc_sm);
   double* const pK_m = reinterpret_cast<double*>(a.pK + m * a.sc_sm);
-  const int WS = (a.Os + 3) & ~3;
   const int lim = a.N - n0 < NT ? a.N - n0 : NT;   // live nodes of the tile
   if (threadIdx.x < 12) {
     LW[threadIdx.x] = a.do_ln ? PM.ln_w[threadIdx.x] : 1.f;
     LW[12 + threadIdx.x] = a.do_ln ? PM.ln_b[threadIdx.x] : 0.f;
   }
+  // the tile's columns of Wt1 / Wt2 converted ONCE (the key partials below are 240 x NT fp64 products: converting both operands
+  // per product was 2 x 240 x NT conversions on the quarter-rate pipe, 46 % of the kernel's samples with the loads behind them)
+  if (a.Ot)
+    for (int i = threadIdx.x; i < 20 * NT; i += blockDim.x) {
+      const int r = i / NT, nl = i - r * NT;
+      const float* W = (r < 10) ? PM.ta_Wt1 + (int64_t)r * a.N : PM.ta_Wt2 + (int64_t)(r - 10) * a.N;
+      Wd[r * (NT + 1) + nl] = nl < lim ? (double)__ldg(W + n0 + nl) : 0.0;
+    }
   if (a.s_pre) stage_wT(WsT, PM.sa_W, a.Os, a.C, WS, 1, 0);
   __syncthreads();
   tile_load_ln(a.x + m * a.x_sm + b * a.x_sb, a.x_sc, a.C, a.N, n0, NT, PS, nullptr, H, LW, LW + 12, a.do_ln, nullptr);
@@ -56,7 +66,7 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
     float s = 0.f, t = 0.f;
     if (a.Os) for (int c = 0; c < a.C; ++c) s = fmaf(__ldg(PM.sa_alpha + c), H[c * PS + p], s);
     if (a.Ot) for (int c = 0; c < a.C; ++c) t = fmaf(__ldg(PM.ta_alpha + c), H[c * PS + p], t);
-    QT[p] = t;
+    QTd[p] = (double)t;
     if (n < a.N) {
       if (a.Os) qs_m[((int64_t)b * a.N + n0) * 12 + p] = s;
       if (a.Ot) qt_m[((int64_t)b * a.N + n0) * 12 + p] = t;
@@ -82,29 +92,28 @@ MSGAT_KERNEL MSGAT_LB(256, 3) k_prep(PrepArgs a) {
           if (o0 + j < a.Cz) st4(Z_m + (((int64_t)b * a.Cz + o0 + j) * a.N + n) * 12 + t0, acc[j]);
     }
   }
-  // per-tile partial of the channel query q_c[c,t] = sum_n alpha[n] h[c,n,t]  (attention.py:92)
+  __syncthreads();   // QTd (and H, already synchronised) complete
+  // per-tile partial of the temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T  (attention.py:65): threads 0..239
+  if (a.Ot && threadIdx.x < 240) {
+    double* dst = pK_m + ((int64_t)b * a.ntile + tile) * 240;
+    const int i = threadIdx.x, t = i / 20, r = i - t * 20;
+    const double* w = Wd + r * (NT + 1);
+    double s = 0.0;
+    MSGAT_UNROLL_N(8)
+    for (int nl = 0; nl < lim; ++nl) s += w[nl] * QTd[nl * 12 + t];
+    dst[i] = s;
+  }
+  // per-tile partial of the channel query q_c[c,t] = sum_n alpha[n] h[c,n,t]  (attention.py:92).  Independent of the keys: the
+  // items start on the 16 threads the key partials leave idle (a narrow input has 12 items: both run side by side; behind a
+  // barrier of its own this phase was 20 % of the kernel's samples)
   if (a.Oc) {
     double* dst = pqc_m + ((int64_t)b * a.ntile + tile) * a.C * 12;
-    for (int i = threadIdx.x; i < a.C * 12; i += blockDim.x) {
+    for (int i = (threadIdx.x + blockDim.x - 240) % blockDim.x; i < a.C * 12; i += blockDim.x) {
       const int c = i / 12, t = i - c * 12;
       double s = 0.0;
-      // same order of additions; without the per-node guard the loads of eight nodes are requested together (the guarded loop
-      // waited for one L1 / L2 round trip per node: a block of k_prep<64> took ~15 us for 3 KB of input)
+      // same order of additions; without the per-node guard the loads of eight nodes are requested together
       MSGAT_UNROLL_N(8)
       for (int nl = 0; nl < lim; ++nl) s += (double)__ldg(PM.ca_alpha + n0 + nl) * (double)H[c * PS + nl * 12 + t];
-      dst[i] = s;
-    }
-  }
-  __syncthreads();
-  // per-tile partial of the temporal keys K1 = q_t Wt1^T, K2 = q_t Wt2^T  (attention.py:65)
-  if (a.Ot) {
-    double* dst = pK_m + ((int64_t)b * a.ntile + tile) * 240;
-    for (int i = threadIdx.x; i < 240; i += blockDim.x) {
-      const int t = i / 20, r = i - t * 20;
-      const float* W = (r < 10) ? PM.ta_Wt1 + (int64_t)r * a.N : PM.ta_Wt2 + (int64_t)(r - 10) * a.N;
-      double s = 0.0;
-      MSGAT_UNROLL_N(8)
-      for (int nl = 0; nl < lim; ++nl) s += (double)__ldg(W + n0 + nl) * (double)QT[nl * 12 + t];
       dst[i] = s;
     }
   }
@@ -550,7 +559,8 @@ int meam_forward_impl(const Plan& p, const msgat_meam_params* prm, const msgat_a
     a.qs = saved + p.o_qs; a.qt = saved + p.o_qt; a.Z = saved + p.o_Z;
     a.pqc = scratch + p.o_pqc; a.pK = scratch + p.o_pK;
     const int NT = p.NTp;
-    size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4;
+    size_t smem = ((size_t)p.C * (NT * 12 + 4) + NT * 12 + 24 + (p.s_pre ? (size_t)p.C * rup4(p.Os) : 0)) * 4 +
+                  (20 * (size_t)(NT + 1) + NT * 12) * 8;
     if (NT == 64) MSGAT_LAUNCH(k_prep<64>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
     else MSGAT_LAUNCH(k_prep<16>, dim3(p.ntile_p, p.B, M), dim3(256), smem, stream, a);
   }
