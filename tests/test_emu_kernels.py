@@ -31,6 +31,18 @@ def test_emulated_kernels_match_reference_golden(case):
     assert not fails, "\n".join(fails)
 
 
+@pytest.mark.parametrize("nt", ["16", "32", "64"])
+def test_emulated_fix_pass_tile_sizes(nt, monkeypatch):
+    """k_bwd_fix picks 64- / 32-node tiles for narrow inputs; MSGAT_FIX_NT forces a size.  Every size must give the golden
+    gradients on a first-layer (C = 1) and a C = 5 operator (the partial-sum layout follows the tile count)."""
+    monkeypatch.setenv("MSGAT_FIX_NT", nt)
+    for case in ("meam_N37C1_d12", "meam_N23C5_peaked_d44"):
+        G = Golden(case)
+        out, grads, gin = run_case(G)
+        fails, _ = check_case(G, out, grads, gin)
+        assert not fails, f"MSGAT_FIX_NT={nt} {case}:\n" + "\n".join(fails)
+
+
 def test_emulated_head_kernels_ragged_shapes():
     """Streaming (Tout = 12) and generic head kernels on ragged node / channel counts (tests/head_cases.py)."""
     import torch
