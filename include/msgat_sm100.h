@@ -45,9 +45,12 @@ extern "C" {
                                  returned already multiplied by (x > 0) so that the previous
                                  MEAM can set MSGAT_F_DOUT_MASKED */
 
-#define MSGAT_PREC_FP32 0 /* fp32-grade results (1e-5 bar): CUDA-core fp32 and, for the layer-2 channel mixes,
-                             tcgen05 kind::tf32 with error-compensated operands (hi/lo split, "3xTF32") */
-#define MSGAT_PREC_TF32 1 /* single-pass tcgen05 kind::tf32 channel mixes in the forward (2e-3 bar) */
+#define MSGAT_PREC_FP32 0 /* fp32-grade results (1e-5 bar): CUDA-core fp32; the layer-2 channel mixes (forward, data and
+                             weight gradients) on tcgen05 kind::tf32 with error-compensated operands (hi/lo split,
+                             "3xTF32"); the N x N attention scores on tcgen05 with a three-way operand split, their
+                             second contraction in fp32 FFMA2 with fp64 sums (spatial_tc32.cu) */
+#define MSGAT_PREC_TF32 1 /* 2e-3 bar on outputs and parameter gradients: single-pass tcgen05 kind::tf32 channel mixes in
+                             the forward, both contractions of the N x N score passes on tcgen05 (spatial_tc.cu) */
 
 /* One MEAM-shaped operator.  With all three widths set, LN|RES|RELU|CMIX|SMIX it is
  * MEAM.forward (msgat.py:121-131); with a single width and no flags it is the bare
