@@ -1,6 +1,9 @@
 """Print the per-kernel table of a bench.py JSON line (developer helper): python tools/kt.py gpurun_out/x.json [filter]"""
 import json
+import signal
 import sys
+
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)   # `| head` closes the pipe early
 
 d = json.load(open(sys.argv[1]))
 flt = sys.argv[2] if len(sys.argv) > 2 else ""
